@@ -1,0 +1,241 @@
+// b200_common.cuh — element traits, 128/256-bit global memory access and the tile walker
+// shared by every kernel of libapex_b200.so.  sm_100a only.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "apex_b200.h"
+
+namespace b200 {
+
+constexpr int kVec = 8;            // elements one thread moves per memory instruction group
+constexpr uint32_t kTableMagic = 0x42325442u;
+
+// ------------------------------------------------------------------------------------------
+// Element conversions.  All arithmetic is done in fp32; storage types are widened on load and
+// rounded to nearest-even on store (same as Tensor.copy_ and oracle/amp_step_oracle.c).
+// ------------------------------------------------------------------------------------------
+template <int DT> struct Elem;
+template <> struct Elem<B200_F32> {
+    using type = float;
+    static __device__ __forceinline__ float to_float(float x) { return x; }
+    static __device__ __forceinline__ float from_float(float x) { return x; }
+};
+template <> struct Elem<B200_F16> {
+    using type = __half;
+    static __device__ __forceinline__ float to_float(__half x) { return __half2float(x); }
+    static __device__ __forceinline__ __half from_float(float x) { return __float2half_rn(x); }
+};
+template <> struct Elem<B200_BF16> {
+    using type = __nv_bfloat16;
+    static __device__ __forceinline__ float to_float(__nv_bfloat16 x) { return __bfloat162float(x); }
+    static __device__ __forceinline__ __nv_bfloat16 from_float(float x) { return __float2bfloat16_rn(x); }
+};
+
+// value a later reader of a DT-typed array would see for the fp32 value x
+template <int DT> __device__ __forceinline__ float round_through(float x) {
+    return Elem<DT>::to_float(Elem<DT>::from_float(x));
+}
+
+__device__ __forceinline__ bool is_finite(float x) {
+    return (__float_as_uint(x) & 0x7f800000u) != 0x7f800000u;
+}
+
+// ------------------------------------------------------------------------------------------
+// 8-element vector access.  fp32 columns use Blackwell's 256-bit LDG/STG (ld.global.v8.f32,
+// new with sm_100); fp16/bf16 columns use 128-bit.  Everything here streams exactly once, so
+// loads bypass L1 (L1::no_allocate); read-only columns additionally take the .nc path.
+// Requirements: address aligned to 32 B (fp32) / 16 B (16-bit types) — the table's row flag
+// guarantees it, otherwise the scalar path is taken.
+// ------------------------------------------------------------------------------------------
+template <bool kReadOnly>
+__device__ __forceinline__ void ldg256(const void* p, uint32_t (&r)[8]) {
+    if constexpr (kReadOnly) {
+        asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                     : "l"(p));
+    } else {
+        asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                     : "l"(p));
+    }
+}
+
+template <bool kReadOnly>
+__device__ __forceinline__ void ldg128(const void* p, uint32_t (&r)[4]) {
+    if constexpr (kReadOnly) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(p));
+    } else {
+        asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(p));
+    }
+}
+
+__device__ __forceinline__ void stg256(void* p, const uint32_t (&r)[8]) {
+    asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 :: "l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7])
+                 : "memory");
+}
+
+__device__ __forceinline__ void stg128(void* p, const uint32_t (&r)[4]) {
+    asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(p), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
+}
+
+// raw 8-element register image of a column slice
+template <int DT> struct Raw8 { uint32_t r[DT == B200_F32 ? 8 : 4]; };
+
+template <int DT, bool kReadOnly>
+__device__ __forceinline__ void load8(const void* base, int64_t idx, Raw8<DT>& raw) {
+    using T = typename Elem<DT>::type;
+    const T* p = reinterpret_cast<const T*>(base) + idx;
+    if constexpr (DT == B200_F32) ldg256<kReadOnly>(p, raw.r);
+    else ldg128<kReadOnly>(p, raw.r);
+}
+
+template <int DT>
+__device__ __forceinline__ void unpack8(const Raw8<DT>& raw, float (&f)[kVec]) {
+    if constexpr (DT == B200_F32) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) f[i] = __uint_as_float(raw.r[i]);
+    } else if constexpr (DT == B200_F16) {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            __half2 h = *reinterpret_cast<const __half2*>(&raw.r[i]);
+            f[2 * i] = __low2float(h);
+            f[2 * i + 1] = __high2float(h);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; i++) {   // bf16 -> f32 is a 16-bit shift
+            f[2 * i] = __uint_as_float(raw.r[i] << 16);
+            f[2 * i + 1] = __uint_as_float(raw.r[i] & 0xffff0000u);
+        }
+    }
+}
+
+template <int DT>
+__device__ __forceinline__ void store8(void* base, int64_t idx, const float (&f)[kVec]) {
+    using T = typename Elem<DT>::type;
+    T* p = reinterpret_cast<T*>(base) + idx;
+    if constexpr (DT == B200_F32) {
+        uint32_t r[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) r[i] = __float_as_uint(f[i]);
+        stg256(p, r);
+    } else if constexpr (DT == B200_F16) {
+        uint32_t r[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            __half2 h = __halves2half2(__float2half_rn(f[2 * i]), __float2half_rn(f[2 * i + 1]));
+            r[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        stg128(p, r);
+    } else {
+        uint32_t r[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            __nv_bfloat162 h = __halves2bfloat162(__float2bfloat16_rn(f[2 * i]), __float2bfloat16_rn(f[2 * i + 1]));
+            r[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        stg128(p, r);
+    }
+}
+
+template <int DT>
+__device__ __forceinline__ float load1(const void* base, int64_t idx) {
+    using T = typename Elem<DT>::type;
+    return Elem<DT>::to_float(reinterpret_cast<const T*>(base)[idx]);
+}
+
+template <int DT>
+__device__ __forceinline__ void store1(void* base, int64_t idx, float x) {
+    using T = typename Elem<DT>::type;
+    reinterpret_cast<T*>(base)[idx] = Elem<DT>::from_float(x);
+}
+
+// ------------------------------------------------------------------------------------------
+// Table access
+// ------------------------------------------------------------------------------------------
+struct TableView {
+    const b200_table_row* rows;
+    const b200_table_tile* tiles;
+    uint32_t n_tiles;
+    uint32_t tile_elems;
+};
+
+__device__ __forceinline__ TableView open_table(const void* table) {
+    const b200_table_header* h = reinterpret_cast<const b200_table_header*>(table);
+    const char* base = reinterpret_cast<const char*>(table);
+    TableView v;
+    v.rows = reinterpret_cast<const b200_table_row*>(base + __ldg(&h->rows_off));
+    v.tiles = reinterpret_cast<const b200_table_tile*>(base + __ldg(&h->tiles_off));
+    v.n_tiles = __ldg(&h->n_tiles);
+    v.tile_elems = __ldg(&h->tile_elems);
+    return v;
+}
+
+// Raise a 0/1 flag for the whole grid: one plain store per warp that saw something.  Every
+// writer stores the same value, so no atomic is needed.
+__device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
+    if (__any_sync(0xffffffffu, bad)) {
+        if ((threadIdx.x & 31) == 0) *flag = 1;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// The tile walker.  A persistent grid strides over the tile list; for each tile the CTA runs
+// Op's vector body over the 8-element groups and its scalar body over the ragged tail (or
+// over the whole tile when the row is not aligned for vector access).
+//
+// Op interface:
+//   using Params;                                      // kernel-argument payload
+//   struct Ctx;  static Ctx make_ctx(params, row)      // per-tile constants (group lookup…)
+//   template <int U> static void vec(row, ctx, idx[U], active[U], bad&)   // U groups in flight
+//   static void scalar(row, ctx, idx, bad&)
+// ------------------------------------------------------------------------------------------
+template <class Op, int kThreads, int kUnroll>
+__device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, bool& bad) {
+    const TableView tv = open_table(table);
+    for (uint32_t t = blockIdx.x; t < tv.n_tiles; t += gridDim.x) {
+        const uint2 tl_raw = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
+        const b200_table_tile tl{tl_raw.x, tl_raw.y};
+        const b200_table_row* rp = tv.rows + tl.tensor;
+        b200_table_row row;
+        {   // 64-byte row, four 128-bit read-only loads (uniform across the CTA, L1-resident)
+            const uint4* src = reinterpret_cast<const uint4*>(rp);
+            uint4* dst = reinterpret_cast<uint4*>(&row);
+#pragma unroll
+            for (int i = 0; i < 4; i++) dst[i] = __ldg(src + i);
+        }
+        const int64_t start = static_cast<int64_t>(tl.tile) * tv.tile_elems;
+        const int64_t left = row.numel - start;
+        const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left)
+                                                                   : static_cast<int>(tv.tile_elems);
+        const typename Op::Ctx ctx = Op::make_ctx(prm, row);
+        if (row.flags & 1u) {
+            const int n8 = n & ~(kVec - 1);
+            for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kUnroll) {
+                int64_t idx[kUnroll];
+                bool act[kUnroll];
+#pragma unroll
+                for (int u = 0; u < kUnroll; u++) {
+                    const int off = base + u * kThreads * kVec;
+                    act[u] = off < n8;
+                    idx[u] = start + off;
+                }
+                Op::template vec<kUnroll>(row, ctx, idx, act, bad);
+            }
+            const int tail = n - n8;
+            if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
+        } else {
+            for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
+        }
+    }
+}
+
+}  // namespace b200

@@ -1,0 +1,711 @@
+// kernels.cu — the sm_100a kernels of libapex_b200.so and their extern "C" launchers.
+//
+// Every kernel here is a single streaming pass bounded by HBM bandwidth: no
+// data is reused, so there is no shared-memory tiling and no tensor-core work; what matters is
+// 128/256-bit coalesced access, enough bytes in flight per SM, a persistent grid sized in
+// multiples of the SM count, and never touching a byte twice.
+//
+// Arithmetic contract: fp32, IEEE sqrt/div, explicit __f*_rn intrinsics so that nothing is
+// contracted into an FMA — results are bit-identical to oracle/amp_step_oracle.c.
+#include <atomic>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "b200_common.cuh"
+
+namespace b200 {
+
+// ============================================================================================
+// host-side state
+// ============================================================================================
+static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_ctas_per_sm{0};     // 0: per-kernel default
+static std::atomic<int> g_threads{256};
+static std::atomic<int> g_unroll{2};
+
+int set_error(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+static int cuda_fail(cudaError_t e, const char* what) {
+    return set_error(static_cast<int>(e), "%s: %s", what, cudaGetErrorString(e));
+}
+
+static int sm_count() {
+    static int cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+static unsigned grid_for(int64_t n_tiles, int default_ctas_per_sm) {
+    int per_sm = g_ctas_per_sm.load();
+    if (per_sm <= 0) per_sm = default_ctas_per_sm;
+    int64_t g = static_cast<int64_t>(sm_count()) * per_sm;
+    if (g > n_tiles) g = n_tiles;
+    if (g < 1) g = 1;
+    return static_cast<unsigned>(g);
+}
+
+static int after_launch(const char* name) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, name);
+    g_launches.fetch_add(1);
+    return 0;
+}
+
+// ============================================================================================
+// generic tile kernel
+// ============================================================================================
+template <class Op, int kThreads, int kUnroll>
+__global__ void __launch_bounds__(kThreads)
+tile_kernel(const void* __restrict__ table, const __grid_constant__ typename Op::Params prm) {
+    if (Op::skip(prm)) return;
+    bool bad = false;
+    walk_tiles<Op, kThreads, kUnroll>(table, prm, bad);
+    Op::finish(prm, bad);
+}
+
+template <class Op>
+static int launch_tiles(const char* name, const void* dev_table, int64_t n_tiles,
+                        const typename Op::Params& prm, int default_ctas_per_sm, void* stream) {
+    if (n_tiles <= 0) return 0;
+    if (dev_table == nullptr) return set_error(B200_EINVAL, "%s: dev_table is NULL", name);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int threads = g_threads.load(), unroll = g_unroll.load();
+    // a CTA moves threads*8*unroll elements per trip; keep ~the same CTA residency per SM
+    const unsigned grid = grid_for(n_tiles, default_ctas_per_sm * (threads == 512 ? 1 : 2));
+    if (threads == 512) {
+        if (unroll == 1) tile_kernel<Op, 512, 1><<<grid, 512, 0, st>>>(dev_table, prm);
+        else tile_kernel<Op, 512, 2><<<grid, 512, 0, st>>>(dev_table, prm);
+    } else {
+        if (unroll == 1) tile_kernel<Op, 256, 1><<<grid, 256, 0, st>>>(dev_table, prm);
+        else tile_kernel<Op, 256, 2><<<grid, 256, 0, st>>>(dev_table, prm);
+    }
+    return after_launch(name);
+}
+
+// ============================================================================================
+// multi_tensor_scale / axpby / check
+// ============================================================================================
+struct ScaleParams {
+    float scale;
+    const float* dev_scale;
+    int32_t* flag;
+};
+
+template <int I, int O>
+struct ScaleOp {
+    using Params = ScaleParams;
+    struct Ctx { float s; };
+    static __device__ __forceinline__ bool skip(const Params&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) {
+        return Ctx{p.dev_scale ? __ldg(p.dev_scale) : p.scale};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool& bad) {
+        Raw8<I> in[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) load8<I, true>(r.ptr[0], idx[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec];
+            unpack8<I>(in[u], x);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                bad |= !is_finite(x[i]);
+                x[i] = __fmul_rn(x[i], c.s);
+            }
+            store8<O>(r.ptr[1], idx[u], x);
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool& bad) {
+        const float x = load1<I>(r.ptr[0], i);
+        bad |= !is_finite(x);
+        store1<O>(r.ptr[1], i, __fmul_rn(x, c.s));
+    }
+    static __device__ __forceinline__ void finish(const Params& p, bool bad) {
+        if (p.flag) raise_flag(p.flag, bad);
+    }
+};
+
+struct AxpbyParams {
+    float a, b;
+    int32_t arg_to_check;
+    int32_t* flag;
+};
+
+template <int X, int Y, int O>
+struct AxpbyOp {
+    using Params = AxpbyParams;
+    struct Ctx { float a, b; int32_t chk; };
+    static __device__ __forceinline__ bool skip(const Params&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) {
+        return Ctx{p.a, p.b, p.arg_to_check};
+    }
+    static __device__ __forceinline__ float one(float x, float y, const Ctx& c, bool& bad) {
+        if (c.chk == 0) bad |= !is_finite(x);
+        else if (c.chk == 1) bad |= !is_finite(y);
+        else bad |= (!is_finite(x)) | (!is_finite(y));
+        return __fadd_rn(__fmul_rn(c.a, x), __fmul_rn(c.b, y));
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool& bad) {
+        Raw8<X> xr[U];
+        Raw8<Y> yr[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                load8<X, true>(r.ptr[0], idx[u], xr[u]);
+                load8<Y, false>(r.ptr[1], idx[u], yr[u]);   // y may alias out (in-place accumulate)
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec], y[kVec];
+            unpack8<X>(xr[u], x);
+            unpack8<Y>(yr[u], y);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) x[i] = one(x[i], y[i], c, bad);
+            store8<O>(r.ptr[2], idx[u], x);
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool& bad) {
+        store1<O>(r.ptr[2], i, one(load1<X>(r.ptr[0], i), load1<Y>(r.ptr[1], i), c, bad));
+    }
+    static __device__ __forceinline__ void finish(const Params& p, bool bad) {
+        if (p.flag) raise_flag(p.flag, bad);
+    }
+};
+
+struct CheckParams {
+    int32_t col;
+    int32_t* flag;
+};
+
+template <int I>
+struct CheckOp {
+    using Params = CheckParams;
+    struct Ctx { int32_t col; };
+    static __device__ __forceinline__ bool skip(const Params&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) { return Ctx{p.col}; }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool& bad) {
+        Raw8<I> in[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) load8<I, true>(r.ptr[c.col], idx[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec];
+            unpack8<I>(in[u], x);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) bad |= !is_finite(x[i]);
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool& bad) {
+        bad |= !is_finite(load1<I>(r.ptr[c.col], i));
+    }
+    static __device__ __forceinline__ void finish(const Params& p, bool bad) { raise_flag(p.flag, bad); }
+};
+
+// ============================================================================================
+// fused unscale + Adam + master->model copy
+// ============================================================================================
+struct AdamConsts {
+    float w1, one_m_w1, b2, w2, neg_step, bc2_sqrt, eps, wd, decay;
+    uint32_t flags;     // bit0 weight decay on, bit1 decoupled (AdamW), bit2 lerp "high weight" form
+};
+
+struct AdamParams {
+    AdamConsts grp[B200_MAX_GROUPS];
+    float inv_scale;
+    const float* dev_inv_scale;
+    const int32_t* dev_found_inf;
+};
+
+// One element, torch.optim.Adam's operation order (see oracle_adam for the line references).
+__device__ __forceinline__ void adam_elem(float g_in, float& p, float& m, float& v, const AdamConsts& k, float s) {
+    float g = __fmul_rn(g_in, s);
+    if (k.flags & 1u) {
+        if (k.flags & 2u) p = __fmul_rn(p, k.decay);
+        else g = __fadd_rn(g, __fmul_rn(k.wd, p));
+    }
+    const float d = __fsub_rn(g, m);
+    if (!(k.flags & 4u)) m = __fadd_rn(m, __fmul_rn(k.w1, d));
+    else m = __fsub_rn(g, __fmul_rn(d, k.one_m_w1));
+    v = __fadd_rn(__fmul_rn(v, k.b2), __fmul_rn(__fmul_rn(k.w2, g), g));
+    const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), k.bc2_sqrt), k.eps);
+    p = __fadd_rn(p, __fmul_rn(k.neg_step, __fdiv_rn(m, denom)));
+}
+
+template <int G, int S, int C>      // grad, state (p/m/v) and copy element types; C may be B200_NONE
+struct AdamOp {
+    using Params = AdamParams;
+    struct Ctx { AdamConsts k; float s; };
+    static constexpr int kCopyCol = 4;
+    static __device__ __forceinline__ bool skip(const Params& p) {
+        return p.dev_found_inf != nullptr && __ldg(p.dev_found_inf) != 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r) {
+        return Ctx{p.grp[r.group], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+        Raw8<G> rg[U];
+        Raw8<S> rp[U], rm[U], rv[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                load8<G, true>(r.ptr[0], idx[u], rg[u]);
+                load8<S, false>(r.ptr[1], idx[u], rp[u]);
+                load8<S, false>(r.ptr[2], idx[u], rm[u]);
+                load8<S, false>(r.ptr[3], idx[u], rv[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float g[kVec], p[kVec], m[kVec], v[kVec];
+            unpack8<G>(rg[u], g);
+            unpack8<S>(rp[u], p);
+            unpack8<S>(rm[u], m);
+            unpack8<S>(rv[u], v);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) adam_elem(g[i], p[i], m[i], v[i], c.k, c.s);
+            store8<S>(r.ptr[1], idx[u], p);
+            store8<S>(r.ptr[2], idx[u], m);
+            store8<S>(r.ptr[3], idx[u], v);
+            if constexpr (C != B200_NONE) {
+                if constexpr (S != B200_F32) {
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) p[i] = round_through<S>(p[i]);
+                }
+                store8<C>(r.ptr[kCopyCol], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        float p = load1<S>(r.ptr[1], i), m = load1<S>(r.ptr[2], i), v = load1<S>(r.ptr[3], i);
+        adam_elem(load1<G>(r.ptr[0], i), p, m, v, c.k, c.s);
+        store1<S>(r.ptr[1], i, p);
+        store1<S>(r.ptr[2], i, m);
+        store1<S>(r.ptr[3], i, v);
+        if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
+// ============================================================================================
+// fused unscale + SGD + master->model copy
+// ============================================================================================
+struct SgdConsts {
+    float wd, mu, damp, neg_lr;
+    uint32_t flags;     // bit0 wd on, bit1 momentum on, bit2 nesterov, bit3 first_run, bit4 wd_after_momentum
+};
+
+struct SgdParams {
+    SgdConsts grp[B200_MAX_GROUPS];
+    float inv_scale;
+    const float* dev_inv_scale;
+    const int32_t* dev_found_inf;
+};
+
+// torch.optim.SGD's order plus apex FusedSGD's extras (see oracle_sgd for the line references).
+template <int S>
+__device__ __forceinline__ void sgd_elem(float g_in, float& p, float& mom, const SgdConsts& k, float s) {
+    float g = __fmul_rn(g_in, s);
+    const bool wd_on = k.flags & 1u, wd_after = k.flags & 16u;
+    if (wd_on && !wd_after) g = __fadd_rn(g, __fmul_rn(k.wd, p));
+    if (k.flags & 2u) {
+        float b = (k.flags & 8u) ? g : __fadd_rn(__fmul_rn(mom, k.mu), __fmul_rn(k.damp, g));
+        mom = b;
+        b = round_through<S>(b);
+        g = (k.flags & 4u) ? __fadd_rn(g, __fmul_rn(k.mu, b)) : b;
+    }
+    if (wd_on && wd_after) g = __fadd_rn(g, __fmul_rn(k.wd, p));
+    p = __fadd_rn(p, __fmul_rn(k.neg_lr, g));
+}
+
+template <int G, int S, int C>
+struct SgdOp {
+    using Params = SgdParams;
+    struct Ctx { SgdConsts k; float s; };
+    static constexpr int kCopyCol = 3;
+    static __device__ __forceinline__ bool skip(const Params& p) {
+        return p.dev_found_inf != nullptr && __ldg(p.dev_found_inf) != 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r) {
+        return Ctx{p.grp[r.group], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+        const bool has_mom = c.k.flags & 2u;
+        const bool read_mom = has_mom && !(c.k.flags & 8u);
+        Raw8<G> rg[U];
+        Raw8<S> rp[U], rm[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                load8<G, true>(r.ptr[0], idx[u], rg[u]);
+                load8<S, false>(r.ptr[1], idx[u], rp[u]);
+                if (read_mom) load8<S, false>(r.ptr[2], idx[u], rm[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float g[kVec], p[kVec], m[kVec];
+            unpack8<G>(rg[u], g);
+            unpack8<S>(rp[u], p);
+            if (read_mom) unpack8<S>(rm[u], m);
+            else {
+#pragma unroll
+                for (int i = 0; i < kVec; i++) m[i] = 0.0f;
+            }
+#pragma unroll
+            for (int i = 0; i < kVec; i++) sgd_elem<S>(g[i], p[i], m[i], c.k, c.s);
+            store8<S>(r.ptr[1], idx[u], p);
+            if (has_mom) store8<S>(r.ptr[2], idx[u], m);
+            if constexpr (C != B200_NONE) {
+                if constexpr (S != B200_F32) {
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) p[i] = round_through<S>(p[i]);
+                }
+                store8<C>(r.ptr[kCopyCol], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        const bool has_mom = c.k.flags & 2u;
+        float p = load1<S>(r.ptr[1], i);
+        float m = (has_mom && !(c.k.flags & 8u)) ? load1<S>(r.ptr[2], i) : 0.0f;
+        sgd_elem<S>(load1<G>(r.ptr[0], i), p, m, c.k, c.s);
+        store1<S>(r.ptr[1], i, p);
+        if (has_mom) store1<S>(r.ptr[2], i, m);
+        if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
+// ============================================================================================
+// DDP bucket epilogue (flat buffer, in place)
+// ============================================================================================
+template <int DT, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+bucket_epilogue_kernel(void* __restrict__ buf, int64_t n, float factor, int read_only, int32_t* flag) {
+    using T = typename Elem<DT>::type;
+    constexpr int kU = 4;
+    constexpr int kAlign = (DT == B200_F32) ? 32 : 16;
+    bool bad = false;
+    T* x = reinterpret_cast<T*>(buf);
+    // ragged head up to the first aligned element
+    int64_t head = ((kAlign - (reinterpret_cast<uintptr_t>(x) & (kAlign - 1))) & (kAlign - 1)) / sizeof(T);
+    if (head > n) head = n;
+    const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    if (gtid < head) {
+        const float r = __fmul_rn(Elem<DT>::to_float(x[gtid]), factor);
+        const float rr = round_through<DT>(r);
+        bad |= !is_finite(rr);
+        if (!read_only) x[gtid] = Elem<DT>::from_float(r);
+    }
+    T* body = x + head;
+    const int64_t nb = n - head;
+    const int64_t n_groups = nb / kVec;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
+    for (int64_t g0 = gtid; g0 < n_groups; g0 += stride * kU) {
+        Raw8<DT> raw[kU];
+        bool act[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const int64_t g = g0 + u * stride;
+            act[u] = g < n_groups;
+            if (act[u]) load8<DT, false>(body, g * kVec, raw[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            if (!act[u]) continue;
+            float f[kVec];
+            unpack8<DT>(raw[u], f);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                f[i] = __fmul_rn(f[i], factor);
+                bad |= !is_finite(round_through<DT>(f[i]));
+            }
+            if (!read_only) store8<DT>(body, (g0 + u * stride) * kVec, f);
+        }
+    }
+    const int64_t tail0 = n_groups * kVec;
+    if (gtid < nb - tail0) {
+        const float r = __fmul_rn(Elem<DT>::to_float(body[tail0 + gtid]), factor);
+        bad |= !is_finite(round_through<DT>(r));
+        if (!read_only) body[tail0 + gtid] = Elem<DT>::from_float(r);
+    }
+    if (flag) raise_flag(flag, bad);
+}
+
+// ============================================================================================
+// loss-scaler state machine (one thread; the whole point is that it runs on the device)
+// ============================================================================================
+__global__ void scaler_init_kernel(b200_scaler_state* s, float init_scale) {
+    s->loss_scale = init_scale;
+    s->inv_scale = __fdiv_rn(1.0f, init_scale);
+    s->found_inf = 0;
+    s->unskipped = 0;
+    s->overflow_acc = 0;
+    s->seq = 0;
+    s->had_overflow = 0;
+    s->inv_loss_scale = s->inv_scale;
+}
+
+__global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scale_window, float scale_factor,
+                                     float min_scale, float max_scale, b200_scaler_state* mirror) {
+    b200_scaler_state st = *s;
+    const int flag = st.overflow_acc != 0;
+    st.inv_scale = __fdiv_rn(1.0f, st.loss_scale);
+    st.had_overflow = flag;
+    st.found_inf = (dynamic && flag) ? 1 : 0;
+    if (dynamic) {
+        if (flag) {
+            float ns = __fdiv_rn(st.loss_scale, 2.0f);
+            if (min_scale > 0.0f && ns < min_scale) ns = min_scale;
+            st.loss_scale = ns;
+            st.unskipped = 0;
+        } else {
+            st.unskipped += 1;
+        }
+        if (st.unskipped == scale_window) {
+            float ns = __fmul_rn(st.loss_scale, scale_factor);
+            if (ns > max_scale) ns = max_scale;
+            st.loss_scale = ns;
+            st.unskipped = 0;
+        }
+    }
+    st.overflow_acc = 0;
+    st.seq += 1;
+    st.inv_loss_scale = __fdiv_rn(1.0f, st.loss_scale);
+    *s = st;
+    if (mirror) {
+        // payload first, sequence number last, so a host that polls `seq` sees a whole record
+        volatile b200_scaler_state* mv = mirror;
+        mv->loss_scale = st.loss_scale;
+        mv->inv_scale = st.inv_scale;
+        mv->found_inf = st.found_inf;
+        mv->unskipped = st.unskipped;
+        mv->overflow_acc = 0;
+        mv->had_overflow = st.had_overflow;
+        mv->inv_loss_scale = st.inv_loss_scale;
+        __threadfence_system();
+        mv->seq = st.seq;
+    }
+}
+
+// ============================================================================================
+// dtype dispatch helpers
+// ============================================================================================
+static bool valid_dt(int dt) { return dt == B200_F32 || dt == B200_F16 || dt == B200_BF16; }
+
+#define B200_DISPATCH_DT(dt, NAME, ...)                                    \
+    switch (dt) {                                                          \
+    case B200_F32: { constexpr int NAME = B200_F32; __VA_ARGS__; } break;  \
+    case B200_F16: { constexpr int NAME = B200_F16; __VA_ARGS__; } break;  \
+    default: { constexpr int NAME = B200_BF16; __VA_ARGS__; } break;       \
+    }
+
+// The (grad, state, copy) triples the mixed-precision path produces:
+//   O2        : (f16|bf16, f32, same 16-bit)     fp16 model grad, fp32 master, fp16 model copy
+//   O2, BN    : (f32, f32, none)                 params kept in fp32
+//   O2 master grads materialised: (f32, f32, f16|bf16)
+//   O0 / O1   : (f32, f32, none)
+//   O3        : (f16, f16, none) / (bf16, bf16, none)
+//   O2 without copy (copy done elsewhere): (f16|bf16, f32, none)
+template <template <int, int, int> class OpT, class Params>
+static int dispatch_step(const char* name, int g, int s, int c, const void* tbl, int64_t n_tiles,
+                         const Params& prm, void* stream) {
+    constexpr int kCtas = 2;
+#define B200_TRY(G_, S_, C_) \
+    if (g == G_ && s == S_ && c == C_) return launch_tiles<OpT<G_, S_, C_>>(name, tbl, n_tiles, prm, kCtas, stream);
+    B200_TRY(B200_F16, B200_F32, B200_F16)
+    B200_TRY(B200_BF16, B200_F32, B200_BF16)
+    B200_TRY(B200_F32, B200_F32, B200_NONE)
+    B200_TRY(B200_F32, B200_F32, B200_F16)
+    B200_TRY(B200_F32, B200_F32, B200_BF16)
+    B200_TRY(B200_F16, B200_F16, B200_NONE)
+    B200_TRY(B200_BF16, B200_BF16, B200_NONE)
+    B200_TRY(B200_F16, B200_F32, B200_NONE)
+    B200_TRY(B200_BF16, B200_F32, B200_NONE)
+#undef B200_TRY
+    return set_error(B200_EDTYPE, "%s: (grad,state,copy) dtypes (%d,%d,%d) not instantiated", name, g, s, c);
+}
+
+}  // namespace b200
+
+// ================================================================================================
+// extern "C" entry points
+// ================================================================================================
+using namespace b200;
+
+extern "C" {
+
+int32_t b200_abi_version(void) { return B200_ABI_VERSION; }
+const char* b200_last_error(void) { return g_err; }
+int64_t b200_launch_count(void) { return g_launches.load(); }
+
+int32_t b200_set_launch_config(int32_t ctas_per_sm, int32_t threads, int32_t unroll) {
+    if (threads != 256 && threads != 512) return set_error(B200_EINVAL, "threads must be 256 or 512");
+    if (unroll != 1 && unroll != 2) return set_error(B200_EINVAL, "unroll must be 1 or 2");
+    if (ctas_per_sm < 0 || ctas_per_sm > 32) return set_error(B200_EINVAL, "ctas_per_sm out of range");
+    g_ctas_per_sm.store(ctas_per_sm);
+    g_threads.store(threads);
+    g_unroll.store(unroll);
+    return 0;
+}
+
+int32_t b200_table_upload(void* dev_image, const void* host_image, int64_t image_bytes, void* stream) {
+    if (!dev_image || !host_image || image_bytes <= 0) return set_error(B200_EINVAL, "table_upload: bad argument");
+    cudaError_t e = cudaMemcpyAsync(dev_image, host_image, static_cast<size_t>(image_bytes), cudaMemcpyHostToDevice,
+                                    static_cast<cudaStream_t>(stream));
+    return e == cudaSuccess ? 0 : cuda_fail(e, "table_upload");
+}
+
+int32_t b200_scaler_init(b200_scaler_state* dev_state, float init_scale, void* stream) {
+    if (!dev_state || !(init_scale > 0.0f)) return set_error(B200_EINVAL, "scaler_init: bad argument");
+    scaler_init_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(dev_state, init_scale);
+    return after_launch("scaler_init");
+}
+
+int32_t b200_scaler_update(b200_scaler_state* dev_state, int32_t dynamic, int32_t scale_window, float scale_factor,
+                           float min_scale, float max_scale, b200_scaler_state* mirror, void* stream) {
+    if (!dev_state) return set_error(B200_EINVAL, "scaler_update: dev_state is NULL");
+    if (dynamic && scale_window <= 0) return set_error(B200_EINVAL, "scaler_update: scale_window must be > 0");
+    scaler_update_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(dev_state, dynamic, scale_window, scale_factor,
+                                                                          min_scale, max_scale, mirror);
+    return after_launch("scaler_update");
+}
+
+int32_t b200_multi_tensor_scale(const void* dev_table, int64_t n_tiles, int32_t in_dtype, int32_t out_dtype, float scale,
+                                const float* dev_scale, int32_t* dev_flag, void* stream) {
+    if (!valid_dt(in_dtype) || !valid_dt(out_dtype)) return set_error(B200_EDTYPE, "multi_tensor_scale: bad dtype");
+    ScaleParams prm{scale, dev_scale, dev_flag};
+    B200_DISPATCH_DT(in_dtype, I,
+        B200_DISPATCH_DT(out_dtype, O,
+            return launch_tiles<ScaleOp<I, O>>("multi_tensor_scale", dev_table, n_tiles, prm, 4, stream)))
+    return 0;
+}
+
+int32_t b200_multi_tensor_axpby(const void* dev_table, int64_t n_tiles, int32_t x_dtype, int32_t y_dtype, int32_t out_dtype,
+                                float a, float b, int32_t arg_to_check, int32_t* dev_flag, void* stream) {
+    if (!valid_dt(x_dtype) || !valid_dt(y_dtype) || !valid_dt(out_dtype))
+        return set_error(B200_EDTYPE, "multi_tensor_axpby: bad dtype");
+    // apex uses axpby to merge freshly unscaled grads into stashed ones: out and y share a type.
+    if (y_dtype != out_dtype) return set_error(B200_EDTYPE, "multi_tensor_axpby: y and out must share a dtype");
+    AxpbyParams prm{a, b, arg_to_check, dev_flag};
+    B200_DISPATCH_DT(x_dtype, X,
+        B200_DISPATCH_DT(out_dtype, O,
+            return launch_tiles<AxpbyOp<X, O, O>>("multi_tensor_axpby", dev_table, n_tiles, prm, 4, stream)))
+    return 0;
+}
+
+int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles, int32_t col, int32_t dtype, int32_t* dev_flag,
+                                void* stream) {
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "multi_tensor_check: bad dtype");
+    if (col < 0 || col >= B200_MAX_DEPTH) return set_error(B200_EINVAL, "multi_tensor_check: bad column");
+    if (!dev_flag) return set_error(B200_EINVAL, "multi_tensor_check: dev_flag is NULL");
+    CheckParams prm{col, dev_flag};
+    B200_DISPATCH_DT(dtype, I, return launch_tiles<CheckOp<I>>("multi_tensor_check", dev_table, n_tiles, prm, 4, stream))
+    return 0;
+}
+
+int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                        const b200_adam_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
+                        const int32_t* dev_found_inf, void* stream) {
+    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
+        return set_error(B200_EINVAL, "fused_adam: n_groups must be 1..%d", B200_MAX_GROUPS);
+    AdamParams prm;
+    memset(&prm, 0, sizeof(prm));
+    for (int i = 0; i < n_groups; i++) {
+        const b200_adam_group& h = groups[i];
+        if (h.step < 1) return set_error(B200_EINVAL, "fused_adam: step must be >= 1");
+        AdamConsts& k = prm.grp[i];
+        // hyper-parameters are derived in double and rounded to float once, exactly like the
+        // Python scalars torch.optim.Adam hands to its fp32 tensor ops
+        k.w1 = static_cast<float>(1.0 - h.beta1);
+        k.one_m_w1 = 1.0f - k.w1;
+        k.b2 = static_cast<float>(h.beta2);
+        k.w2 = static_cast<float>(1.0 - h.beta2);
+        const double bc1 = h.bias_correction ? 1.0 - std::pow(h.beta1, static_cast<double>(h.step)) : 1.0;
+        const double bc2 = h.bias_correction ? 1.0 - std::pow(h.beta2, static_cast<double>(h.step)) : 1.0;
+        k.neg_step = static_cast<float>(-(h.lr / bc1));
+        k.bc2_sqrt = static_cast<float>(std::pow(bc2, 0.5));
+        k.eps = static_cast<float>(h.eps);
+        k.wd = static_cast<float>(h.weight_decay);
+        k.decay = static_cast<float>(1.0 - h.lr * h.weight_decay);
+        k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.adam_w_mode ? 2u : 0u) | (k.w1 < 0.5f ? 0u : 4u);
+    }
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.dev_found_inf = dev_found_inf;
+    return dispatch_step<AdamOp>("fused_adam", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                       const b200_sgd_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
+                       const int32_t* dev_found_inf, void* stream) {
+    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
+        return set_error(B200_EINVAL, "fused_sgd: n_groups must be 1..%d", B200_MAX_GROUPS);
+    SgdParams prm;
+    memset(&prm, 0, sizeof(prm));
+    for (int i = 0; i < n_groups; i++) {
+        const b200_sgd_group& h = groups[i];
+        SgdConsts& k = prm.grp[i];
+        k.wd = static_cast<float>(h.weight_decay);
+        k.mu = static_cast<float>(h.momentum);
+        k.damp = static_cast<float>(1.0 - h.dampening);
+        k.neg_lr = static_cast<float>(-h.lr);
+        k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.momentum != 0.0 ? 2u : 0u) | (h.nesterov ? 4u : 0u) |
+                  (h.first_run ? 8u : 0u) | (h.wd_after_momentum ? 16u : 0u);
+    }
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.dev_found_inf = dev_found_inf;
+    return dispatch_step<SgdOp>("fused_sgd", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype, float factor, int32_t* dev_flag, void* stream) {
+    if (numel < 0) return set_error(B200_EINVAL, "bucket_epilogue: negative numel");
+    if (numel == 0) return 0;
+    if (!dev_bucket) return set_error(B200_EINVAL, "bucket_epilogue: dev_bucket is NULL");
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "bucket_epilogue: bad dtype");
+    constexpr int kThreads = 256;
+    const int read_only = factor == 1.0f;
+    const int64_t groups = numel / kVec + 1;
+    int64_t blocks = (groups + kThreads * 4 - 1) / (kThreads * 4);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B200_DISPATCH_DT(dtype, DT,
+        (bucket_epilogue_kernel<DT, kThreads><<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(
+            dev_bucket, numel, factor, read_only, dev_flag)))
+    return after_launch("bucket_epilogue");
+}
+
+}  // extern "C"

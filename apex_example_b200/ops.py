@@ -1,0 +1,103 @@
+"""Thin Python launchers over the C ABI (include/apex_b200.h).  Every function enqueues one
+kernel of libapex_b200.so on the current CUDA stream and returns; none synchronises."""
+from __future__ import annotations
+
+import ctypes
+from typing import Sequence
+
+import torch
+
+from . import _lib
+from .tables import TensorTable, dtype_code
+
+AdamGroup, SgdGroup = _lib.AdamGroup, _lib.SgdGroup
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _addr(t) -> int:
+    """Device address of a tensor (or 0)."""
+    if t is None:
+        return 0
+    if isinstance(t, int):
+        return t
+    return t.data_ptr()
+
+
+def _require_cuda(t: TensorTable):
+    if t.dev.device.type != "cuda":
+        raise RuntimeError("libapex_b200 kernels need CUDA tensors; there is no CPU fallback")
+
+
+def multi_tensor_scale(table: TensorTable, in_dtype, out_dtype, scale: float = 1.0, dev_scale=None, dev_flag=None):
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_multi_tensor_scale(table.ptr, table.n_tiles, dtype_code(in_dtype), dtype_code(out_dtype),
+                                                   scale, _addr(dev_scale), _addr(dev_flag), _stream()),
+               "multi_tensor_scale")
+
+
+def multi_tensor_axpby(table: TensorTable, x_dtype, y_dtype, out_dtype, a: float, b: float, arg_to_check: int = -1,
+                       dev_flag=None):
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_multi_tensor_axpby(table.ptr, table.n_tiles, dtype_code(x_dtype), dtype_code(y_dtype),
+                                                   dtype_code(out_dtype), a, b, arg_to_check, _addr(dev_flag), _stream()),
+               "multi_tensor_axpby")
+
+
+def multi_tensor_check(table: TensorTable, col: int, dtype, dev_flag):
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_multi_tensor_check(table.ptr, table.n_tiles, col, dtype_code(dtype), _addr(dev_flag),
+                                                   _stream()), "multi_tensor_check")
+
+
+def fused_adam(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup],
+               inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+    _require_cuda(table)
+    arr = (AdamGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_fused_adam(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                           dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                           _addr(dev_found_inf), _stream()), "fused_adam")
+
+
+def fused_sgd(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[SgdGroup],
+              inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+    _require_cuda(table)
+    arr = (SgdGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_fused_sgd(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                          dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                          _addr(dev_found_inf), _stream()), "fused_sgd")
+
+
+def bucket_epilogue(bucket: torch.Tensor, factor: float, dev_flag=None):
+    if bucket.device.type != "cuda":
+        raise RuntimeError("libapex_b200 kernels need CUDA tensors; there is no CPU fallback")
+    if not bucket.is_contiguous():
+        raise RuntimeError("bucket must be contiguous")
+    _lib.check(_lib.load().b200_bucket_epilogue(bucket.data_ptr(), bucket.numel(), dtype_code(bucket.dtype), factor,
+                                                _addr(dev_flag), _stream()), "bucket_epilogue")
+
+
+# ---- loss-scaler state ------------------------------------------------------------------------
+SCALER_WORDS = 8            # sizeof(b200_scaler_state) / 4
+(IDX_LOSS_SCALE, IDX_INV_SCALE, IDX_FOUND_INF, IDX_UNSKIPPED, IDX_OVERFLOW_ACC, IDX_SEQ, IDX_HAD_OVERFLOW,
+ IDX_INV_LOSS_SCALE) = range(8)
+
+
+def scaler_init(state: torch.Tensor, init_scale: float):
+    _lib.check(_lib.load().b200_scaler_init(state.data_ptr(), init_scale, _stream()), "scaler_init")
+
+
+def scaler_update(state: torch.Tensor, dynamic: bool, scale_window: int, scale_factor: float, min_scale: float,
+                  max_scale: float, mirror: torch.Tensor | None = None):
+    _lib.check(_lib.load().b200_scaler_update(state.data_ptr(), int(dynamic), scale_window, scale_factor, min_scale,
+                                              max_scale, _addr(mirror), _stream()), "scaler_update")
+
+
+def set_launch_config(ctas_per_sm: int = 0, threads: int = 256, unroll: int = 2):
+    _lib.check(_lib.load().b200_set_launch_config(ctas_per_sm, threads, unroll), "set_launch_config")
+
+
+def launch_count() -> int:
+    return int(_lib.load().b200_launch_count())

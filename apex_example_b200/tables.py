@@ -1,0 +1,98 @@
+"""S1 — tensor-list tables: the host side of the multi_tensor_apply chunk scheduler.
+
+apex re-packs tensor addresses into kernel arguments on every ``multi_tensor_applier`` call
+(SURVEY.md §2.4 K1).  Here a list is described once by a table image (include/apex_b200.h),
+uploaded to device memory, and reused for as long as the tensors' addresses do not change.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Sequence
+
+import torch
+
+from . import _lib
+
+_DT = {torch.float32: _lib.F32, torch.float16: _lib.F16, torch.bfloat16: _lib.BF16}
+
+
+def dtype_code(dt) -> int:
+    if dt is None:
+        return _lib.NONE
+    try:
+        return _DT[dt]
+    except KeyError:
+        raise RuntimeError(f"libapex_b200 only supports fp16, bf16 and fp32 tensors, got {dt}") from None
+
+
+def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequence[int] | None = None,
+                tile_elems: int = _lib.TILE_ELEMS, pin: bool = False):
+    """Build the host image for ``columns`` (column-major: columns[d][t]).
+
+    Returns (uint8 host tensor, n_tiles).  Pure host code — works without a GPU.
+    """
+    lib = _lib.load()
+    depth = len(columns)
+    n = len(columns[0]) if depth else 0
+    if depth < 1 or depth > _lib.MAX_DEPTH:
+        raise RuntimeError(f"tensor_lists depth must be 1..{_lib.MAX_DEPTH}, got {depth}")
+    ref = None
+    for col in columns:
+        if len(col) != n:
+            raise RuntimeError("tensor_lists must all have the same length")
+        if ref is None and all(t is not None for t in col):
+            ref = col
+    if ref is None:
+        raise RuntimeError("at least one column must be fully present")
+    numel = (ctypes.c_int64 * max(n, 1))()
+    ptrs = (ctypes.c_void_p * max(n * depth, 1))()
+    esize = (ctypes.c_int32 * depth)()
+    for t in range(n):
+        numel[t] = ref[t].numel()
+    for d, col in enumerate(columns):
+        es = 4
+        for t, x in enumerate(col):
+            if x is None:
+                ptrs[d * n + t] = None
+                continue
+            if x.numel() != numel[t]:
+                raise RuntimeError(f"size mismatch in tensor_lists[{d}][{t}]: {x.numel()} vs {numel[t]}")
+            if not x.is_contiguous():
+                raise RuntimeError(f"tensor_lists[{d}][{t}] is not contiguous")
+            es = x.element_size()
+            ptrs[d * n + t] = x.data_ptr()
+        esize[d] = es if es in (2, 4) else 4
+    grp = None
+    if groups is not None:
+        grp = (ctypes.c_int32 * max(n, 1))(*groups)
+    nbytes = _lib.check(lib.b200_table_bytes(n, numel, tile_elems), "table_bytes", count=True)
+    image = torch.empty(nbytes, dtype=torch.uint8, pin_memory=pin)
+    n_tiles = _lib.check(lib.b200_table_build(image.data_ptr(), nbytes, n, depth, ptrs, esize, numel, grp,
+                                              tile_elems), "table_build", count=True)
+    return image, int(n_tiles)
+
+
+class TensorTable:
+    """A table image resident in device memory plus what the launchers need on the host."""
+
+    __slots__ = ("image", "dev", "n_tiles", "n_tensors", "total_elems", "signature", "keepalive")
+
+    def __init__(self, columns, groups=None, tile_elems: int = _lib.TILE_ELEMS, device=None, signature=None):
+        ref = next(c for c in columns if all(t is not None for t in c)) if columns and columns[0] else []
+        if device is None:
+            device = ref[0].device if len(ref) else torch.device("cuda")
+        self.image, self.n_tiles = build_image(columns, groups, tile_elems, pin=torch.cuda.is_available())
+        self.dev = self.image.to(device, non_blocking=True)
+        self.n_tensors = len(ref)
+        self.total_elems = sum(t.numel() for t in ref)
+        self.signature = signature
+        self.keepalive = None
+
+    @property
+    def ptr(self) -> int:
+        return self.dev.data_ptr()
+
+
+def signature_of(columns) -> tuple:
+    """Cheap identity of a list of columns: the device addresses (sizes are fixed per parameter)."""
+    return tuple(tuple(0 if t is None else t.data_ptr() for t in col) for col in columns)

@@ -1,0 +1,235 @@
+/*
+ * apex_b200.h — C ABI of libapex_b200.so
+ *
+ * The B200-native (sm_100a) replacement for the native layer that the reference
+ * script reaches through NVIDIA/apex (pinned at f3a960f8 by /root/reference/README.md:16-19,
+ * /root/reference/test_apex_distributed_spawn.py:13-16): the pybind modules `amp_C`
+ * (multi_tensor_scale / axpby / sgd / adam) and `apex_C` (flatten / unflatten), plus the
+ * host-side LossScaler state machine that apex keeps in Python.
+ *
+ * The reference call sites that end up here:
+ *   test_apex_distributed_spawn.py:160 (`with amp.scale_loss(...)`, exit)  -> unscale + overflow check + scale update
+ *   test_apex_distributed_spawn.py:161 (`scaled_loss.backward()`, DDP hooks) -> bucket flatten + allreduce epilogue
+ *   test_apex_distributed_spawn.py:164 (`optimizer.step()`)                 -> fused Adam / SGD + master->model copy
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / pybind types.
+ *   - every pointer named dev_* is a device address, host_* a host address.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - kernels never allocate, free or synchronise; they launch on `stream` and return.
+ *   - return value: 0 on success, a positive cudaError_t, or a negative B200_E* code.
+ *     b200_last_error() returns a thread-local message for the last non-zero return.
+ *   - numerical overflow of gradients is NOT an error: it raises the device flag and the
+ *     step is skipped on the device (same contract as apex's noop_flag / torch's found_inf).
+ */
+#ifndef APEX_B200_H_
+#define APEX_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+/* element types */
+#define B200_F32  0
+#define B200_F16  1
+#define B200_BF16 2
+#define B200_NONE (-1)          /* "column absent" (e.g. no fp16 model copy) */
+
+/* error codes (negative; positive values are cudaError_t) */
+#define B200_EINVAL   (-1)      /* bad argument */
+#define B200_ESIZE    (-2)      /* buffer too small / size beyond a stated maximum */
+#define B200_EDTYPE   (-3)      /* dtype combination not instantiated */
+#define B200_ENODEV   (-4)      /* no usable sm_100 device */
+
+#define B200_MAX_DEPTH   5      /* pointer columns per tensor row */
+#define B200_MAX_GROUPS  8      /* hyper-parameter groups one launch can carry */
+#define B200_TILE_ELEMS_DEFAULT 4096
+
+int32_t     b200_abi_version(void);
+const char* b200_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * S1 — chunk table ("multi_tensor_apply" scheduler).
+ * Replaces apex csrc/multi_tensor_apply.cuh (K1 in SURVEY.md §2.4), which re-packs tensor
+ * addresses into a <4 KB kernel-argument struct on every call and needs ceil(chunks/320)
+ * launches.  Here the list is described ONCE by a table that lives in device memory; every
+ * kernel below takes the table's device address and covers the whole list in one launch.
+ *
+ * Image layout (identical bytes on host and device):
+ *   b200_table_header | b200_table_row[n_tensors] | b200_table_tile[n_tiles]
+ * A row holds up to B200_MAX_DEPTH column pointers for one tensor (what each column means is
+ * fixed by the kernel that consumes the table, see below), its element count and its
+ * hyper-parameter group.  A tile is (tensor index, tile index inside the tensor); tile k of a
+ * tensor covers elements [k*tile_elems, min(numel,(k+1)*tile_elems)).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_table_header {
+    uint32_t magic;             /* 0x42325442 "B2TB" */
+    uint32_t version;           /* B200_ABI_VERSION */
+    uint32_t n_tensors;
+    uint32_t depth;
+    uint32_t tile_elems;
+    uint32_t n_tiles;
+    uint64_t rows_off;          /* byte offset of the row array from the image start */
+    uint64_t tiles_off;         /* byte offset of the tile array */
+    uint64_t total_elems;
+    uint64_t image_bytes;
+    uint64_t reserved;
+} b200_table_header;            /* 64 bytes */
+
+typedef struct b200_table_row {
+    void*    ptr[B200_MAX_DEPTH];
+    int64_t  numel;
+    uint32_t group;
+    uint32_t flags;             /* bit 0: every column is aligned for the 128/256-bit path */
+    uint64_t reserved;
+} b200_table_row;               /* 64 bytes */
+
+typedef struct b200_table_tile {
+    uint32_t tensor;
+    uint32_t tile;
+} b200_table_tile;              /* 8 bytes */
+
+/* Bytes of the image for a list with these element counts (zero-sized tensors get no tile).
+ * Returns <0 on error. */
+int64_t b200_table_bytes(int32_t n_tensors, const int64_t* numel, int32_t tile_elems);
+
+/* Fill `host_image` (at least b200_table_bytes() bytes).  `ptrs` is column-major:
+ * ptrs[d * n_tensors + t] is column d of tensor t (device addresses; may be NULL for an
+ * absent column).  elem_size[d] is the byte size of column d's element type (2 or 4) and
+ * decides the row's alignment flag.  `group` may be NULL (all zero).  Pure host code: usable
+ * without a GPU.  Returns the number of tiles (>=0) or a negative error. */
+int64_t b200_table_build(void* host_image, int64_t image_bytes,
+                         int32_t n_tensors, int32_t depth,
+                         const void* const* ptrs, const int32_t* elem_size,
+                         const int64_t* numel, const int32_t* group,
+                         int32_t tile_elems);
+
+/* Convenience for non-torch callers: cudaMemcpyAsync(host image -> device) on `stream`. */
+int32_t b200_table_upload(void* dev_image, const void* host_image, int64_t image_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * S4 — loss-scaler state, resident on the device.
+ * Replaces apex/amp/scaler.py LossScaler.update_scale (a6 in SURVEY.md §8a), which reads the
+ * overflow flag with .item() (a full stream sync per step).  Here the flag, the scale and the
+ * window counter stay in HBM; the optimizer kernels read `found_inf` / `inv_scale` directly.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_scaler_state {
+    float   loss_scale;         /* scale the NEXT backward is multiplied with */
+    float   inv_scale;          /* 1 / (scale of the backward whose grads await the step) */
+    int32_t found_inf;          /* 1: skip the pending step */
+    int32_t unskipped;          /* clean steps since the last change of scale */
+    int32_t overflow_acc;       /* raised by check / scale / epilogue kernels; cleared by update */
+    int32_t seq;                /* number of updates so far (lets the host see fresh mirrors) */
+    int32_t had_overflow;       /* overflow_acc as seen by the last update (also set when static) */
+    float   inv_loss_scale;     /* 1 / loss_scale: what an unscale BEFORE the next update multiplies by */
+} b200_scaler_state;            /* 32 bytes */
+
+/* Initialise *dev_state (loss_scale = init_scale, inv_scale = inv_loss_scale = 1/init_scale, rest 0). */
+int32_t b200_scaler_init(b200_scaler_state* dev_state, float init_scale, void* stream);
+
+/* One LossScaler.update_scale() on the device:
+ *   flag = overflow_acc != 0;  inv_scale = 1/loss_scale;  found_inf = dynamic && flag
+ *   dynamic: flag ? (loss_scale = max(min_scale, loss_scale/2), unskipped = 0) : ++unskipped;
+ *            unskipped == scale_window ? (loss_scale = min(max_scale, loss_scale*scale_factor), unskipped = 0)
+ *   overflow_acc = 0; ++seq; inv_loss_scale = 1/loss_scale
+ * min_scale <= 0 means "no minimum".  If `mirror` is non-NULL the new state is also stored
+ * there (a device-accessible host address, e.g. pinned memory) so the host can print apex's
+ * "Gradient overflow. Skipping step" line later without synchronising. */
+int32_t b200_scaler_update(b200_scaler_state* dev_state, int32_t dynamic,
+                           int32_t scale_window, float scale_factor,
+                           float min_scale, float max_scale,
+                           b200_scaler_state* mirror, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * amp_C.multi_tensor_scale (K2): column 0 = in, column 1 = out.  out = in * scale, and
+ * *dev_flag = 1 if any INPUT element is inf/NaN.  Used for the generic unscale
+ * (fp16 model grad -> fp32 master grad), the master->model weight copy (scale 1) and the DDP
+ * flatten (grads -> bucket views).  If dev_scale is non-NULL the factor is read from the
+ * device (e.g. &state->inv_scale) and `scale` is ignored.
+ * ------------------------------------------------------------------------------------------ */
+int32_t b200_multi_tensor_scale(const void* dev_table, int64_t n_tiles,
+                                int32_t in_dtype, int32_t out_dtype,
+                                float scale, const float* dev_scale,
+                                int32_t* dev_flag, void* stream);
+
+/* amp_C.multi_tensor_axpby (K3): columns x, y, out.  out = a*x + b*y; the flag is raised on
+ * non-finite x (arg_to_check 0), y (1) or either (-1). */
+int32_t b200_multi_tensor_axpby(const void* dev_table, int64_t n_tiles,
+                                int32_t x_dtype, int32_t y_dtype, int32_t out_dtype,
+                                float a, float b, int32_t arg_to_check,
+                                int32_t* dev_flag, void* stream);
+
+/* Overflow check only (read-only pass over column `col`): *dev_flag = 1 if any element is
+ * inf/NaN.  This is the "check" half of apex's unscale when the arithmetic half is fused into
+ * the optimizer kernel below. */
+int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles,
+                                int32_t col, int32_t dtype,
+                                int32_t* dev_flag, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * S2 — fused optimizer step: unscale + Adam/SGD + master->model cast in ONE pass.
+ * Replaces the three passes apex makes per step: multi_tensor_scale
+ * (unscale, a5), multi_tensor_adam / multi_tensor_sgd (K4/K5, a7) and multi_tensor_scale
+ * again (master->model copy, a8).
+ *
+ * Table columns: 0 = grad (read), 1 = param / fp32 master (read+write), 2 = exp_avg or
+ * momentum (rw), 3 = exp_avg_sq (rw, Adam only), last = model copy (write, optional):
+ *   Adam: depth 4 (g,p,m,v) or 5 (g,p,m,v,copy);  SGD: depth 3 (g,p,mom) or 4 (g,p,mom,copy).
+ * Grad handling: g = float(grad) * s, s = dev_inv_scale ? *dev_inv_scale : inv_scale.
+ * Skip: if dev_found_inf is non-NULL and *dev_found_inf != 0 the kernel writes nothing.
+ * Arithmetic is fp32 with IEEE sqrt/div and no fused multiply-add, in torch.optim's order
+ * (TORCH/optim/adam.py:414-547, TORCH/optim/sgd.py:340-380), so results are bit-identical to
+ * oracle/amp_step_oracle.c.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_adam_group {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;               /* 1-based step number used for bias correction */
+    int32_t bias_correction;    /* 0: bc1 = bc2 = 1 */
+    int32_t adam_w_mode;        /* 1: decoupled decay (AdamW, apex default); 0: L2 */
+} b200_adam_group;
+
+int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles,
+                        int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                        const b200_adam_group* groups, int32_t n_groups,
+                        float inv_scale, const float* dev_inv_scale,
+                        const int32_t* dev_found_inf, void* stream);
+
+typedef struct b200_sgd_group {
+    double  lr, momentum, dampening, weight_decay;
+    int32_t nesterov;
+    int32_t first_run;          /* 1: momentum buffer is uninitialised, mom = g */
+    int32_t wd_after_momentum;
+    int32_t reserved;
+} b200_sgd_group;
+
+int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles,
+                       int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                       const b200_sgd_group* groups, int32_t n_groups,
+                       float inv_scale, const float* dev_inv_scale,
+                       const int32_t* dev_found_inf, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * S3 — DDP bucket epilogue.  Replaces apex DistributedDataParallel.allreduce_bucket's
+ * `mul_(1/world_size)` + apex_C.unflatten + multi_tensor_scale copy-back (a4) and folds the
+ * overflow check of a5 into the same pass: in place on the flat bucket,
+ *   x = dtype(float(x) * factor);  *dev_flag = 1 if any result is inf/NaN.
+ * factor == 1 makes it a read-only check.  The bucket is one contiguous buffer, so no table.
+ * ------------------------------------------------------------------------------------------ */
+int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype,
+                             float factor, int32_t* dev_flag, void* stream);
+
+/* Tuning knobs (process-wide; defaults chosen by measurement): CTAs per SM of
+ * the persistent grids (0 = per-kernel default), threads per CTA (256 or 512) and how many
+ * 8-element groups each thread keeps in flight (1 or 2). */
+int32_t b200_set_launch_config(int32_t ctas_per_sm, int32_t threads, int32_t unroll);
+/* Number of kernels this library has launched since load (for bench.py's gpu_launches). */
+int64_t b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APEX_B200_H_ */

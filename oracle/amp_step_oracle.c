@@ -1,0 +1,343 @@
+/*
+ * amp_step_oracle.c — CPU restatement of the mixed-precision step hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Nothing under apex_example_b200/ may import, link or call this
+ * file; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs do, and there only as the checker or the timed CPU baseline.
+ *
+ * What it restates.  The reference script (/root/reference/test_apex_distributed_spawn.py)
+ * reaches this arithmetic through NVIDIA/apex pinned at f3a960f80244cf9e80558ab30f7f7e8cbf03c0a0
+ * (/root/reference/README.md:16-19).  Apex is NOT vendored and NOT installed here, so the
+ * algorithm is restated from (1) the numerical contract BASELINE.json's north_star names —
+ * torch.optim.Adam / torch.optim.SGD, whose source IS on disk — and (2) the published apex
+ * semantics summarised in SURVEY.md Appendix B.
+ *
+ * PARITY STATUS: unpinned against apex itself (the reference holds no golden vectors, tests
+ * or fixtures for this path and apex cannot be run here).  Pinned against torch 2.11's own
+ * CPU ops: tests/test_oracle.py checks every function below against torch.optim.Adam/AdamW/SGD
+ * (foreach=False), torch._amp_foreach_non_finite_check_and_unscale_, torch._amp_update_scale_
+ * and Tensor.copy_ casts, and against the committed fixtures in tests/golden/ that
+ * tests/golden/make_golden.py generated from those torch ops.
+ *
+ * Arithmetic rules (the CUDA kernels follow the same ones, which is why they match this file
+ * bit for bit): fp32 scalar math, IEEE sqrtf / division, NO fused multiply-add (compile with
+ * -ffp-contract=off), hyper-parameters derived in double and rounded to float once.
+ *
+ * TORCH = site-packages/torch (2.11.0).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#define DT_F32  0
+#define DT_F16  1
+#define DT_BF16 2
+
+/* ---- element conversions (software; round-to-nearest-even like Tensor.copy_) ------------ */
+static inline float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+static inline float half_to_float(uint16_t h) {
+    uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1fu, man = h & 0x3ffu;
+    if (exp == 0) {
+        if (man == 0) return u2f(sign);
+        /* subnormal: value = man * 2^-24 */
+        float v = (float)man * 5.9604644775390625e-08f;
+        return sign ? -v : v;
+    }
+    if (exp == 31) return u2f(sign | 0x7f800000u | (man << 13));
+    return u2f(sign | ((exp + 112u) << 23) | (man << 13));
+}
+
+static inline uint16_t float_to_half(float f) {
+    uint32_t x = f2u(f);
+    uint16_t sign = (uint16_t)((x >> 16) & 0x8000u);
+    uint32_t ax = x & 0x7fffffffu;
+    if (ax >= 0x7f800000u)                       /* inf / NaN */
+        return (uint16_t)(sign | 0x7c00u | (ax > 0x7f800000u ? 0x200u : 0u));
+    if (ax >= 0x477ff000u) return (uint16_t)(sign | 0x7c00u);   /* >= 65520 rounds to inf */
+    if (ax < 0x38800000u) {                      /* below the smallest normal half (2^-14) */
+        if (ax < 0x33000000u) return sign;       /* < 2^-25 rounds to zero */
+        uint32_t exp = ax >> 23;
+        uint32_t man = (ax & 0x7fffffu) | 0x800000u;
+        uint32_t shift = 126u - exp;             /* 14..24 */
+        uint32_t q = man >> shift;
+        uint32_t rem = man & ((1u << shift) - 1u), halfway = 1u << (shift - 1u);
+        if (rem > halfway || (rem == halfway && (q & 1u))) q++;
+        return (uint16_t)(sign | q);
+    }
+    uint32_t q = (ax - 0x38000000u) >> 13;       /* rebias 127 -> 15 */
+    uint32_t rem = ax & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (q & 1u))) q++;
+    return (uint16_t)(sign | q);
+}
+
+static inline float bf16_to_float(uint16_t b) { return u2f((uint32_t)b << 16); }
+
+static inline uint16_t float_to_bf16(float f) {
+    uint32_t x = f2u(f);
+    if ((x & 0x7fffffffu) > 0x7f800000u) return 0x7fffu;        /* NaN (cuda's canonical NaN) */
+    uint32_t lsb = (x >> 16) & 1u;
+    x += 0x7fffu + lsb;
+    return (uint16_t)(x >> 16);
+}
+
+static inline float load_as_float(const void* p, int dt, int64_t i) {
+    switch (dt) {
+    case DT_F16:  return half_to_float(((const uint16_t*)p)[i]);
+    case DT_BF16: return bf16_to_float(((const uint16_t*)p)[i]);
+    default:      return ((const float*)p)[i];
+    }
+}
+
+static inline void store_from_float(void* p, int dt, int64_t i, float v) {
+    switch (dt) {
+    case DT_F16:  ((uint16_t*)p)[i] = float_to_half(v); break;
+    case DT_BF16: ((uint16_t*)p)[i] = float_to_bf16(v); break;
+    default:      ((float*)p)[i] = v; break;
+    }
+}
+
+static inline int finite_f(float v) { return (f2u(v) & 0x7f800000u) != 0x7f800000u; }
+
+/* exported so the tests can pin the conversions against Tensor.copy_ / Tensor.float() */
+void oracle_convert(const void* in, int in_dt, void* out, int out_dt, int64_t n) {
+    for (int64_t i = 0; i < n; i++) store_from_float(out, out_dt, i, load_as_float(in, in_dt, i));
+}
+
+/* ---- overflow check --------------------------------------------------------------------- */
+/* apex LossScaler.unscale raises the flag if any INPUT element is inf/NaN;
+ * same rule as torch._amp_foreach_non_finite_check_and_unscale_ (TORCH/amp/grad_scaler.py:292-298). */
+int oracle_check(const void* g, int dt, int64_t n) {
+    int flag = 0;
+    #pragma omp parallel for reduction(|:flag) schedule(static)
+    for (int64_t i = 0; i < n; i++) flag |= !finite_f(load_as_float(g, dt, i));
+    return flag;
+}
+
+/* amp_C.multi_tensor_scale: out = in * scale, flag on non-finite input. */
+void oracle_scale(const void* in, int in_dt, void* out, int out_dt, int64_t n, float scale, int* flag) {
+    int f = 0;
+    #pragma omp parallel for reduction(|:f) schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float x = load_as_float(in, in_dt, i);
+        f |= !finite_f(x);
+        store_from_float(out, out_dt, i, x * scale);
+    }
+    if (f && flag) *flag = 1;
+}
+
+/* amp_C.multi_tensor_axpby: out = a*x + b*y. arg_to_check: 0 x, 1 y, -1 both. */
+void oracle_axpby(const void* x, int x_dt, const void* y, int y_dt, void* out, int out_dt,
+                  int64_t n, float a, float b, int arg_to_check, int* flag) {
+    int f = 0;
+    #pragma omp parallel for reduction(|:f) schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float xv = load_as_float(x, x_dt, i), yv = load_as_float(y, y_dt, i);
+        if (arg_to_check == 0) f |= !finite_f(xv);
+        else if (arg_to_check == 1) f |= !finite_f(yv);
+        else f |= (!finite_f(xv)) | (!finite_f(yv));
+        float ax = a * xv, by = b * yv;
+        store_from_float(out, out_dt, i, ax + by);
+    }
+    if (f && flag) *flag = 1;
+}
+
+/* ---- fused unscale + Adam + master->model copy ------------------------------------------- */
+typedef struct {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;
+    int32_t bias_correction;
+    int32_t adam_w_mode;
+} oracle_adam_group;
+
+/* Follows torch.optim.Adam's single-tensor path op for op:
+ *   TORCH/optim/adam.py:416-419  AdamW: param.mul_(1 - lr*wd)
+ *   TORCH/optim/adam.py:429      L2:    grad = grad.add(param, alpha=wd)
+ *   TORCH/optim/adam.py:457      exp_avg.lerp_(grad, 1-beta1)
+ *   TORCH/optim/adam.py:476      exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1-beta2)
+ *   TORCH/optim/adam.py:531-547  bias corrections in double; denom = sqrt(v)/sqrt(bc2)+eps;
+ *                                param.addcdiv_(exp_avg, denom, value=-lr/bc1)
+ * with apex FusedAdam's surroundings: grad is first multiplied by
+ * inv_scale (the unscale of LossScaler.unscale), and the fp16/bf16 model copy is written from
+ * the new fp32 master (apex _master_params_to_model_params).  State may be fp16/bf16 (O3):
+ * values are widened to float, updated, and rounded back. */
+void oracle_adam(const void* g, int g_dt, void* p, void* m, void* v, int s_dt,
+                 void* copy, int c_dt, int64_t n,
+                 const oracle_adam_group* grp, float inv_scale) {
+    const float w1 = (float)(1.0 - grp->beta1);
+    const float b2 = (float)grp->beta2;
+    const float w2 = (float)(1.0 - grp->beta2);
+    const double bc1 = grp->bias_correction ? 1.0 - pow(grp->beta1, (double)grp->step) : 1.0;
+    const double bc2 = grp->bias_correction ? 1.0 - pow(grp->beta2, (double)grp->step) : 1.0;
+    const float neg_step = (float)(-(grp->lr / bc1));
+    const float bc2_sqrt = (float)pow(bc2, 0.5);
+    const float eps = (float)grp->eps;
+    const float wd = (float)grp->weight_decay;
+    const float decay = (float)(1.0 - grp->lr * grp->weight_decay);
+    const int has_wd = grp->weight_decay != 0.0;
+    const int adamw = grp->adam_w_mode;
+
+    #pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float gi = load_as_float(g, g_dt, i) * inv_scale;
+        float pi = load_as_float(p, s_dt, i);
+        float mi = load_as_float(m, s_dt, i);
+        float vi = load_as_float(v, s_dt, i);
+        if (has_wd) {
+            if (adamw) pi = pi * decay;
+            else { float t = wd * pi; gi = gi + t; }
+        }
+        /* lerp_: ATen picks the form by |weight| < 0.5 */
+        float d = gi - mi;
+        if (w1 < 0.5f) { float t = w1 * d; mi = mi + t; }
+        else { float t = d * (1.0f - w1); mi = gi - t; }
+        float vb = vi * b2;
+        float t1 = w2 * gi;
+        float t2 = t1 * gi;
+        vi = vb + t2;
+        float denom = sqrtf(vi) / bc2_sqrt + eps;
+        float q = mi / denom;
+        float u = neg_step * q;
+        pi = pi + u;
+        store_from_float(p, s_dt, i, pi);
+        store_from_float(m, s_dt, i, mi);
+        store_from_float(v, s_dt, i, vi);
+        if (copy) store_from_float(copy, c_dt, i, s_dt == DT_F32 ? pi : load_as_float(p, s_dt, i));
+    }
+}
+
+/* ---- fused unscale + SGD + master->model copy -------------------------------------------- */
+typedef struct {
+    double  lr, momentum, dampening, weight_decay;
+    int32_t nesterov;
+    int32_t first_run;
+    int32_t wd_after_momentum;
+    int32_t reserved;
+} oracle_sgd_group;
+
+/* torch.optim.SGD single-tensor path (TORCH/optim/sgd.py:340-380: wd :356, first step
+ * buf = grad.clone() :361-363, buf.mul_(momentum).add_(grad, alpha=1-dampening) :365,
+ * nesterov :367-370, param.add_(grad, alpha=-lr) :380) plus apex FusedSGD's extras
+ * (SURVEY.md App. B.6): in-kernel grad scale, wd_after_momentum, first_run, model copy. */
+void oracle_sgd(const void* g, int g_dt, void* p, void* mom, int s_dt,
+                void* copy, int c_dt, int64_t n,
+                const oracle_sgd_group* grp, float inv_scale) {
+    const float wd = (float)grp->weight_decay;
+    const float mu = (float)grp->momentum;
+    const float damp = (float)(1.0 - grp->dampening);
+    const float neg_lr = (float)(-grp->lr);
+    const int has_wd = grp->weight_decay != 0.0;
+    const int has_mom = grp->momentum != 0.0;
+
+    #pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float gi = load_as_float(g, g_dt, i) * inv_scale;
+        float pi = load_as_float(p, s_dt, i);
+        if (has_wd && !grp->wd_after_momentum) { float t = wd * pi; gi = gi + t; }
+        if (has_mom) {
+            float bi;
+            if (grp->first_run) bi = gi;
+            else {
+                float a = load_as_float(mom, s_dt, i) * mu;
+                float t = damp * gi;
+                bi = a + t;
+            }
+            store_from_float(mom, s_dt, i, bi);
+            if (s_dt != DT_F32) bi = load_as_float(mom, s_dt, i);   /* what later ops see is the stored value */
+            if (grp->nesterov) { float t = mu * bi; gi = gi + t; }
+            else gi = bi;
+        }
+        if (has_wd && grp->wd_after_momentum) { float t = wd * pi; gi = gi + t; }
+        float u = neg_lr * gi;
+        pi = pi + u;
+        store_from_float(p, s_dt, i, pi);
+        if (copy) store_from_float(copy, c_dt, i, s_dt == DT_F32 ? pi : load_as_float(p, s_dt, i));
+    }
+}
+
+/* ---- loss-scaler state machine ------------------------------------------------------------ */
+typedef struct {
+    float   loss_scale;
+    float   inv_scale;
+    int32_t found_inf;
+    int32_t unskipped;
+    int32_t overflow_acc;
+    int32_t seq;
+    int32_t had_overflow;
+    float   inv_loss_scale;
+} oracle_scaler_state;
+
+/* apex LossScaler.update_scale; equal to torch._amp_update_scale_
+ * (TORCH/amp/grad_scaler.py:549-556) with backoff 0.5 / growth `scale_factor`, plus apex's
+ * max_loss_scale (2**24) and optional min_loss_scale which torch lacks. */
+void oracle_scaler_update(oracle_scaler_state* s, int dynamic, int scale_window,
+                          float scale_factor, float min_scale, float max_scale) {
+    int flag = s->overflow_acc != 0;
+    s->inv_scale = 1.0f / s->loss_scale;
+    s->had_overflow = flag;
+    s->found_inf = (dynamic && flag) ? 1 : 0;
+    if (dynamic) {
+        if (flag) {
+            float ns = s->loss_scale / 2.0f;
+            if (min_scale > 0.0f && ns < min_scale) ns = min_scale;
+            s->loss_scale = ns;
+            s->unskipped = 0;
+        } else {
+            s->unskipped += 1;
+        }
+        if (s->unskipped == scale_window) {
+            float ns = s->loss_scale * scale_factor;
+            if (ns > max_scale) ns = max_scale;
+            s->loss_scale = ns;
+            s->unskipped = 0;
+        }
+    }
+    s->overflow_acc = 0;
+    s->seq += 1;
+    s->inv_loss_scale = 1.0f / s->loss_scale;
+}
+
+/* ---- DDP bucket epilogue -------------------------------------------------------------------- */
+/* apex allreduce_bucket after the NCCL SUM: tensor.mul_(1/world_size) in the gradient dtype
+ * (SURVEY.md App. B.7), with the overflow check of the following unscale folded in. */
+void oracle_bucket_epilogue(void* x, int dt, int64_t n, float factor, int* flag) {
+    int f = 0;
+    #pragma omp parallel for reduction(|:f) schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float r = load_as_float(x, dt, i) * factor;
+        store_from_float(x, dt, i, r);
+        f |= !finite_f(load_as_float(x, dt, i));
+    }
+    if (f && flag) *flag = 1;
+}
+
+/* ---- whole-list step, used as the timed CPU baseline ------------------------------------------
+ * One O2 step over a tensor list the way the path runs it: check every gradient, and unless
+ * an overflow was found, unscale + Adam + model copy.  Returns the flag. */
+int oracle_adam_list(int n_tensors, const void* const* g, int g_dt,
+                     void* const* p, void* const* m, void* const* v, int s_dt,
+                     void* const* copy, int c_dt, const int64_t* numel,
+                     const oracle_adam_group* grp, float inv_scale, int check) {
+    int flag = 0;
+    if (check)
+        for (int t = 0; t < n_tensors; t++) flag |= oracle_check(g[t], g_dt, numel[t]);
+    if (flag) return 1;
+    for (int t = 0; t < n_tensors; t++)
+        oracle_adam(g[t], g_dt, p[t], m[t], v[t], s_dt, copy ? copy[t] : 0, c_dt, numel[t], grp, inv_scale);
+    return 0;
+}
+
+int oracle_sgd_list(int n_tensors, const void* const* g, int g_dt,
+                    void* const* p, void* const* mom, int s_dt,
+                    void* const* copy, int c_dt, const int64_t* numel,
+                    const oracle_sgd_group* grp, float inv_scale, int check) {
+    int flag = 0;
+    if (check)
+        for (int t = 0; t < n_tensors; t++) flag |= oracle_check(g[t], g_dt, numel[t]);
+    if (flag) return 1;
+    for (int t = 0; t < n_tensors; t++)
+        oracle_sgd(g[t], g_dt, p[t], mom ? mom[t] : 0, s_dt, copy ? copy[t] : 0, c_dt, numel[t], grp, inv_scale);
+    return 0;
+}
