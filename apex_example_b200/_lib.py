@@ -28,8 +28,15 @@ class AdamGroup(ctypes.Structure):           # b200_adam_group
 
 class SgdGroup(ctypes.Structure):            # b200_sgd_group
     _fields_ = [("lr", c_double), ("momentum", c_double), ("dampening", c_double),
-                ("weight_decay", c_double), ("nesterov", c_int32), ("first_run", c_int32),
-                ("wd_after_momentum", c_int32), ("reserved", c_int32)]
+                ("weight_decay", c_double), ("step", c_int64), ("nesterov", c_int32),
+                ("wd_after_momentum", c_int32)]
+
+
+class StepSync(ctypes.Structure):            # b200_step_sync
+    _fields_ = [("dev_counters", c_void_p), ("mirror", c_void_p), ("known_skips", c_int32),
+                ("read_only", c_int32)]
+
+STEP_WINDOW = 4
 
 
 class TableHeader(ctypes.Structure):         # b200_table_header
@@ -64,9 +71,9 @@ SIGNATURES = {
                                           c_int32, c_void_p, c_void_p]),
     "b200_multi_tensor_check": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
     "b200_fused_adam": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
-                                  c_int32, c_float, c_void_p, c_void_p, c_void_p]),
+                                  c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_fused_sgd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
-                                 c_int32, c_float, c_void_p, c_void_p, c_void_p]),
+                                 c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
     "b200_set_launch_config": (c_int32, [c_int32, c_int32, c_int32]),
     "b200_launch_count": (c_int64, []),

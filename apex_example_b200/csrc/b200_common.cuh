@@ -179,6 +179,44 @@ __device__ __forceinline__ TableView open_table(const void* table) {
     return v;
 }
 
+// ------------------------------------------------------------------------------------------
+// Step window (b200_step_sync): which of the host's candidate step numbers is the true one,
+// and the {calls, skips} bookkeeping that lets the host catch up without synchronising.
+// ------------------------------------------------------------------------------------------
+struct StepSync {
+    int32_t* counters;
+    int32_t* mirror;
+    int32_t known_skips;
+    int32_t read_only;
+};
+
+// returns true when the whole step must be skipped; `win` = candidate index otherwise
+__device__ __forceinline__ bool step_prologue(const int32_t* found_inf, const StepSync& ss, int& win) {
+    win = 0;
+    if (ss.counters) {
+        // counters[1] only changes in launches that skip (where `win` is not used), so every CTA of
+        // a stepping launch reads the same value no matter when it starts
+        const int d = *(reinterpret_cast<const volatile int32_t*>(ss.counters) + 1) - ss.known_skips;
+        win = d < 0 ? 0 : (d > B200_STEP_WINDOW - 1 ? B200_STEP_WINDOW - 1 : d);
+    }
+    return found_inf != nullptr && *reinterpret_cast<const volatile int32_t*>(found_inf) != 0;
+}
+
+__device__ __forceinline__ void step_epilogue(const StepSync& ss, bool skipped) {
+    if (ss.counters && !ss.read_only && blockIdx.x == 0 && threadIdx.x == 0) {
+        const int calls = ss.counters[0] + 1;
+        const int skips = ss.counters[1] + (skipped ? 1 : 0);
+        if (skipped) ss.counters[1] = skips;
+        ss.counters[0] = calls;
+        if (ss.mirror) {
+            volatile int32_t* m = ss.mirror;
+            m[1] = skips;
+            __threadfence_system();
+            m[0] = calls;
+        }
+    }
+}
+
 // Raise a 0/1 flag for the whole grid: one plain store per warp that saw something.  Every
 // writer stores the same value, so no atomic is needed.
 __device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
@@ -194,12 +232,13 @@ __device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
 //
 // Op interface:
 //   using Params;                                      // kernel-argument payload
-//   struct Ctx;  static Ctx make_ctx(params, row)      // per-tile constants (group lookup…)
+//   struct Ctx;  static Ctx make_ctx(params, row, win) // per-tile constants (group lookup…);
+//                                                      // win = step-window candidate (see b200_step_sync)
 //   template <int U> static void vec(row, ctx, idx[U], active[U], bad&)   // U groups in flight
 //   static void scalar(row, ctx, idx, bad&)
 // ------------------------------------------------------------------------------------------
 template <class Op, int kThreads, int kUnroll>
-__device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, bool& bad) {
+__device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, int win, bool& bad) {
     const TableView tv = open_table(table);
     for (uint32_t t = blockIdx.x; t < tv.n_tiles; t += gridDim.x) {
         const uint2 tl_raw = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
@@ -216,7 +255,7 @@ __device__ __forceinline__ void walk_tiles(const void* table, const typename Op:
         const int64_t left = row.numel - start;
         const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left)
                                                                    : static_cast<int>(tv.tile_elems);
-        const typename Op::Ctx ctx = Op::make_ctx(prm, row);
+        const typename Op::Ctx ctx = Op::make_ctx(prm, row, win);
         if (row.flags & 1u) {
             const int n8 = n & ~(kVec - 1);
             for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kUnroll) {

@@ -72,9 +72,10 @@ static int after_launch(const char* name) {
 template <class Op, int kThreads, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 tile_kernel(const void* __restrict__ table, const __grid_constant__ typename Op::Params prm) {
-    if (Op::skip(prm)) return;
+    int win = 0;
+    if (Op::prologue(prm, win)) return;
     bool bad = false;
-    walk_tiles<Op, kThreads, kUnroll>(table, prm, bad);
+    walk_tiles<Op, kThreads, kUnroll>(table, prm, win, bad);
     Op::finish(prm, bad);
 }
 
@@ -110,8 +111,8 @@ template <int I, int O>
 struct ScaleOp {
     using Params = ScaleParams;
     struct Ctx { float s; };
-    static __device__ __forceinline__ bool skip(const Params&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) {
+    static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
         return Ctx{p.dev_scale ? __ldg(p.dev_scale) : p.scale};
     }
     template <int U>
@@ -154,8 +155,8 @@ template <int X, int Y, int O>
 struct AxpbyOp {
     using Params = AxpbyParams;
     struct Ctx { float a, b; int32_t chk; };
-    static __device__ __forceinline__ bool skip(const Params&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) {
+    static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
         return Ctx{p.a, p.b, p.arg_to_check};
     }
     static __device__ __forceinline__ float one(float x, float y, const Ctx& c, bool& bad) {
@@ -203,8 +204,8 @@ template <int I>
 struct CheckOp {
     using Params = CheckParams;
     struct Ctx { int32_t col; };
-    static __device__ __forceinline__ bool skip(const Params&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&) { return Ctx{p.col}; }
+    static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) { return Ctx{p.col}; }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
                                                const bool (&act)[U], bool& bad) {
@@ -236,10 +237,11 @@ struct AdamConsts {
 };
 
 struct AdamParams {
-    AdamConsts grp[B200_MAX_GROUPS];
+    AdamConsts grp[B200_MAX_GROUPS][B200_STEP_WINDOW];   // [group][step-window candidate]
     float inv_scale;
     const float* dev_inv_scale;
     const int32_t* dev_found_inf;
+    StepSync sync;
 };
 
 // One element, torch.optim.Adam's operation order (see oracle_adam for the line references).
@@ -262,11 +264,13 @@ struct AdamOp {
     using Params = AdamParams;
     struct Ctx { AdamConsts k; float s; };
     static constexpr int kCopyCol = 4;
-    static __device__ __forceinline__ bool skip(const Params& p) {
-        return p.dev_found_inf != nullptr && __ldg(p.dev_found_inf) != 0;
+    static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
+        const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
+        if (skip) step_epilogue(p.sync, true);
+        return skip;
     }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r) {
-        return Ctx{p.grp[r.group], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win) {
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
     }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
@@ -311,7 +315,7 @@ struct AdamOp {
         store1<S>(r.ptr[3], i, v);
         if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
     }
-    static __device__ __forceinline__ void finish(const Params&, bool) {}
+    static __device__ __forceinline__ void finish(const Params& p, bool) { step_epilogue(p.sync, false); }
 };
 
 // ============================================================================================
@@ -323,10 +327,11 @@ struct SgdConsts {
 };
 
 struct SgdParams {
-    SgdConsts grp[B200_MAX_GROUPS];
+    SgdConsts grp[B200_MAX_GROUPS][B200_STEP_WINDOW];
     float inv_scale;
     const float* dev_inv_scale;
     const int32_t* dev_found_inf;
+    StepSync sync;
 };
 
 // torch.optim.SGD's order plus apex FusedSGD's extras (see oracle_sgd for the line references).
@@ -350,11 +355,13 @@ struct SgdOp {
     using Params = SgdParams;
     struct Ctx { SgdConsts k; float s; };
     static constexpr int kCopyCol = 3;
-    static __device__ __forceinline__ bool skip(const Params& p) {
-        return p.dev_found_inf != nullptr && __ldg(p.dev_found_inf) != 0;
+    static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
+        const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
+        if (skip) step_epilogue(p.sync, true);
+        return skip;
     }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r) {
-        return Ctx{p.grp[r.group], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win) {
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
     }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
@@ -403,7 +410,7 @@ struct SgdOp {
         if (has_mom) store1<S>(r.ptr[2], i, m);
         if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
     }
-    static __device__ __forceinline__ void finish(const Params&, bool) {}
+    static __device__ __forceinline__ void finish(const Params& p, bool) { step_epilogue(p.sync, false); }
 };
 
 // ============================================================================================
@@ -634,9 +641,15 @@ int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles, int32_t 
     return 0;
 }
 
+static StepSync to_sync(const b200_step_sync* s) {
+    StepSync r{nullptr, nullptr, 0, 0};
+    if (s) { r.counters = s->dev_counters; r.mirror = s->mirror; r.known_skips = s->known_skips; r.read_only = s->read_only; }
+    return r;
+}
+
 int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                         const b200_adam_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
-                        const int32_t* dev_found_inf, void* stream) {
+                        const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
     if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
         return set_error(B200_EINVAL, "fused_adam: n_groups must be 1..%d", B200_MAX_GROUPS);
     AdamParams prm;
@@ -644,48 +657,57 @@ int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dty
     for (int i = 0; i < n_groups; i++) {
         const b200_adam_group& h = groups[i];
         if (h.step < 1) return set_error(B200_EINVAL, "fused_adam: step must be >= 1");
-        AdamConsts& k = prm.grp[i];
-        // hyper-parameters are derived in double and rounded to float once, exactly like the
-        // Python scalars torch.optim.Adam hands to its fp32 tensor ops
-        k.w1 = static_cast<float>(1.0 - h.beta1);
-        k.one_m_w1 = 1.0f - k.w1;
-        k.b2 = static_cast<float>(h.beta2);
-        k.w2 = static_cast<float>(1.0 - h.beta2);
-        const double bc1 = h.bias_correction ? 1.0 - std::pow(h.beta1, static_cast<double>(h.step)) : 1.0;
-        const double bc2 = h.bias_correction ? 1.0 - std::pow(h.beta2, static_cast<double>(h.step)) : 1.0;
-        k.neg_step = static_cast<float>(-(h.lr / bc1));
-        k.bc2_sqrt = static_cast<float>(std::pow(bc2, 0.5));
-        k.eps = static_cast<float>(h.eps);
-        k.wd = static_cast<float>(h.weight_decay);
-        k.decay = static_cast<float>(1.0 - h.lr * h.weight_decay);
-        k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.adam_w_mode ? 2u : 0u) | (k.w1 < 0.5f ? 0u : 4u);
+        for (int w = 0; w < B200_STEP_WINDOW; w++) {
+            AdamConsts& k = prm.grp[i][w];
+            const int64_t step = h.step - w > 1 ? h.step - w : 1;
+            // hyper-parameters are derived in double and rounded to float once, exactly like the
+            // Python scalars torch.optim.Adam hands to its fp32 tensor ops
+            k.w1 = static_cast<float>(1.0 - h.beta1);
+            k.one_m_w1 = 1.0f - k.w1;
+            k.b2 = static_cast<float>(h.beta2);
+            k.w2 = static_cast<float>(1.0 - h.beta2);
+            const double bc1 = h.bias_correction ? 1.0 - std::pow(h.beta1, static_cast<double>(step)) : 1.0;
+            const double bc2 = h.bias_correction ? 1.0 - std::pow(h.beta2, static_cast<double>(step)) : 1.0;
+            k.neg_step = static_cast<float>(-(h.lr / bc1));
+            k.bc2_sqrt = static_cast<float>(std::pow(bc2, 0.5));
+            k.eps = static_cast<float>(h.eps);
+            k.wd = static_cast<float>(h.weight_decay);
+            k.decay = static_cast<float>(1.0 - h.lr * h.weight_decay);
+            k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.adam_w_mode ? 2u : 0u) | (k.w1 < 0.5f ? 0u : 4u);
+        }
     }
     prm.inv_scale = inv_scale;
     prm.dev_inv_scale = dev_inv_scale;
     prm.dev_found_inf = dev_found_inf;
+    prm.sync = to_sync(sync);
     return dispatch_step<AdamOp>("fused_adam", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
 }
 
 int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                        const b200_sgd_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
-                       const int32_t* dev_found_inf, void* stream) {
+                       const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
     if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
         return set_error(B200_EINVAL, "fused_sgd: n_groups must be 1..%d", B200_MAX_GROUPS);
     SgdParams prm;
     memset(&prm, 0, sizeof(prm));
     for (int i = 0; i < n_groups; i++) {
         const b200_sgd_group& h = groups[i];
-        SgdConsts& k = prm.grp[i];
-        k.wd = static_cast<float>(h.weight_decay);
-        k.mu = static_cast<float>(h.momentum);
-        k.damp = static_cast<float>(1.0 - h.dampening);
-        k.neg_lr = static_cast<float>(-h.lr);
-        k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.momentum != 0.0 ? 2u : 0u) | (h.nesterov ? 4u : 0u) |
-                  (h.first_run ? 8u : 0u) | (h.wd_after_momentum ? 16u : 0u);
+        if (h.step < 1) return set_error(B200_EINVAL, "fused_sgd: step must be >= 1");
+        for (int w = 0; w < B200_STEP_WINDOW; w++) {
+            SgdConsts& k = prm.grp[i][w];
+            const bool first_run = h.step - w <= 1;
+            k.wd = static_cast<float>(h.weight_decay);
+            k.mu = static_cast<float>(h.momentum);
+            k.damp = static_cast<float>(1.0 - h.dampening);
+            k.neg_lr = static_cast<float>(-h.lr);
+            k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.momentum != 0.0 ? 2u : 0u) | (h.nesterov ? 4u : 0u) |
+                      (first_run ? 8u : 0u) | (h.wd_after_momentum ? 16u : 0u);
+        }
     }
     prm.inv_scale = inv_scale;
     prm.dev_inv_scale = dev_inv_scale;
     prm.dev_found_inf = dev_found_inf;
+    prm.sync = to_sync(sync);
     return dispatch_step<SgdOp>("fused_sgd", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
 }
 

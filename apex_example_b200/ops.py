@@ -10,7 +10,8 @@ import torch
 from . import _lib
 from .tables import TensorTable, dtype_code
 
-AdamGroup, SgdGroup = _lib.AdamGroup, _lib.SgdGroup
+AdamGroup, SgdGroup, StepSync = _lib.AdamGroup, _lib.SgdGroup, _lib.StepSync
+STEP_WINDOW = _lib.STEP_WINDOW
 
 
 def _stream() -> int:
@@ -53,21 +54,52 @@ def multi_tensor_check(table: TensorTable, col: int, dtype, dev_flag):
 
 
 def fused_adam(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup],
-               inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+               inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None):
     _require_cuda(table)
     arr = (AdamGroup * len(groups))(*groups)
     _lib.check(_lib.load().b200_fused_adam(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
                                            dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
-                                           _addr(dev_found_inf), _stream()), "fused_adam")
+                                           _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
+                                           _stream()), "fused_adam")
 
 
 def fused_sgd(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[SgdGroup],
-              inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+              inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None):
     _require_cuda(table)
     arr = (SgdGroup * len(groups))(*groups)
     _lib.check(_lib.load().b200_fused_sgd(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
                                           dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
-                                          _addr(dev_found_inf), _stream()), "fused_sgd")
+                                          _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
+                                          _stream()), "fused_sgd")
+
+
+class StepCounter:
+    """Host half of b200_step_sync for one launch set: device {calls, skips}, a pinned mirror the
+    kernel writes, and the bookkeeping that turns them into an exact step number."""
+
+    def __init__(self, device):
+        self.dev = torch.zeros(2, dtype=torch.int32, device=device)
+        self.mirror = torch.zeros(2, dtype=torch.int32).pin_memory()
+        self.calls = 0                      # launches issued by the host
+        self.base_step = 0                  # successful steps before this counter existed (load_state_dict)
+
+    def next(self):
+        """Account for one more launch.  Returns (step, StepSync) where step is the 1-based step
+        number assuming no skip the host has not seen yet."""
+        self.calls += 1
+        seen_calls = int(self.mirror[0])
+        known_skips = int(self.mirror[1])
+        if self.calls - 1 - seen_calls > STEP_WINDOW - 1:
+            # the device is more than a window behind what the host has enqueued: wait for it
+            torch.cuda.current_stream(self.dev.device).synchronize()
+            known_skips = int(self.mirror[1])
+        step = self.base_step + self.calls - known_skips
+        return max(step, 1), StepSync(self.dev.data_ptr(), self.mirror.data_ptr(), known_skips, 0)
+
+    def exact_steps(self) -> int:
+        """Number of steps that really ran (synchronises)."""
+        torch.cuda.current_stream(self.dev.device).synchronize()
+        return self.base_step + int(self.mirror[0]) - int(self.mirror[1]) if self.calls else self.base_step
 
 
 def bucket_epilogue(bucket: torch.Tensor, factor: float, dev_flag=None):

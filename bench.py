@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py — the mixed-precision step hot path on B200 (BASELINE.json metric
+"fused optimizer step HBM GB/s").
+
+    python bench.py --gpus 1 --steps 50 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference            # the CPU restatement on the host cores
+
+Workload (BASELINE.json configs[1]): the 148-tensor / 124,439,808-element
+GPT-2-small parameter list at amp O2 — fp16 gradients carrying the loss scale, fp32 master / m / v,
+fp16 model copy.  One *step* = everything between backward and the next forward:
+  N = 1 : overflow check over the gradients -> loss-scaler update -> fused unscale+AdamW+copy
+  N > 1 : per gradient bucket NCCL all-reduce + epilogue (x 1/N and overflow check) -> loss-scaler
+          update -> fused unscale+AdamW+copy           (weak scaling: every rank owns a full replica)
+`value` = 28 B/param x params x ranks / step time, inputs resident in HBM.  `e2e` = the same step
+through the public API (apex.amp + apex.optimizers.FusedAdam) with the step's gradients copied in
+from pinned host memory and the scaler state read back, every step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+
+BYTES_PER_PARAM = 28            # 2 (fp16 g) + 12 (p,m,v in) + 12 (p,m,v out) + 2 (fp16 copy)
+LOSS_SCALE = 65536.0
+HYPER = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01)
+BUCKET_ELEMS = 10_000_000       # apex DistributedDataParallel message_size default
+
+
+def workload_sizes(name):
+    from workloads import GPT2_MEDIUM, GPT2_SMALL
+    if name == "gpt2_small":
+        return GPT2_SMALL, "GPT-2-small-shaped list: 148 tensors, 124,439,808 params, amp O2 (fp16 grad, fp32 master/m/v, fp16 copy)"
+    if name == "gpt2_medium":
+        return GPT2_MEDIUM, "GPT-2-medium-shaped list: 292 tensors, 354,823,168 params, amp O2"
+    raise SystemExit(f"unknown workload {name}")
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.idx = device_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"], stdout=f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1])); mx.append(float(c[2]))
+                except ValueError:
+                    continue
+                for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def host_list(sizes, seed=0):
+    """Seeded host tensors of the workload (also what the CPU baseline steps on)."""
+    g = torch.Generator().manual_seed(seed)
+    copy = [(torch.randn(n, generator=g) * 0.02).half() for n in sizes]
+    p = [c.float() for c in copy]
+    m = [torch.zeros(n) for n in sizes]
+    v = [torch.zeros(n) for n in sizes]
+    grad = [(torch.randn(n, generator=g) * 1e-3 * LOSS_SCALE).half() for n in sizes]
+    return grad, p, m, v, copy
+
+
+# ---------------------------------------------------------------------------------------------------
+# reference arm: the CPU restatement (oracle/) on the host cores
+# ---------------------------------------------------------------------------------------------------
+def run_cpu(sizes, steps, warmup):
+    import oracle
+    torch.set_num_threads(os.cpu_count() or 1)
+    grad, p, m, v, copy = host_list(sizes)
+    times = []
+    for s in range(warmup + steps):
+        t0 = time.perf_counter()
+        oracle.adam_list(grad, p, m, v, copy, inv_scale=1.0 / LOSS_SCALE, step=s + 1, adam_w_mode=True,
+                         check_overflow=True, **HYPER)
+        if s >= warmup:
+            times.append(time.perf_counter() - t0)
+    return times
+
+
+def omp_threads():
+    try:
+        import ctypes
+        return int(ctypes.CDLL("libgomp.so.1").omp_get_max_threads())
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def reference_arm(args, sizes, desc):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    n = sum(sizes)
+    steps = max(1, min(args.steps, 20))
+    warm = max(1, min(args.warmup, 2))
+    times = run_cpu(sizes, steps, warm)
+    t = sum(times) / len(times)
+    gbs = BYTES_PER_PARAM * n / t / 1e9
+    cores = omp_threads()
+    line = {
+        "impl": "reference", "metric": "fused optimizer step HBM GB/s", "value": gbs, "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "note": "reference's hot path lives in NVIDIA/apex (CUDA only, not installed); "
+                   "this arm times its CPU restatement oracle/amp_step_oracle.c on the host cores"},
+        "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
+                         "sample": f"full list, {steps} steps of check + unscale+AdamW+copy (OpenMP, {cores} threads)"},
+        "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="gpt2_small", choices=["gpt2_small", "gpt2_medium"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
+    ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
+    ap.add_argument("--ctas-per-sm", type=int, default=0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    sizes, desc = workload_sizes(args.workload)
+    if args.impl == "reference":
+        return reference_arm(args, sizes, desc)
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback (use --impl reference for the CPU restatement)")
+    import torch.distributed as dist
+    from apex_example_b200 import ops
+    from apex_example_b200.tables import TensorTable
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.threads or args.unroll or args.ctas_per_sm:
+        ops.set_launch_config(args.ctas_per_sm, args.threads or 256, args.unroll or 2)
+
+    n = sum(sizes)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    # gradients live in flat buckets (what apex DDP's flatten produces; at N=1 just contiguous storage)
+    gflat = (torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half()
+    grads = list(torch.split(gflat, sizes))
+    copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
+    p = [c.float() for c in copy]
+    m = [torch.zeros(s, device=dev) for s in sizes]
+    v = [torch.zeros(s, device=dev) for s in sizes]
+    table = TensorTable([grads, p, m, v, copy])
+    buckets = []
+    off = 0
+    while off < n:
+        end = min(n, off + BUCKET_ELEMS)
+        buckets.append(gflat[off:end])
+        off = end
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device=dev)
+    ops.scaler_init(state, LOSS_SCALE)
+    fstate = state.view(torch.float32)
+    inv_ref, found_ref, acc_ref = fstate[ops.IDX_INV_SCALE:], state[ops.IDX_FOUND_INF:], state[ops.IDX_OVERFLOW_ACC:]
+    step_no = [0]
+
+    def step(ev=None):
+        step_no[0] += 1
+        if world > 1:
+            # in-place SUM then x 1/N: after the first step every rank holds the mean, which the
+            # following steps reproduce exactly (N equal addends / N), so values stay finite
+            for b in buckets:
+                dist.all_reduce(b)
+                ops.bucket_epilogue(b, 1.0 / world, acc_ref)
+        else:
+            ops.multi_tensor_check(table, 0, torch.float16, acc_ref)
+        ops.scaler_update(state, True, 2000, 2.0, 0.0, 2.0 ** 24)
+        if ev is not None:
+            ev[0].record()
+        grp = [ops.AdamGroup(HYPER["lr"], HYPER["beta1"], HYPER["beta2"], HYPER["eps"], HYPER["weight_decay"],
+                             step_no[0], 1, 1)]
+        ops.fused_adam(table, torch.float16, torch.float32, torch.float16, grp, dev_inv_scale=inv_ref,
+                       dev_found_inf=found_ref)
+        if ev is not None:
+            ev[1].record()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ops.launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_begin.record()
+    for k in range(args.steps):
+        step(evs[k])
+    t_end.record()
+    barrier()
+    launches = ops.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    total_ms = t_begin.elapsed_time(t_end)
+    adam_ms = [a.elapsed_time(b) for a, b in evs]
+    if world > 1:
+        t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms = float(t.item())
+    ms_per_step = total_ms / args.steps
+    value = BYTES_PER_PARAM * n * world / (ms_per_step * 1e-3) / 1e9
+    skipped = int(state.cpu()[ops.IDX_FOUND_INF])
+    assert skipped == 0, "synthetic gradients are finite: the step must not have been skipped"
+
+    # ---- roofline of the dominant kernel (fused step) ----
+    peak, peak_src = peaks()
+    adam_avg_ms = sum(adam_ms) / len(adam_ms)
+    achieved = BYTES_PER_PARAM * n / (adam_avg_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": "tile_kernel<AdamOp<f16,f32,f16>> (b200_fused_adam)", "achieved": achieved,
+            "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+            "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
+            "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            roof["traffic"] = json.load(open(tpath)).get(args.workload)
+        except Exception:
+            pass
+
+    # ---- allreduce bus bandwidth (N > 1) ----
+    extra = {}
+    if world > 1:
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        reps = 10
+        for _ in range(reps):
+            for b in buckets:
+                dist.all_reduce(b)
+        a1.record()
+        barrier()
+        ar_ms = a0.elapsed_time(a1) / reps
+        t = torch.tensor([ar_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ar_ms = float(t.item())
+        nbytes = gflat.numel() * 2
+        extra["allreduce"] = {"bytes_per_step": nbytes, "buckets": len(buckets), "ms": ar_ms,
+                              "busbw_gbs": nbytes / (ar_ms * 1e-3) * 2 * (world - 1) / world / 1e9,
+                              "nvlink_peak_gbs_per_dir": 900.0}
+
+    # ---- e2e through the public API with host buffers ----
+    e2e = None
+    if not args.no_e2e:
+        del table
+        e2e = run_e2e(sizes, dev, world, max(3, min(args.steps, 20)), args.warmup, barrier)
+
+    # ---- CPU baseline (rank 0, N = 1 only) ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        times = run_cpu(sizes, 3, 1)
+        tc = sum(times) / len(times)
+        cores = omp_threads()
+        cpu = {"value": BYTES_PER_PARAM * n / tc / 1e9, "unit": "GB/s", "cores": cores, "kind": "port",
+               "cpu": cpu_model(), "ms_per_step": tc * 1e3,
+               "sample": f"full list, 3 steps of check + unscale+AdamW+copy via oracle/amp_step_oracle.c (OpenMP, {cores} threads)"}
+
+    if rank == 0:
+        line = {
+            "metric": "fused optimizer step HBM GB/s", "value": value, "unit": "GB/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
+                       "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
+                       "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS},
+            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        line.update(extra)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(sizes, dev, world, steps, warmup, barrier):
+    """Same step through apex.amp + apex.optimizers.FusedAdam; per step the gradients come from
+    pinned host memory (H2D) and the scaler state is read back (D2H)."""
+    import torch.distributed as dist
+    from apex import amp
+    from apex.optimizers import FusedAdam
+
+    n = sum(sizes)
+    gen = torch.Generator(device=dev).manual_seed(0)
+
+    class ParamList(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.ps = torch.nn.ParameterList(
+                [torch.nn.Parameter(torch.randn(s, device=dev, generator=gen) * 0.02) for s in sizes])
+
+    model = ParamList()
+    opt = FusedAdam(model.parameters(), lr=HYPER["lr"], betas=(HYPER["beta1"], HYPER["beta2"]), eps=HYPER["eps"],
+                    weight_decay=HYPER["weight_decay"], set_grad_none=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    host_g = (torch.randn(n) * 1e-3 * LOSS_SCALE).half().pin_memory()
+    dev_g = torch.empty(n, dtype=torch.float16, device=dev)
+    for prm, g in zip(model.parameters(), torch.split(dev_g, sizes)):
+        prm.grad = g
+    dummy = torch.zeros((), device=dev)
+    scaler = amp._amp_state.loss_scalers[0]
+
+    def one():
+        dev_g.copy_(host_g, non_blocking=True)                 # H2D: this step's gradients
+        if world > 1:
+            dist.all_reduce(dev_g)
+            dev_g.mul_(1.0 / world)
+        with amp.scale_loss(dummy, opt):
+            pass                                               # backward already "happened": grads are in place
+        opt.step()
+        return scaler.loss_scale()                             # D2H: the step's result (scale / skip state)
+
+    for _ in range(warmup):
+        one()
+    barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(steps):
+        one()
+    t1.record()
+    barrier()
+    ms = t0.elapsed_time(t1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return {"value": BYTES_PER_PARAM * n * world / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms,
+            "h2d_bytes_per_step": n * 2, "d2h_bytes_per_step": 32, "steps": steps,
+            "api": "apex.amp.scale_loss + apex.optimizers.FusedAdam.step (O2)"}
+
+
+if __name__ == "__main__":
+    main()

@@ -185,9 +185,28 @@ int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles,
  * (TORCH/optim/adam.py:414-547, TORCH/optim/sgd.py:340-380), so results are bit-identical to
  * oracle/amp_step_oracle.c.
  * ------------------------------------------------------------------------------------------ */
+/* Exact step numbers without a host sync.
+ * apex decides "skip" on the host, so its step counter (Adam's bias correction, SGD's first_run)
+ * only advances on steps that really ran.  Here the decision is taken on the device, after the
+ * host has already enqueued the step kernel, so the host cannot know the exact step number when
+ * it computes the hyper-parameters.  b200_step_sync closes the gap: the kernel keeps
+ * {calls, skips} in `dev_counters` (and mirrors them to `mirror`); the host passes the skips it
+ * had observed (`known_skips`) and derives every per-step constant for the B200_STEP_WINDOW
+ * candidates step, step-1, ... ; the kernel picks candidate (skips_now - known_skips).
+ * The caller must not let more than B200_STEP_WINDOW-1 launches be unobserved (it synchronises
+ * if the mirror lags that far; in steady state it never does).  NULL = the host's `step` is exact. */
+#define B200_STEP_WINDOW 4
+typedef struct b200_step_sync {
+    int32_t* dev_counters;      /* int32[2] {calls, skips}, zeroed by the caller before first use */
+    int32_t* mirror;            /* device-accessible host int32[2] (pinned), or NULL */
+    int32_t  known_skips;       /* skips already reflected in the groups' `step` */
+    int32_t  read_only;         /* 1: use the counters but do not advance them (2nd, 3rd ... launch
+                                   of one optimizer step that is split over several dtype sets) */
+} b200_step_sync;
+
 typedef struct b200_adam_group {
     double  lr, beta1, beta2, eps, weight_decay;
-    int64_t step;               /* 1-based step number used for bias correction */
+    int64_t step;               /* 1-based number of this step if no unobserved skip happened */
     int32_t bias_correction;    /* 0: bc1 = bc2 = 1 */
     int32_t adam_w_mode;        /* 1: decoupled decay (AdamW, apex default); 0: L2 */
 } b200_adam_group;
@@ -196,21 +215,22 @@ int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles,
                         int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                         const b200_adam_group* groups, int32_t n_groups,
                         float inv_scale, const float* dev_inv_scale,
-                        const int32_t* dev_found_inf, void* stream);
+                        const int32_t* dev_found_inf, const b200_step_sync* sync,
+                        void* stream);
 
 typedef struct b200_sgd_group {
     double  lr, momentum, dampening, weight_decay;
+    int64_t step;               /* as above; step 1 is apex's first_run (momentum buffer = grad) */
     int32_t nesterov;
-    int32_t first_run;          /* 1: momentum buffer is uninitialised, mom = g */
     int32_t wd_after_momentum;
-    int32_t reserved;
 } b200_sgd_group;
 
 int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles,
                        int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                        const b200_sgd_group* groups, int32_t n_groups,
                        float inv_scale, const float* dev_inv_scale,
-                       const int32_t* dev_found_inf, void* stream);
+                       const int32_t* dev_found_inf, const b200_step_sync* sync,
+                       void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * S3 — DDP bucket epilogue.  Replaces apex DistributedDataParallel.allreduce_bucket's

@@ -41,6 +41,7 @@ def test_struct_sizes_match_header():
     assert ctypes.sizeof(_lib.TableTile) == 8
     assert ctypes.sizeof(_lib.AdamGroup) == 56
     assert ctypes.sizeof(_lib.SgdGroup) == 48
+    assert ctypes.sizeof(_lib.StepSync) == 24
 
 
 def test_product_does_not_import_oracle():
@@ -138,8 +139,8 @@ def test_absent_column_and_gpt2_small_tile_count():
 def test_kernel_entry_points_validate_arguments_without_a_gpu():
     lib = _lib.load()
     grp = (_lib.AdamGroup * 1)(_lib.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.0, 0, 1, 1))
-    assert lib.b200_fused_adam(None, 1, _lib.F16, _lib.F32, _lib.F16, grp, 1, 1.0, None, None, None) == -1   # step 0
-    assert lib.b200_fused_adam(None, 1, _lib.F16, _lib.F32, _lib.F16, grp, 9, 1.0, None, None, None) == -1   # groups
+    assert lib.b200_fused_adam(None, 1, _lib.F16, _lib.F32, _lib.F16, grp, 1, 1.0, None, None, None, None) == -1   # step 0
+    assert lib.b200_fused_adam(None, 1, _lib.F16, _lib.F32, _lib.F16, grp, 9, 1.0, None, None, None, None) == -1   # groups
     assert lib.b200_multi_tensor_scale(None, 1, 7, _lib.F32, 1.0, None, None, None) == -3
     assert lib.b200_bucket_epilogue(None, -1, _lib.F16, 1.0, None, None) == -1
     assert lib.b200_set_launch_config(0, 100, 2) == -1

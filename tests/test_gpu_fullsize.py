@@ -90,7 +90,7 @@ def test_sgd_without_momentum_is_linear_in_the_gradient():
     c = torch.zeros(n, dtype=torch.float16, device="cuda")
     table = TensorTable([list(torch.split(g, sizes)), list(torch.split(w, sizes)), [None] * len(sizes),
                          list(torch.split(c, sizes))])
-    ops.fused_sgd(table, torch.float16, torch.float32, torch.float16, [ops.SgdGroup(0.25, 0.0, 0.0, 0.0, 0, 0, 0, 0)],
+    ops.fused_sgd(table, torch.float16, torch.float32, torch.float16, [ops.SgdGroup(0.25, 0.0, 0.0, 0.0, 1, 0, 0)],
                   inv_scale=0.5)
     torch.cuda.synchronize()
     assert torch.equal(w, w0 - 0.125 * g.float())

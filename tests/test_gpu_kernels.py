@@ -154,7 +154,7 @@ def test_fused_sgd_matches_oracle_bit_exact(gdt, sdt, cdt, variant):
         cols = [dg, dp, db if has_mom else [None] * len(sizes)] + ([dc] if dc else [])
         table = TensorTable(cols)
         grp = [ops.SgdGroup(kw["lr"], kw.get("momentum", 0.0), kw.get("dampening", 0.0), kw.get("weight_decay", 0.0),
-                            int(kw.get("nesterov", False)), int(step == 0), int(kw.get("wd_after_momentum", False)), 0)]
+                            step + 1, int(kw.get("nesterov", False)), int(kw.get("wd_after_momentum", False)))]
         ops.fused_sgd(table, gdt, sdt, cdt, grp, inv_scale=inv)
         for i in range(len(sizes)):
             oracle.sgd(hg[i], hp[i], hb[i] if has_mom else None, hc[i] if hc else None, first_run=(step == 0),
