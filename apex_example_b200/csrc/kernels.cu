@@ -50,9 +50,21 @@ static int sm_count() {
     return cached[dev];
 }
 
-static unsigned grid_for(int64_t n_tiles, int default_ctas_per_sm) {
+// Persistent grids must not exceed what is resident at once (a second wave would run at a
+// fraction of the occupancy): CTAs/SM comes from the occupancy calculator, per kernel and device.
+template <class Kernel>
+static int resident_ctas_per_sm(Kernel kernel, int threads) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, 0) != cudaSuccess || n < 1) {
+        cudaGetLastError();
+        n = 1;
+    }
+    return n;
+}
+
+static unsigned grid_for(int64_t n_tiles, int resident_per_sm) {
     int per_sm = g_ctas_per_sm.load();
-    if (per_sm <= 0) per_sm = default_ctas_per_sm;
+    if (per_sm <= 0 || per_sm > resident_per_sm) per_sm = resident_per_sm;
     int64_t g = static_cast<int64_t>(sm_count()) * per_sm;
     if (g > n_tiles) g = n_tiles;
     if (g < 1) g = 1;
@@ -75,27 +87,37 @@ tile_kernel(const void* __restrict__ table, const __grid_constant__ typename Op:
     int win = 0;
     if (Op::prologue(prm, win)) return;
     bool bad = false;
-    walk_tiles<Op, kThreads, kUnroll>(table, prm, win, bad);
+    walk_tiles<Op, kThreads, kUnroll * Op::kUnrollMul>(table, prm, win, bad);
     Op::finish(prm, bad);
+}
+
+template <class Op, int kThreads, int kUnroll>
+static int launch_one(const char* name, const void* dev_table, int64_t n_tiles, const typename Op::Params& prm,
+                      cudaStream_t st) {
+    auto kernel = tile_kernel<Op, kThreads, kUnroll>;
+    static int occ[64];                       // per device; one static per instantiation
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (occ[dev] == 0) occ[dev] = resident_ctas_per_sm(kernel, kThreads);
+    const unsigned grid = grid_for(n_tiles, occ[dev]);
+    kernel<<<grid, kThreads, 0, st>>>(dev_table, prm);
+    return after_launch(name);
 }
 
 template <class Op>
 static int launch_tiles(const char* name, const void* dev_table, int64_t n_tiles,
-                        const typename Op::Params& prm, int default_ctas_per_sm, void* stream) {
+                        const typename Op::Params& prm, void* stream) {
     if (n_tiles <= 0) return 0;
     if (dev_table == nullptr) return set_error(B200_EINVAL, "%s: dev_table is NULL", name);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int threads = g_threads.load(), unroll = g_unroll.load();
-    // a CTA moves threads*8*unroll elements per trip; keep ~the same CTA residency per SM
-    const unsigned grid = grid_for(n_tiles, default_ctas_per_sm * (threads == 512 ? 1 : 2));
     if (threads == 512) {
-        if (unroll == 1) tile_kernel<Op, 512, 1><<<grid, 512, 0, st>>>(dev_table, prm);
-        else tile_kernel<Op, 512, 2><<<grid, 512, 0, st>>>(dev_table, prm);
-    } else {
-        if (unroll == 1) tile_kernel<Op, 256, 1><<<grid, 256, 0, st>>>(dev_table, prm);
-        else tile_kernel<Op, 256, 2><<<grid, 256, 0, st>>>(dev_table, prm);
+        if (unroll == 1) return launch_one<Op, 512, 1>(name, dev_table, n_tiles, prm, st);
+        return launch_one<Op, 512, 2>(name, dev_table, n_tiles, prm, st);
     }
-    return after_launch(name);
+    if (unroll == 1) return launch_one<Op, 256, 1>(name, dev_table, n_tiles, prm, st);
+    return launch_one<Op, 256, 2>(name, dev_table, n_tiles, prm, st);
 }
 
 // ============================================================================================
@@ -110,6 +132,7 @@ struct ScaleParams {
 template <int I, int O>
 struct ScaleOp {
     using Params = ScaleParams;
+    static constexpr int kUnrollMul = 2;     // 1-2 light columns: keep more groups in flight
     struct Ctx { float s; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
@@ -154,6 +177,7 @@ struct AxpbyParams {
 template <int X, int Y, int O>
 struct AxpbyOp {
     using Params = AxpbyParams;
+    static constexpr int kUnrollMul = 1;
     struct Ctx { float a, b; int32_t chk; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
@@ -203,6 +227,7 @@ struct CheckParams {
 template <int I>
 struct CheckOp {
     using Params = CheckParams;
+    static constexpr int kUnrollMul = 4;     // read-only, one column: 4-8 loads in flight per thread
     struct Ctx { int32_t col; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) { return Ctx{p.col}; }
@@ -262,6 +287,7 @@ __device__ __forceinline__ void adam_elem(float g_in, float& p, float& m, float&
 template <int G, int S, int C>      // grad, state (p/m/v) and copy element types; C may be B200_NONE
 struct AdamOp {
     using Params = AdamParams;
+    static constexpr int kUnrollMul = 1;
     struct Ctx { AdamConsts k; float s; };
     static constexpr int kCopyCol = 4;
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
@@ -353,6 +379,7 @@ __device__ __forceinline__ void sgd_elem(float g_in, float& p, float& mom, const
 template <int G, int S, int C>
 struct SgdOp {
     using Params = SgdParams;
+    static constexpr int kUnrollMul = 1;
     struct Ctx { SgdConsts k; float s; };
     static constexpr int kCopyCol = 3;
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
@@ -547,9 +574,8 @@ static bool valid_dt(int dt) { return dt == B200_F32 || dt == B200_F16 || dt == 
 template <template <int, int, int> class OpT, class Params>
 static int dispatch_step(const char* name, int g, int s, int c, const void* tbl, int64_t n_tiles,
                          const Params& prm, void* stream) {
-    constexpr int kCtas = 2;
 #define B200_TRY(G_, S_, C_) \
-    if (g == G_ && s == S_ && c == C_) return launch_tiles<OpT<G_, S_, C_>>(name, tbl, n_tiles, prm, kCtas, stream);
+    if (g == G_ && s == S_ && c == C_) return launch_tiles<OpT<G_, S_, C_>>(name, tbl, n_tiles, prm, stream);
     B200_TRY(B200_F16, B200_F32, B200_F16)
     B200_TRY(B200_BF16, B200_F32, B200_BF16)
     B200_TRY(B200_F32, B200_F32, B200_NONE)
@@ -614,7 +640,7 @@ int32_t b200_multi_tensor_scale(const void* dev_table, int64_t n_tiles, int32_t 
     ScaleParams prm{scale, dev_scale, dev_flag};
     B200_DISPATCH_DT(in_dtype, I,
         B200_DISPATCH_DT(out_dtype, O,
-            return launch_tiles<ScaleOp<I, O>>("multi_tensor_scale", dev_table, n_tiles, prm, 4, stream)))
+            return launch_tiles<ScaleOp<I, O>>("multi_tensor_scale", dev_table, n_tiles, prm, stream)))
     return 0;
 }
 
@@ -627,7 +653,7 @@ int32_t b200_multi_tensor_axpby(const void* dev_table, int64_t n_tiles, int32_t 
     AxpbyParams prm{a, b, arg_to_check, dev_flag};
     B200_DISPATCH_DT(x_dtype, X,
         B200_DISPATCH_DT(out_dtype, O,
-            return launch_tiles<AxpbyOp<X, O, O>>("multi_tensor_axpby", dev_table, n_tiles, prm, 4, stream)))
+            return launch_tiles<AxpbyOp<X, O, O>>("multi_tensor_axpby", dev_table, n_tiles, prm, stream)))
     return 0;
 }
 
@@ -637,7 +663,7 @@ int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles, int32_t 
     if (col < 0 || col >= B200_MAX_DEPTH) return set_error(B200_EINVAL, "multi_tensor_check: bad column");
     if (!dev_flag) return set_error(B200_EINVAL, "multi_tensor_check: dev_flag is NULL");
     CheckParams prm{col, dev_flag};
-    B200_DISPATCH_DT(dtype, I, return launch_tiles<CheckOp<I>>("multi_tensor_check", dev_table, n_tiles, prm, 4, stream))
+    B200_DISPATCH_DT(dtype, I, return launch_tiles<CheckOp<I>>("multi_tensor_check", dev_table, n_tiles, prm, stream))
     return 0;
 }
 
@@ -719,14 +745,17 @@ int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype, flo
     constexpr int kThreads = 256;
     const int read_only = factor == 1.0f;
     const int64_t groups = numel / kVec + 1;
-    int64_t blocks = (groups + kThreads * 4 - 1) / (kThreads * 4);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks < 1) blocks = 1;
+    const int64_t want = (groups + kThreads * 4 - 1) / (kThreads * 4);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    B200_DISPATCH_DT(dtype, DT,
-        (bucket_epilogue_kernel<DT, kThreads><<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(
-            dev_bucket, numel, factor, read_only, dev_flag)))
+    B200_DISPATCH_DT(dtype, DT, {
+        auto kernel = bucket_epilogue_kernel<DT, kThreads>;
+        static int occ = 0;
+        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
+        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;      // one resident wave, grid-stride inside
+        if (blocks > want) blocks = want;
+        if (blocks < 1) blocks = 1;
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(dev_bucket, numel, factor, read_only, dev_flag);
+    })
     return after_launch("bucket_epilogue");
 }
 

@@ -246,7 +246,11 @@ def main():
                 dist.all_reduce(b)
                 ops.bucket_epilogue(b, 1.0 / world, acc_ref)
         else:
+            if ev is not None:
+                ev[2].record()
             ops.multi_tensor_check(table, 0, torch.float16, acc_ref)
+            if ev is not None:
+                ev[3].record()
         ops.scaler_update(state, True, 2000, 2.0, 0.0, 2.0 ** 24)
         if ev is not None:
             ev[0].record()
@@ -269,7 +273,7 @@ def main():
     if rank == 0:
         sampler.start()
     l0 = ops.launch_count()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    evs = [tuple(torch.cuda.Event(enable_timing=True) for _ in range(4)) for _ in range(args.steps)]
     t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_begin.record()
@@ -280,7 +284,8 @@ def main():
     launches = ops.launch_count() - l0
     clocks = sampler.stop() if rank == 0 else None
     total_ms = t_begin.elapsed_time(t_end)
-    adam_ms = [a.elapsed_time(b) for a, b in evs]
+    adam_ms = [e[0].elapsed_time(e[1]) for e in evs]
+    check_ms = [e[2].elapsed_time(e[3]) for e in evs] if world == 1 else None
     if world > 1:
         t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -298,6 +303,10 @@ def main():
             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
             "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
+    if check_ms:
+        cm = sum(check_ms) / len(check_ms)
+        roof["other_kernels"] = {"multi_tensor_check": {"ms_avg": cm, "achieved_gbs": 2 * n / (cm * 1e-3) / 1e9,
+                                                        "algorithmic_bytes_per_launch": 2 * n}}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
