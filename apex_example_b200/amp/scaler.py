@@ -36,6 +36,8 @@ class LossScaler:
         self._state = None          # int32[8] device tensor == b200_scaler_state
         self._mirror = None         # pinned host copy written by the update kernel
         self._seen_seq = 0
+        self._seen_skips = 0
+        self._quiet = False
         self._loss_id = 0
         self._tables = {}
 
@@ -121,38 +123,35 @@ class LossScaler:
         ops.scaler_update(self._state, self.dynamic, self._scale_seq_len, self._scale_factor,
                           float(self._min_loss_scale or 0.0), float(self._max_loss_scale), self._mirror)
         if need_host_decision and self.dynamic:
-            self._refresh(sync=True)
+            self._refresh(sync=True, quiet=True)        # the patched skip_step prints the message (as apex)
             return bool(self._mirror[ops.IDX_FOUND_INF])
         if not self.dynamic:
             return False
         return None
 
-    def _refresh(self, sync: bool):
+    def _refresh(self, sync: bool, quiet: bool = False):
+        """Fold what the device has mirrored so far into the host copy; prints apex's overflow line
+        once per skip the host had not seen yet."""
         if self._state is None:
             return
         if sync:
             torch.cuda.current_stream(self._state.device).synchronize()
         m = self._mirror
         seq = int(m[ops.IDX_SEQ])
-        if seq != self._seen_seq:
-            self._seen_seq = seq
-            self._loss_scale = float(m.view(torch.float32)[ops.IDX_LOSS_SCALE])
-            self._unskipped = int(m[ops.IDX_UNSKIPPED])
+        if seq == self._seen_seq:
+            return
+        self._seen_seq = seq
+        self._loss_scale = float(m.view(torch.float32)[ops.IDX_LOSS_SCALE])
+        self._unskipped = int(m[ops.IDX_UNSKIPPED])
+        skipped = int(m[ops.IDX_SKIPPED_TOTAL])
+        for _ in range(0 if quiet else skipped - self._seen_skips):
+            maybe_print("Gradient overflow.  Skipping step, loss scaler {} reducing loss scale to {}".format(
+                self._loss_id, self._loss_scale))
+        self._seen_skips = skipped
 
     def poll_overflow_message(self):
-        """Print apex's overflow line for an update the host has not reported yet (no sync: looks at
-        whatever the device has mirrored so far)."""
-        if self._mirror is None:
-            return
-        m = self._mirror
-        seq = int(m[ops.IDX_SEQ])
-        if seq != self._seen_seq:
-            self._seen_seq = seq
-            self._loss_scale = float(m.view(torch.float32)[ops.IDX_LOSS_SCALE])
-            self._unskipped = int(m[ops.IDX_UNSKIPPED])
-            if int(m[ops.IDX_FOUND_INF]):
-                maybe_print("Gradient overflow.  Skipping step, loss scaler {} reducing loss scale to {}".format(
-                    self._loss_id, self._loss_scale))
+        """No-sync variant used at scale_loss entry: report whatever has been mirrored by now."""
+        self._refresh(sync=False)
 
     # ---- checkpoint surface (amp.state_dict) -----------------------------------------------------
     def state_dict(self):

@@ -237,21 +237,52 @@ __device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
 //   template <int U> static void vec(row, ctx, idx[U], active[U], bad&)   // U groups in flight
 //   static void scalar(row, ctx, idx, bad&)
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// The descriptor chain (tile entry -> row -> data) is three dependent memory latencies.  To keep
+// it off the critical path, the row of the NEXT tile is fetched with cp.async into a two-slot
+// shared-memory ring by four threads while the current tile streams, and the tile entry after
+// that is already sitting in a register; one __syncthreads per tile hands the slot over.
+struct RowSlot {
+    b200_table_row row;      // 64 B, filled by 4 x cp.async(16 B)
+};
+
 template <class Op, int kThreads, int kUnroll>
 __device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, int win, bool& bad) {
+    __shared__ __align__(16) RowSlot s_slot[2];
+    __shared__ uint32_t s_tile[2];
     const TableView tv = open_table(table);
-    for (uint32_t t = blockIdx.x; t < tv.n_tiles; t += gridDim.x) {
-        const uint2 tl_raw = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
-        const b200_table_tile tl{tl_raw.x, tl_raw.y};
-        const b200_table_row* rp = tv.rows + tl.tensor;
-        b200_table_row row;
-        {   // 64-byte row, four 128-bit read-only loads (uniform across the CTA, L1-resident)
-            const uint4* src = reinterpret_cast<const uint4*>(rp);
-            uint4* dst = reinterpret_cast<uint4*>(&row);
-#pragma unroll
-            for (int i = 0; i < 4; i++) dst[i] = __ldg(src + i);
+    const uint32_t G = gridDim.x;
+    uint32_t t = blockIdx.x;
+    if (t >= tv.n_tiles) return;
+    const bool loader = threadIdx.x < 4;
+    uint2 tl_next = make_uint2(0u, 0u);          // tile entry of iteration i+1 (loader threads only)
+    if (loader) {
+        const uint2 tl0 = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
+        cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
+                   reinterpret_cast<const char*>(tv.rows + tl0.x) + threadIdx.x * 16);
+        if (threadIdx.x == 0) s_tile[0] = tl0.y;
+        if (t + G < tv.n_tiles) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t + G));
+        cp_async_wait_all();
+    }
+    __syncthreads();
+    int slot = 0;
+    for (;;) {
+        const bool has_next = t + G < tv.n_tiles;
+        if (loader && has_next) {
+            cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
+                       reinterpret_cast<const char*>(tv.rows + tl_next.x) + threadIdx.x * 16);
+            if (threadIdx.x == 0) s_tile[slot ^ 1] = tl_next.y;
+            const uint32_t t2 = t + 2 * G;
+            if (t2 < tv.n_tiles && t2 > t) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t2));
         }
-        const int64_t start = static_cast<int64_t>(tl.tile) * tv.tile_elems;
+        const b200_table_row row = s_slot[slot].row;
+        const uint32_t tile_idx = s_tile[slot];
+        const int64_t start = static_cast<int64_t>(tile_idx) * tv.tile_elems;
         const int64_t left = row.numel - start;
         const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left)
                                                                    : static_cast<int>(tv.tile_elems);
@@ -274,6 +305,11 @@ __device__ __forceinline__ void walk_tiles(const void* table, const typename Op:
         } else {
             for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
         }
+        if (!has_next) break;
+        if (loader) cp_async_wait_all();
+        __syncthreads();
+        slot ^= 1;
+        t += G;
     }
 }
 

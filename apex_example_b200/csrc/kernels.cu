@@ -508,6 +508,8 @@ __global__ void scaler_init_kernel(b200_scaler_state* s, float init_scale) {
     s->seq = 0;
     s->had_overflow = 0;
     s->inv_loss_scale = s->inv_scale;
+    s->skipped_total = 0;
+    s->reserved[0] = s->reserved[1] = s->reserved[2] = 0;
 }
 
 __global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scale_window, float scale_factor,
@@ -535,6 +537,7 @@ __global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scal
     }
     st.overflow_acc = 0;
     st.seq += 1;
+    st.skipped_total += st.found_inf;
     st.inv_loss_scale = __fdiv_rn(1.0f, st.loss_scale);
     *s = st;
     if (mirror) {
@@ -547,6 +550,7 @@ __global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scal
         mv->overflow_acc = 0;
         mv->had_overflow = st.had_overflow;
         mv->inv_loss_scale = st.inv_loss_scale;
+        mv->skipped_total = st.skipped_total;
         __threadfence_system();
         mv->seq = st.seq;
     }

@@ -15,7 +15,7 @@ namespace {
 
 constexpr uint32_t kMagic = 0x42325442u;
 static_assert(sizeof(b200_table_header) == 64 && sizeof(b200_table_row) == 64 && sizeof(b200_table_tile) == 8 &&
-                  sizeof(b200_scaler_state) == 32,
+                  sizeof(b200_scaler_state) == 48,
               "table / scaler layouts are part of the ABI");
 
 inline int64_t tiles_of(int64_t numel, int32_t tile_elems) {

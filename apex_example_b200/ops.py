@@ -112,9 +112,9 @@ def bucket_epilogue(bucket: torch.Tensor, factor: float, dev_flag=None):
 
 
 # ---- loss-scaler state ------------------------------------------------------------------------
-SCALER_WORDS = 8            # sizeof(b200_scaler_state) / 4
+SCALER_WORDS = 12           # sizeof(b200_scaler_state) / 4
 (IDX_LOSS_SCALE, IDX_INV_SCALE, IDX_FOUND_INF, IDX_UNSKIPPED, IDX_OVERFLOW_ACC, IDX_SEQ, IDX_HAD_OVERFLOW,
- IDX_INV_LOSS_SCALE) = range(8)
+ IDX_INV_LOSS_SCALE, IDX_SKIPPED_TOTAL) = range(9)
 
 
 def scaler_init(state: torch.Tensor, init_scale: float):

@@ -25,13 +25,28 @@ def dtype_code(dt) -> int:
         raise RuntimeError(f"libapex_b200 only supports fp16, bf16 and fp32 tensors, got {dt}") from None
 
 
+def auto_tile_elems(columns) -> int:
+    """Tile size by measurement (profiles/r1_tuning.md): a tile should be exactly one trip of a
+    CTA — 256 threads x 8 elements x the kernel's groups in flight.  The 4-5 column optimizer
+    kernels keep 2 groups in flight (4096 elements, ~114 KB of traffic); the one-column overflow
+    check keeps 8 and wants at least 32 KB per tile, so it gets 32768 elements."""
+    width = 0
+    for col in columns:
+        t = next((x for x in col if x is not None), None)
+        if t is not None:
+            width += t.element_size()
+    return 32768 if width <= 4 else _lib.TILE_ELEMS
+
+
 def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequence[int] | None = None,
-                tile_elems: int = _lib.TILE_ELEMS, pin: bool = False):
+                tile_elems: int | None = None, pin: bool = False):
     """Build the host image for ``columns`` (column-major: columns[d][t]).
 
     Returns (uint8 host tensor, n_tiles).  Pure host code — works without a GPU.
     """
     lib = _lib.load()
+    if tile_elems is None:
+        tile_elems = auto_tile_elems(columns)
     depth = len(columns)
     n = len(columns[0]) if depth else 0
     if depth < 1 or depth > _lib.MAX_DEPTH:
@@ -77,7 +92,7 @@ class TensorTable:
 
     __slots__ = ("image", "dev", "n_tiles", "n_tensors", "total_elems", "signature", "keepalive")
 
-    def __init__(self, columns, groups=None, tile_elems: int = _lib.TILE_ELEMS, device=None, signature=None):
+    def __init__(self, columns, groups=None, tile_elems: int | None = None, device=None, signature=None):
         ref = next(c for c in columns if all(t is not None for t in c)) if columns and columns[0] else []
         if device is None:
             device = ref[0].device if len(ref) else torch.device("cuda")

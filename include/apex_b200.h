@@ -126,7 +126,9 @@ typedef struct b200_scaler_state {
     int32_t seq;                /* number of updates so far (lets the host see fresh mirrors) */
     int32_t had_overflow;       /* overflow_acc as seen by the last update (also set when static) */
     float   inv_loss_scale;     /* 1 / loss_scale: what an unscale BEFORE the next update multiplies by */
-} b200_scaler_state;            /* 32 bytes */
+    int32_t skipped_total;      /* updates so far that ended in a skip (lets a late host count them) */
+    int32_t reserved[3];
+} b200_scaler_state;            /* 48 bytes */
 
 /* Initialise *dev_state (loss_scale = init_scale, inv_scale = inv_loss_scale = 1/init_scale, rest 0). */
 int32_t b200_scaler_init(b200_scaler_state* dev_state, float init_scale, void* stream);

@@ -58,7 +58,8 @@ class _ScalerState(ctypes.Structure):
     _fields_ = [("loss_scale", ctypes.c_float), ("inv_scale", ctypes.c_float),
                 ("found_inf", ctypes.c_int32), ("unskipped", ctypes.c_int32),
                 ("overflow_acc", ctypes.c_int32), ("seq", ctypes.c_int32),
-                ("had_overflow", ctypes.c_int32), ("inv_loss_scale", ctypes.c_float)]
+                ("had_overflow", ctypes.c_int32), ("inv_loss_scale", ctypes.c_float),
+                ("skipped_total", ctypes.c_int32), ("reserved", ctypes.c_int32 * 3)]
 
 
 _lib = None
@@ -148,7 +149,7 @@ class LossScaler:
     def __post_init__(self):
         if self.dynamic:
             self.loss_scale = min(self.max_loss_scale, self.loss_scale)
-        self._s = _ScalerState(self.loss_scale, 1.0 / self.loss_scale, 0, self.unskipped, 0, 0, 0, 1.0 / self.loss_scale)
+        self._s = _ScalerState(self.loss_scale, 1.0 / self.loss_scale, 0, self.unskipped, 0, 0, 0, 1.0 / self.loss_scale, 0)
 
     def update_scale(self, overflow: bool) -> bool:
         """Returns should_skip."""

@@ -267,6 +267,8 @@ typedef struct {
     int32_t seq;
     int32_t had_overflow;
     float   inv_loss_scale;
+    int32_t skipped_total;
+    int32_t reserved[3];
 } oracle_scaler_state;
 
 /* apex LossScaler.update_scale; equal to torch._amp_update_scale_
@@ -296,6 +298,7 @@ void oracle_scaler_update(oracle_scaler_state* s, int dynamic, int scale_window,
     }
     s->overflow_acc = 0;
     s->seq += 1;
+    s->skipped_total += s->found_inf;
     s->inv_loss_scale = 1.0f / s->loss_scale;
 }
 

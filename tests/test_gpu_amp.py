@@ -1,0 +1,372 @@
+"""-m gpu tests of the drop-in API: apex.optimizers.FusedAdam/FusedSGD, apex.amp (O0-O3),
+amp_C / multi_tensor_applier, against the oracle (bit-exact where the inputs are identical) and
+against a plain-torch emulation of apex's O2 recipe (tolerance: the forward/backward is torch's
+own and identical on both sides; only the optimizer arithmetic differs, rtol 1e-6 / atol 1e-7)."""
+import copy
+import io
+import contextlib
+
+import pytest
+import torch
+
+import oracle
+from gpu_util import assert_lists_bit_equal
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _fresh_amp_state():
+    from apex_example_b200.amp._amp_state import _amp_state
+    _amp_state.reset()
+    yield
+    _amp_state.reset()
+
+
+def _mlp(seed=0, din=32, dh=64, dout=8):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(din, dh), torch.nn.ReLU(), torch.nn.Linear(dh, dh), torch.nn.ReLU(),
+                               torch.nn.Linear(dh, dout)).cuda()
+
+
+# ------------------------------------------------------------------------------------------------
+# fused optimizers without amp: Python-side grouping / step logic, bit-exact vs the oracle
+# ------------------------------------------------------------------------------------------------
+def test_fused_adam_param_groups_bit_exact_vs_oracle():
+    from apex.optimizers import FusedAdam
+    gen = torch.Generator().manual_seed(0)
+    sizes = [(33, 7), (129,), (64, 64), (5,), (4097,)]
+    host = [torch.randn(s, generator=gen) * 0.1 for s in sizes]
+    params = [torch.nn.Parameter(h.clone().cuda()) for h in host]
+    opt = FusedAdam([{"params": params[:2], "lr": 1e-2, "weight_decay": 0.1},
+                     {"params": params[2:4], "betas": (0.8, 0.95)},
+                     {"params": params[4:], "bias_correction": False, "eps": 1e-6}], lr=1e-3, weight_decay=0.0)
+    hyper = [dict(lr=1e-2, weight_decay=0.1), dict(lr=1e-2, weight_decay=0.1),
+             dict(lr=1e-3, beta1=0.8, beta2=0.95), dict(lr=1e-3, beta1=0.8, beta2=0.95),
+             dict(lr=1e-3, bias_correction=False, eps=1e-6)]
+    hp = [h.flatten().clone() for h in host]
+    hm = [torch.zeros_like(h) for h in hp]
+    hv = [torch.zeros_like(h) for h in hp]
+    for step in range(1, 5):
+        grads = [torch.randn(s, generator=gen) for s in sizes]
+        for p, g in zip(params, grads):
+            p.grad = g.cuda()
+        opt.step()
+        for i, g in enumerate(grads):
+            oracle.adam(g.flatten(), hp[i], hm[i], hv[i], None, step=step, adam_w_mode=True, **hyper[i])
+    torch.cuda.synchronize()
+    assert_lists_bit_equal([p.detach().flatten() for p in params], hp, "p")
+    assert_lists_bit_equal([opt.state[p]["exp_avg"].flatten() for p in params], hm, "exp_avg")
+    assert_lists_bit_equal([opt.state[p]["exp_avg_sq"].flatten() for p in params], hv, "exp_avg_sq")
+    assert [g["step"] for g in opt.param_groups] == [4, 4, 4]
+
+
+def test_fused_adam_matches_torch_adamw_cuda():
+    from apex.optimizers import FusedAdam
+    m1, m2 = _mlp(1), _mlp(1)
+    o1 = FusedAdam(m1.parameters(), lr=1e-3, weight_decay=0.01)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=1e-3, weight_decay=0.01, foreach=False)
+    x = torch.randn(64, 32, device="cuda")
+    for _ in range(5):
+        for m, o in ((m1, o1), (m2, o2)):
+            o.zero_grad()
+            m(x).pow(2).mean().backward()
+            o.step()
+    for a, b in zip(m1.parameters(), m2.parameters()):
+        torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-7)
+
+
+def test_fused_sgd_matches_torch_sgd_and_oracle():
+    from apex.optimizers import FusedSGD
+    gen = torch.Generator().manual_seed(3)
+    host = [torch.randn(n, generator=gen) * 0.1 for n in (1000, 17, 4096)]
+    params = [torch.nn.Parameter(h.clone().cuda()) for h in host]
+    tparams = [torch.nn.Parameter(h.clone().cuda()) for h in host]
+    opt = FusedSGD(params, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    topt = torch.optim.SGD(tparams, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True, foreach=False)
+    hp = [h.clone() for h in host]
+    hb = [torch.zeros_like(h) for h in host]
+    for step in range(4):
+        grads = [torch.randn(h.shape, generator=gen) for h in host]
+        for p, tp, g in zip(params, tparams, grads):
+            p.grad = g.cuda()
+            tp.grad = g.cuda()
+        opt.step()
+        topt.step()
+        for i, g in enumerate(grads):
+            oracle.sgd(g, hp[i], hb[i], None, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True, first_run=(step == 0))
+    torch.cuda.synchronize()
+    assert_lists_bit_equal([p.detach() for p in params], hp, "w")
+    assert_lists_bit_equal([opt.state[p]["momentum_buffer"] for p in params], hb, "momentum_buffer")
+    for a, b in zip(params, tparams):
+        torch.testing.assert_close(a, b, rtol=1e-6, atol=1e-7)
+
+
+def test_fused_optimizer_error_behaviour():
+    from apex.optimizers import FusedAdam, FusedSGD
+    p = torch.nn.Parameter(torch.zeros(4, device="cuda"))
+    with pytest.raises(RuntimeError, match="AMSGrad"):
+        FusedAdam([p], amsgrad=True)
+    opt = FusedAdam([p])
+    p.grad = torch.zeros(4, device="cuda")
+    with pytest.raises(RuntimeError, match="has been updated"):
+        opt.step(grads=[p.grad])
+    p64 = torch.nn.Parameter(torch.zeros(4, device="cuda", dtype=torch.float64))
+    p64.grad = torch.zeros(4, device="cuda", dtype=torch.float64)
+    with pytest.raises(RuntimeError, match="only support fp16 and fp32"):
+        FusedAdam([p64]).step()
+    cpu = torch.nn.Parameter(torch.zeros(4))
+    cpu.grad = torch.zeros(4)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        FusedSGD([cpu], lr=0.1).step()
+    with pytest.raises(ValueError):
+        FusedSGD([p], lr=0.1, nesterov=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# the step window: skips decided on the device, exact step numbers, no host sync in between
+# ------------------------------------------------------------------------------------------------
+def test_device_side_skips_keep_bias_correction_exact():
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    gen = torch.Generator().manual_seed(4)
+    sizes = [5000, 33, 4096]
+    p16 = [torch.nn.Parameter((torch.randn(n, generator=gen) * 0.1).cuda()) for n in sizes]
+
+    class Holder(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.ps = torch.nn.ParameterList(p16)
+    model = Holder()
+    opt = FusedAdam(model.parameters(), lr=1e-2, weight_decay=0.01)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    hp = [p.detach().float().cpu().clone() for p in model.parameters()]      # masters start as the fp16 values
+    hm = [torch.zeros_like(h) for h in hp]
+    hv = [torch.zeros_like(h) for h in hp]
+    hc = [h.half() for h in hp]
+    sc = oracle.LossScaler()
+    overflow_at = {0, 1, 2, 6, 7, 11}          # includes three in a row at the start (the usual warm-up pattern)
+    good = 0
+    dummy = torch.zeros((), device="cuda")
+    for it in range(14):
+        S = sc.loss_scale
+        grads = [(torch.randn(n, generator=gen) * 1e-3 * S).half() for n in sizes]
+        if it in overflow_at:
+            grads[it % 3][it] = float("inf") if it % 2 else float("nan")
+        for p, g in zip(model.parameters(), grads):
+            p.grad = g.cuda()
+        with amp.scale_loss(dummy, opt):
+            pass
+        opt.step()                              # never synchronises; the kernel picks the right step number
+        skip = sc.update_scale(any(oracle.check(g) for g in grads))
+        assert skip == (it in overflow_at)
+        if not skip:
+            good += 1
+            for i, g in enumerate(grads):
+                oracle.adam(g, hp[i], hm[i], hv[i], hc[i], lr=1e-2, weight_decay=0.01, step=good, inv_scale=sc.inv_scale)
+    torch.cuda.synchronize()
+    masters = list(amp.master_params(opt))
+    assert_lists_bit_equal([m.detach() for m in masters], hp, "master")
+    assert_lists_bit_equal([opt.state[m]["exp_avg"] for m in masters], hm, "exp_avg")
+    assert_lists_bit_equal([opt.state[m]["exp_avg_sq"] for m in masters], hv, "exp_avg_sq")
+    assert_lists_bit_equal([p.detach() for p in model.parameters()], hc, "model copy")
+    scaler = amp._amp_state.loss_scalers[0]
+    assert scaler.loss_scale() == sc.loss_scale and scaler._unskipped == sc.unskipped
+    assert opt.state_dict()["param_groups"][0]["step"] == good == 8
+
+
+# ------------------------------------------------------------------------------------------------
+# amp end to end vs a plain-torch emulation of apex's O2 recipe
+# ------------------------------------------------------------------------------------------------
+def _torch_o2_emulation(model32, xs, ys, lr, wd, overflow_steps, make_opt):
+    model16 = copy.deepcopy(model32).half()
+    masters = [p.detach().clone().float().requires_grad_(True) for p in model16.parameters()]
+    opt = make_opt(masters)
+    scale, unskipped, trace = 65536.0, 0, []
+    for it, (x, y) in enumerate(zip(xs, ys)):
+        if it in overflow_steps:
+            x = x * float("inf")
+        for p in model16.parameters():
+            p.grad = None
+        loss = torch.nn.functional.mse_loss(model16(x.half()).float(), y)
+        (loss.float() * scale).backward()
+        grads = [p.grad for p in model16.parameters()]
+        found = any(not torch.isfinite(g).all() for g in grads)
+        if found:
+            scale, unskipped = scale / 2, 0
+        else:
+            unskipped += 1
+            for m, g in zip(masters, grads):
+                m.grad = g.float() * (1.0 / (scale))
+            opt.step()
+            with torch.no_grad():
+                for p, m in zip(model16.parameters(), masters):
+                    p.copy_(m)
+            if unskipped == 2000:
+                scale, unskipped = min(scale * 2, 2.0 ** 24), 0
+        trace.append((found, scale))
+    return model16, masters, trace
+
+
+@pytest.mark.parametrize("which", ["fused_adam", "fused_sgd_lazy", "fused_sgd_materialized", "torch_sgd"])
+def test_amp_o2_training_matches_torch_emulation(which):
+    from apex import amp
+    from apex.optimizers import FusedAdam, FusedSGD
+    model = _mlp(7)
+    ref = copy.deepcopy(model)
+    torch.manual_seed(11)
+    xs = [torch.randn(32, 32, device="cuda") for _ in range(12)]
+    ys = [torch.randn(32, 8, device="cuda") for _ in range(12)]
+    overflow = {0, 1, 5}
+    lr, wd = 1e-2, 0.01
+    if which == "fused_adam":
+        opt = FusedAdam(model.parameters(), lr=lr, weight_decay=wd)
+        mk = lambda ps: torch.optim.AdamW(ps, lr=lr, weight_decay=wd, foreach=False)
+    elif which.startswith("fused_sgd"):
+        opt = FusedSGD(model.parameters(), lr=lr, momentum=0.9, weight_decay=wd,
+                       materialize_master_grads=which.endswith("materialized"))
+        mk = lambda ps: torch.optim.SGD(ps, lr=lr, momentum=0.9, weight_decay=wd, foreach=False)
+    else:   # the reference script's own choice: a stock torch optimizer under amp O2
+        opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=0.9, weight_decay=wd, foreach=False)
+        mk = lambda ps: torch.optim.SGD(ps, lr=lr, momentum=0.9, weight_decay=wd, foreach=False)
+    out = io.StringIO()
+    with contextlib.redirect_stdout(out):
+        model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=1)
+        trace = []
+        for it, (x, y) in enumerate(zip(xs, ys)):
+            if it in overflow:
+                x = x * float("inf")
+            loss = torch.nn.functional.mse_loss(model(x), y)          # forward patch casts x to fp16, output to fp32
+            opt.zero_grad()
+            with amp.scale_loss(loss, opt) as scaled:
+                scaled.backward()
+            opt.step()
+            trace.append(amp._amp_state.loss_scalers[0].loss_scale())
+        with amp.scale_loss(torch.zeros((), device="cuda"), opt, delay_unscale=True):
+            pass                                                       # flushes any pending overflow message
+    ref16, ref_masters, ref_trace = _torch_o2_emulation(ref, xs, ys, lr, wd, overflow, mk)
+    assert trace == [s for _, s in ref_trace]                           # scale decisions: exact
+    assert out.getvalue().count("Gradient overflow.  Skipping step, loss scaler 0 reducing loss scale to") == len(overflow)
+    for p, q in zip(model.parameters(), ref16.parameters()):
+        assert p.dtype == torch.float16
+        torch.testing.assert_close(p.float(), q.float(), rtol=0, atol=2e-3 * float(q.abs().max()))   # fp16 ulp
+    for m, q in zip(amp.master_params(opt), ref_masters):
+        assert m.dtype == torch.float32
+        torch.testing.assert_close(m, q, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("level", ["O0", "O1", "O3"])
+def test_other_opt_levels_run_and_keep_their_dtypes(level):
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    model = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.BatchNorm1d(32), torch.nn.ReLU(),
+                                torch.nn.Linear(32, 4)).cuda()
+    opt = FusedAdam(model.parameters(), lr=1e-3)
+    kwargs = dict(loss_scale="dynamic") if level == "O3" else {}
+    model, opt = amp.initialize(model, opt, opt_level=level, verbosity=0, **kwargs)
+    want = {"O0": torch.float32, "O1": torch.float32, "O3": torch.float16}[level]
+    assert all(p.dtype == want for p in model.parameters())
+    x = torch.randn(8, 16, device="cuda")
+    before = [p.detach().clone() for p in model.parameters()]
+    for _ in range(2):
+        out = model(x)
+        assert out.dtype == (torch.float16 if level == "O1" else torch.float32)
+        loss = out.float().pow(2).mean()
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+    torch.cuda.synchronize()
+    assert any(not torch.equal(a, p.detach()) for a, p in zip(before, model.parameters()))
+    assert list(amp.master_params(opt))[0].dtype == want
+
+
+def test_o2_keeps_batchnorm_fp32_and_state_dict_is_fp32():
+    from apex import amp
+    from apex.optimizers import FusedSGD
+    model = torch.nn.Sequential(torch.nn.Conv2d(1, 4, 3), torch.nn.BatchNorm2d(4), torch.nn.ReLU(), torch.nn.Flatten(),
+                                torch.nn.Linear(4 * 26 * 26, 10)).cuda()
+    opt = FusedSGD(model.parameters(), lr=0.1, momentum=0.9, materialize_master_grads=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    assert model[0].weight.dtype == torch.float16 and model[1].weight.dtype == torch.float32
+    assert all(v.dtype != torch.float16 for v in model.state_dict().values())
+    x = torch.randn(4, 1, 28, 28, device="cuda")
+    loss = model(x).pow(2).mean()
+    with amp.scale_loss(loss, opt) as scaled:
+        scaled.backward()
+    opt.step()
+    sd = amp.state_dict()
+    assert sd == {"loss_scaler0": {"loss_scale": 65536.0, "unskipped": 1}}
+    amp.load_state_dict({"loss_scaler0": {"loss_scale": 1024.0, "unskipped": 7}})
+    assert amp.state_dict()["loss_scaler0"] == {"loss_scale": 1024.0, "unskipped": 7}
+
+
+def test_master_params_materialises_unscaled_fp32_grads_for_clipping():
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    model = _mlp(9)
+    opt = FusedAdam(model.parameters(), lr=1e-3)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    x = torch.randn(16, 32, device="cuda")
+    loss = model(x).pow(2).mean()
+    with amp.scale_loss(loss, opt) as scaled:
+        scaled.backward()
+    model_grads = [p.grad.detach().clone() for p in model.parameters()]
+    masters = list(amp.master_params(opt))
+    for m, g in zip(masters, model_grads):
+        assert m.grad is not None and m.grad.dtype == torch.float32
+        assert torch.equal(m.grad, g.float() * (1.0 / 65536.0))
+    torch.nn.utils.clip_grad_norm_(masters, 0.1)
+    before = [m.detach().clone() for m in masters]
+    opt.step()
+    torch.cuda.synchronize()
+    assert all(not torch.equal(a, m.detach()) for a, m in zip(before, masters))
+
+
+def test_amp_api_misuse_raises():
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    model = _mlp(2)
+    opt = FusedAdam(model.parameters())
+    with pytest.raises(RuntimeError, match="has not been initialized"):
+        with amp.scale_loss(torch.zeros((), device="cuda"), opt):
+            pass
+    with pytest.raises(RuntimeError, match="Unexpected optimization level"):
+        amp.initialize(model, opt, opt_level="02")
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    with pytest.raises(RuntimeError, match="closure"):
+        opt.step(closure=lambda: None)
+    with pytest.raises(RuntimeError, match="only be passed through amp.initialize once"):
+        amp.initialize(_mlp(3), opt, opt_level="O2", verbosity=0)
+    m2, o2 = amp.initialize(_mlp(4), FusedAdam(_mlp(4).parameters()), enabled=False)
+    assert next(m2.parameters()).dtype == torch.float32
+
+
+def test_amp_c_compat_through_multi_tensor_applier():
+    import amp_C
+    from apex.multi_tensor_apply import multi_tensor_applier
+    gen = torch.Generator().manual_seed(5)
+    hs = [(torch.randn(n, generator=gen) * 50).half() for n in (100, 4097, 7)]
+    src = [h.cuda() for h in hs]
+    dst = [torch.empty(h.shape, device="cuda") for h in hs]
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    multi_tensor_applier(amp_C.multi_tensor_scale, flag, [src, dst], 1.0 / 128)
+    assert int(flag.item()) == 0
+    for d, h in zip(dst, hs):
+        assert torch.equal(d.cpu(), h.float() * (1.0 / 128))
+    src[1][-1] = float("nan")
+    multi_tensor_applier(amp_C.multi_tensor_scale, flag, [src, dst], 1.0)
+    assert int(flag.item()) == 1
+    # adam / sgd early-out on a raised noop flag, like apex's `if(*noop) return`
+    p = [torch.ones(64, device="cuda")]
+    g = [torch.ones(64, device="cuda")]
+    m, v = [torch.zeros(64, device="cuda")], [torch.zeros(64, device="cuda")]
+    multi_tensor_applier(amp_C.multi_tensor_adam, flag, [g, p, m, v], 1e-3, 0.9, 0.999, 1e-8, 1, 1, 1, 0.0)
+    multi_tensor_applier(amp_C.multi_tensor_sgd, flag, [g, p, m], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0)
+    assert torch.equal(p[0], torch.ones(64, device="cuda"))
+    flag.zero_()
+    multi_tensor_applier(amp_C.multi_tensor_sgd, flag, [g, p, m], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0)
+    assert torch.allclose(p[0], torch.full((64,), 0.9, device="cuda")) and torch.equal(m[0], g[0])
+    out = [torch.zeros(64, device="cuda")]
+    multi_tensor_applier(amp_C.multi_tensor_axpby, flag, [g, p, out], 2.0, 1.0, -1)
+    assert torch.allclose(out[0], torch.full((64,), 2.9, device="cuda"))

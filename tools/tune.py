@@ -31,6 +31,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="gpt2_small")
     ap.add_argument("--tiles", default="4096")
+    ap.add_argument("--threads", default="256,512")
+    ap.add_argument("--unrolls", default="1,2")
+    ap.add_argument("--ctas", default="0,1,2,3,4")
     args = ap.parse_args()
     sizes = {"gpt2_small": GPT2_SMALL, "gpt2_medium": GPT2_MEDIUM,
              "many_small": many_small(total=300_000_000)}[args.workload]
@@ -50,9 +53,9 @@ def main():
         t1 = TensorTable([g], tile_elems=tile)
         t2 = TensorTable([g, mg], tile_elems=tile)
         t4 = TensorTable([g, p, m, c], tile_elems=tile)
-        for threads in (256, 512):
-            for unroll in (1, 2):
-                for ctas in (0, 1, 2, 3, 4):
+        for threads in [int(x) for x in args.threads.split(',')]:
+            for unroll in [int(x) for x in args.unrolls.split(',')]:
+                for ctas in [int(x) for x in args.ctas.split(',')]:
                     ops.set_launch_config(ctas, threads, unroll)
                     step = [0]
 
