@@ -194,7 +194,8 @@ def test_overflow_flag_positions(where):
                  "nan": (1, 40000, float("nan"))}[where]
     di[t][e] = val
     hi[t][e] = val
-    table = TensorTable([di, [torch.empty(n, dtype=torch.float32, device="cuda") for n in sizes]])
+    outs = [torch.empty(n, dtype=torch.float32, device="cuda") for n in sizes]     # must outlive the launches
+    table = TensorTable([di, outs])
     for fn in ("check", "scale"):
         flag = _flag()
         if fn == "check":
