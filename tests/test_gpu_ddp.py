@@ -1,0 +1,153 @@
+"""-m gpu tests of apex.parallel.DistributedDataParallel over NCCL.  The single-rank cases run on
+one GPU; the 2-rank cases need `gpurun --gpus 2` and skip themselves otherwise."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from test_ddp_gloo import _free_port
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _init(rank, world, port):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+
+
+def _mlp(seed):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 256), torch.nn.ReLU(),
+                               torch.nn.Linear(256, 16))
+
+
+def _worker_train(rank, world, port, kwargs, out):
+    _init(rank, world, port)
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    from apex.parallel import DistributedDataParallel
+    model = _mlp(rank).cuda()                       # different per rank; DDP must broadcast rank 0's
+    opt = FusedAdam(model.parameters(), lr=1e-3, weight_decay=0.01)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    ddp = DistributedDataParallel(model, **kwargs)
+    gen = torch.Generator().manual_seed(50 + rank)
+    scales = []
+    for it in range(8):
+        x = torch.randn(32, 64, generator=gen).cuda()
+        if it in (0, 4) and rank == world - 1:
+            x = x * float("inf")                    # overflow on ONE rank only: every rank must skip
+        loss = ddp(x).float().pow(2).mean()
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        # post-allreduce gradients are bit-identical on every rank
+        for p in model.parameters():
+            g = p.grad.detach().float().clone()
+            lo, hi = g.clone(), g.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            same = (lo == hi) | (lo.isnan() & hi.isnan()) | (g.isnan())
+            assert bool(same.all()), "gradients differ across ranks after the bucket all-reduce"
+        opt.step()
+        scales.append(amp._amp_state.loss_scalers[0].loss_scale())
+    assert scales == [32768.0] * 4 + [16384.0] * 4, scales
+    for p in list(model.parameters()) + list(amp.master_params(opt)):
+        v = p.detach().float().clone()
+        lo, hi = v.clone(), v.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo, hi), "parameters diverged across ranks"
+    if rank == 0:
+        out.put((scales, len(ddp.buckets)))
+    dist.destroy_process_group()
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs (run under gpurun --gpus {n})")
+
+
+@pytest.mark.parametrize("kwargs", [dict(), dict(message_size=20000), dict(delay_allreduce=True),
+                                    dict(message_size=20000, num_allreduce_streams=2),
+                                    dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0)])
+def test_two_rank_training_identical_ranks_and_skips(kwargs):
+    _need(2)
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    mp.spawn(_worker_train, args=(2, _free_port(), kwargs, out), nprocs=2, join=True)
+    scales, n_buckets = out.get()
+    assert n_buckets >= (3 if kwargs.get("message_size") else 1)
+
+
+def _worker_mean(rank, world, port):
+    _init(rank, world, port)
+    from apex.parallel import DistributedDataParallel
+    model = _mlp(0).cuda().half()
+    ref = _mlp(0).cuda().half()
+    ddp = DistributedDataParallel(model, message_size=30000)
+    gen = torch.Generator().manual_seed(9 + rank)
+    x = torch.randn(16, 64, generator=gen).cuda().half()
+    ddp(x).float().pow(2).mean().backward()
+    ref(x).float().pow(2).mean().backward()
+    for p, q in zip(model.parameters(), ref.parameters()):
+        want = q.grad.clone()
+        dist.all_reduce(want)                       # fp16 SUM, then x 1/world in fp16: apex's order
+        want.mul_(1.0 / world)
+        assert torch.equal(p.grad, want)
+    dist.destroy_process_group()
+
+
+def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype():
+    _need(2)
+    mp.spawn(_worker_mean, args=(2, _free_port()), nprocs=2, join=True)
+
+
+def _worker_single(rank, world, port):
+    _init(rank, world, port)
+    from apex import amp
+    from apex.optimizers import FusedSGD
+    from apex.parallel import DistributedDataParallel
+    model = _mlp(3).cuda()
+    opt = FusedSGD(model.parameters(), lr=0.1, momentum=0.9, materialize_master_grads=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    with pytest.raises(RuntimeError, match="AFTER"):
+        amp.initialize(DistributedDataParallel(_mlp(4).cuda()), None, opt_level="O2", verbosity=0)
+    ddp = DistributedDataParallel(model)
+    x = torch.randn(8, 64, device="cuda")
+    before = [p.detach().clone() for p in model.parameters()]
+    for _ in range(3):
+        loss = ddp(x).float().pow(2).mean()
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+    torch.cuda.synchronize()
+    assert all(not torch.equal(a, p.detach()) for a, p in zip(before, model.parameters()))
+    dist.destroy_process_group()
+
+
+def test_single_rank_nccl_wrapper_is_a_pass_through():
+    mp.spawn(_worker_single, args=(1, _free_port()), nprocs=1, join=True)
+
+
+@pytest.mark.parametrize("optimizer", ["sgd", "fused_adam"])
+def test_reference_workload_example_runs(optimizer):
+    """The reference's flow (examples/convnet_ddp_spawn.py mirrors its call order) on 1 GPU, amp O2."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "convnet_ddp_spawn.py"), "--gpus", "1", "--steps",
+                        "100", "--optimizer", optimizer, "--port", str(_free_port())], capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Training complete in" in r.stdout and "identical across ranks: True" in r.stdout
+    losses = [float(l.rsplit("Loss:", 1)[1]) for l in r.stdout.splitlines() if "Loss:" in l]
+    assert len(losses) == 2 and all(l == l for l in losses)
+    if optimizer == "fused_adam":
+        assert losses[-1] < losses[0]
