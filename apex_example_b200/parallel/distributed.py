@@ -165,12 +165,32 @@ class DistributedDataParallel(Module):
                                                             if b.is_floating_point()]
         if tensors:
             flat_dist_call(tensors, dist.broadcast, (0,))
+            self._resync_amp_masters()
 
         self._build_buckets(params)
         self._sync_bucket_structure()
         if self.world_size > 1 or not self._on_cuda:
             for p in params:
                 p.register_post_accumulate_grad_hook(self._hook)
+
+    def _resync_amp_masters(self):
+        """amp.initialize runs BEFORE this wrapper (reference :121 then :122), so at O2 the fp32
+        masters were cloned from each rank's own initial weights.  apex leaves them as they are
+        (ranks must seed identically); here the masters of the broadcast parameters are re-derived
+        from rank 0's weights so the replicas cannot start apart."""
+        try:
+            from ..amp._amp_state import _amp_state
+        except Exception:
+            return
+        mine = set(id(p) for p in self.module.parameters())
+        with torch.no_grad():
+            for opt in getattr(_amp_state, "optimizers", []):
+                stash = getattr(opt, "_amp_stash", None)
+                if stash is None:
+                    continue
+                for master, model_p in stash.model_of.items():
+                    if id(model_p) in mine:
+                        master.copy_(model_p.float())
 
     # ---- layout --------------------------------------------------------------------------------------
     def _build_buckets(self, params):
