@@ -37,6 +37,7 @@ class StepSync(ctypes.Structure):            # b200_step_sync
                 ("read_only", c_int32)]
 
 STEP_WINDOW = 4
+NOALLOC_TABLE_BYTES = 256 * 1024
 
 
 class TableHeader(ctypes.Structure):         # b200_table_header
@@ -74,6 +75,8 @@ SIGNATURES = {
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_fused_sgd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
                                  c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
+    "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
+                                          c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),
     "b200_set_launch_config": (c_int32, [c_int32, c_int32, c_int32]),
     "b200_launch_count": (c_int64, []),

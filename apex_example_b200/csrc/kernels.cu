@@ -12,6 +12,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 #include "b200_common.cuh"
 
@@ -739,6 +740,70 @@ int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtyp
     prm.dev_found_inf = dev_found_inf;
     prm.sync = to_sync(sync);
     return dispatch_step<SgdOp>("fused_sgd", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// b200_fused_adam_noalloc: the Adam step for callers that cannot allocate (see the header).
+// The tensor-list table — the one piece of global memory this path needs beyond the caller's own
+// buffers — lives in a static device array instead of caller-allocated memory.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_table[B200_NOALLOC_TABLE_BYTES];
+
+// In host code `g_noalloc_table` is only a handle for the runtime, not an address the GPU can
+// use; the real device address is looked up once per device (with that device current).
+static void* g_noalloc_table_addr[64];
+static unsigned char g_noalloc_host_image[B200_NOALLOC_TABLE_BYTES];
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_table_address(void** out) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "fused_adam_noalloc: cudaGetDevice");
+    if (dev < 0 || dev >= 64) return set_error(B200_ENODEV, "fused_adam_noalloc: device index %d not supported", dev);
+    if (g_noalloc_table_addr[dev] == nullptr) {
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress(&ptr, g_noalloc_table);
+        if (e != cudaSuccess || ptr == nullptr) return cuda_fail(e, "fused_adam_noalloc: cudaGetSymbolAddress");
+        g_noalloc_table_addr[dev] = ptr;
+    }
+    *out = g_noalloc_table_addr[dev];
+    return 0;
+}
+
+int32_t b200_fused_adam_noalloc(int32_t n_tensors, const void* const* ptrs, const int64_t* numel, int32_t grad_dtype,
+                                int32_t state_dtype, int32_t copy_dtype, const b200_adam_group* group, float inv_scale,
+                                const float* dev_inv_scale, const int32_t* dev_found_inf, void* stream) {
+    if (n_tensors < 0 || (n_tensors > 0 && (!ptrs || !numel)) || !group)
+        return set_error(B200_EINVAL, "fused_adam_noalloc: bad argument");
+    if (!valid_dt(grad_dtype) || !valid_dt(state_dtype) || (copy_dtype != B200_NONE && !valid_dt(copy_dtype)))
+        return set_error(B200_EDTYPE, "fused_adam_noalloc: bad dtype");
+    if (n_tensors == 0) return 0;
+    const int64_t need = b200_table_bytes(n_tensors, numel, B200_TILE_ELEMS_DEFAULT);
+    if (need < 0) return static_cast<int32_t>(need);
+    if (need > B200_NOALLOC_TABLE_BYTES)
+        return set_error(B200_ESIZE,
+                         "fused_adam_noalloc: this tensor list needs a %lld-byte table but the built-in static table "
+                         "holds %d bytes; use b200_fused_adam with a caller-allocated table instead",
+                         static_cast<long long>(need), B200_NOALLOC_TABLE_BYTES);
+    const int depth = copy_dtype == B200_NONE ? 4 : 5;
+    const int g_sz = grad_dtype == B200_F32 ? 4 : 2, s_sz = state_dtype == B200_F32 ? 4 : 2;
+    const int32_t elem_size[5] = {g_sz, s_sz, s_sz, s_sz, copy_dtype == B200_F32 ? 4 : 2};
+
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    void* dev_table = nullptr;
+    int rc = noalloc_table_address(&dev_table);
+    if (rc != 0) return rc;
+    const int64_t n_tiles = b200_table_build(g_noalloc_host_image, B200_NOALLOC_TABLE_BYTES, n_tensors, depth, ptrs, elem_size,
+                                             numel, nullptr, B200_TILE_ELEMS_DEFAULT);
+    if (n_tiles < 0) return static_cast<int32_t>(n_tiles);
+    // Pageable source: the runtime has consumed the host image by the time this returns, so the
+    // static host buffer can be reused by the next call; the device copy is ordered on `stream`
+    // ahead of the kernel below.
+    cudaError_t e = cudaMemcpyAsync(dev_table, g_noalloc_host_image, static_cast<size_t>(need), cudaMemcpyHostToDevice,
+                                    static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "fused_adam_noalloc: table upload");
+    return b200_fused_adam(dev_table, n_tiles, grad_dtype, state_dtype, copy_dtype, group, 1, inv_scale, dev_inv_scale,
+                           dev_found_inf, nullptr, stream);
 }
 
 int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype, float factor, int32_t* dev_flag, void* stream) {

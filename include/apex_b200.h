@@ -244,6 +244,44 @@ int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles,
 int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype,
                              float factor, int32_t* dev_flag, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * b200_fused_adam_noalloc — the fused Adam step for callers that must not allocate.
+ * (No counterpart in the reference: apex always goes through the torch allocator.)
+ *
+ * Who this is for: code that runs where cudaMalloc / the torch caching allocator are off
+ * limits — a hook that fires while someone else's CUDA graph is being captured or replayed, a
+ * plugin that was handed a fixed memory budget by its host application, a C caller that brings
+ * its own p/m/v/grad buffers and has nowhere to put a tensor-list table.  b200_fused_adam needs
+ * such a table in device memory and leaves allocating it to the caller; this entry point keeps
+ * the table in a B200_NOALLOC_TABLE_BYTES static device array that is part of the library image
+ * instead (every GPU that loads the library carries those bytes until the process exits).
+ *
+ * Arguments are b200_table_build's description of the list (`ptrs` column-major over the Adam
+ * columns g, p, m, v [, copy]; depth 4 when copy_dtype is B200_NONE, else 5), one
+ * hyper-parameter group, and b200_fused_adam's scale / skip arguments.  The caller still owns
+ * every input and output buffer.  Same arithmetic, same results as b200_fused_adam.
+ *
+ * Limits and rules:
+ *   - the list must fit: b200_table_bytes(n_tensors, numel, 4096) <= B200_NOALLOC_TABLE_BYTES
+ *     (256 KiB = 64 B + 64 B per tensor + 8 B per 4096-element tile: e.g. the whole 148-tensor,
+ *     124M-parameter GPT-2-small list fits).  Larger lists are refused with B200_ESIZE and a
+ *     message that says so.
+ *   - it calls no cudaMalloc / cudaFree and nothing that allocates; the table image is assembled
+ *     in a static host buffer and sent with one cudaMemcpyAsync on `stream`.
+ *   - the first call on each device looks up the array's device address (a one-time set-up with
+ *     that device current).  Make that first call before starting any stream capture.
+ *   - all calls share the one array, and each call overwrites the previous table in full
+ *     (nothing in it needs to start out zero).  Two calls whose GPU work can overlap — different
+ *     streams, or different host threads without ordering between their streams — race on it:
+ *     order them yourself.  Host-side the call is serialised by a mutex.
+ * ------------------------------------------------------------------------------------------ */
+#define B200_NOALLOC_TABLE_BYTES (256 * 1024)
+int32_t b200_fused_adam_noalloc(int32_t n_tensors, const void* const* ptrs, const int64_t* numel,
+                                int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                                const b200_adam_group* group,
+                                float inv_scale, const float* dev_inv_scale,
+                                const int32_t* dev_found_inf, void* stream);
+
 /* Tuning knobs (process-wide; defaults chosen by measurement): CTAs per SM of
  * the persistent grids (0 = per-kernel default), threads per CTA (256 or 512) and how many
  * 8-element groups each thread keeps in flight (1 or 2). */
