@@ -763,7 +763,8 @@ static int noalloc_table_address(void** out) {
     if (g_noalloc_table_addr[dev] == nullptr) {
         void* ptr = nullptr;
         e = cudaGetSymbolAddress(&ptr, g_noalloc_table);
-        if (e != cudaSuccess || ptr == nullptr) return cuda_fail(e, "fused_adam_noalloc: cudaGetSymbolAddress");
+        if (e != cudaSuccess) return cuda_fail(e, "fused_adam_noalloc: cudaGetSymbolAddress");
+        if (ptr == nullptr) return set_error(B200_ENODEV, "fused_adam_noalloc: static table has no device address");
         g_noalloc_table_addr[dev] = ptr;
     }
     *out = g_noalloc_table_addr[dev];

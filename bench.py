@@ -184,8 +184,8 @@ def reference_arm(args, sizes, desc):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="gpt2_small", choices=["gpt2_small", "gpt2_medium"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
