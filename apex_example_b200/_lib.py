@@ -37,6 +37,13 @@ class StepSync(ctypes.Structure):            # b200_step_sync
                 ("read_only", c_int32)]
 
 STEP_WINDOW = 4
+MAX_PEERS = 8
+
+
+class PeerPull(ctypes.Structure):            # b200_peer_pull
+    _fields_ = [("local_base", c_void_p), ("bounds", c_int64 * (MAX_PEERS + 1)), ("delta", c_int64 * MAX_PEERS),
+                ("world", c_int32), ("elem_size", c_int32)]
+
 NOALLOC_TABLE_BYTES = 256 * 1024
 
 
@@ -75,6 +82,14 @@ SIGNATURES = {
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_fused_sgd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
                                  c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
+    "b200_peer_reduce_shard": (c_int32, [ctypes.POINTER(c_void_p), c_int32, c_void_p, c_int64, c_int64, c_int32, c_float,
+                                         c_void_p, c_void_p]),
+    "b200_fused_adam_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
+                                       c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync),
+                                       ctypes.POINTER(PeerPull), c_void_p]),
+    "b200_fused_sgd_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
+                                      c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync),
+                                      ctypes.POINTER(PeerPull), c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

@@ -217,6 +217,27 @@ __device__ __forceinline__ void step_epilogue(const StepSync& ss, bool skipped) 
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Peer pull (b200_peer_pull): where a tile's gradient lives when the mean was reduce-scattered.
+// ------------------------------------------------------------------------------------------
+struct PeerPull {
+    const char* local_base;
+    long long bounds[B200_MAX_PEERS + 1];
+    long long delta[B200_MAX_PEERS];
+    int world;
+    int elem_size;
+};
+
+// byte offset to add to a column-0 pointer for the tile that starts at `tile_ptr`
+__device__ __forceinline__ long long peer_delta(const PeerPull& pp, const void* tile_ptr) {
+    if (pp.world <= 1) return 0;
+    const long long flat = (reinterpret_cast<const char*>(tile_ptr) - pp.local_base) / pp.elem_size;
+    int owner = 0;
+#pragma unroll
+    for (int k = 1; k < B200_MAX_PEERS; k++) owner += (k < pp.world && flat >= pp.bounds[k]) ? 1 : 0;
+    return pp.delta[owner];
+}
+
 // Raise a 0/1 flag for the whole grid: one plain store per warp that saw something.  Every
 // writer stores the same value, so no atomic is needed.
 __device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
@@ -232,7 +253,7 @@ __device__ __forceinline__ void raise_flag(int32_t* flag, bool bad) {
 //
 // Op interface:
 //   using Params;                                      // kernel-argument payload
-//   struct Ctx;  static Ctx make_ctx(params, row, win) // per-tile constants (group lookup…);
+//   struct Ctx;  static Ctx make_ctx(params, row, win, start) // per-tile constants (group lookup…);
 //                                                      // win = step-window candidate (see b200_step_sync)
 //   template <int U> static void vec(row, ctx, idx[U], active[U], bad&)   // U groups in flight
 //   static void scalar(row, ctx, idx, bad&)
@@ -286,7 +307,7 @@ __device__ __forceinline__ void walk_tiles(const void* table, const typename Op:
         const int64_t left = row.numel - start;
         const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left)
                                                                    : static_cast<int>(tv.tile_elems);
-        const typename Op::Ctx ctx = Op::make_ctx(prm, row, win);
+        const typename Op::Ctx ctx = Op::make_ctx(prm, row, win, start);
         if (row.flags & 1u) {
             const int n8 = n & ~(kVec - 1);
             for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kUnroll) {

@@ -136,7 +136,7 @@ struct ScaleOp {
     static constexpr int kUnrollMul = 2;     // 1-2 light columns: keep more groups in flight
     struct Ctx { float s; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) {
         return Ctx{p.dev_scale ? __ldg(p.dev_scale) : p.scale};
     }
     template <int U>
@@ -181,7 +181,7 @@ struct AxpbyOp {
     static constexpr int kUnrollMul = 1;
     struct Ctx { float a, b; int32_t chk; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) {
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) {
         return Ctx{p.a, p.b, p.arg_to_check};
     }
     static __device__ __forceinline__ float one(float x, float y, const Ctx& c, bool& bad) {
@@ -231,7 +231,7 @@ struct CheckOp {
     static constexpr int kUnrollMul = 4;     // read-only, one column: 4-8 loads in flight per thread
     struct Ctx { int32_t col; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int) { return Ctx{p.col}; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) { return Ctx{p.col}; }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
                                                const bool (&act)[U], bool& bad) {
@@ -268,6 +268,7 @@ struct AdamParams {
     const float* dev_inv_scale;
     const int32_t* dev_found_inf;
     StepSync sync;
+    PeerPull pull;
 };
 
 // One element, torch.optim.Adam's operation order (see oracle_adam for the line references).
@@ -289,15 +290,18 @@ template <int G, int S, int C>      // grad, state (p/m/v) and copy element type
 struct AdamOp {
     using Params = AdamParams;
     static constexpr int kUnrollMul = 1;
-    struct Ctx { AdamConsts k; float s; };
+    struct Ctx { AdamConsts k; float s; const void* g; };     // g: the tile's gradient column (local or a peer's)
     static constexpr int kCopyCol = 4;
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
         const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
         if (skip) step_epilogue(p.sync, true);
         return skip;
     }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win) {
-        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win, int64_t start) {
+        using GT = typename Elem<G>::type;
+        const char* g0 = reinterpret_cast<const char*>(r.ptr[0]);
+        const long long d = peer_delta(p.pull, reinterpret_cast<const GT*>(g0) + start);
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale, g0 + d};
     }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
@@ -307,7 +311,7 @@ struct AdamOp {
 #pragma unroll
         for (int u = 0; u < U; u++)
             if (act[u]) {
-                load8<G, true>(r.ptr[0], idx[u], rg[u]);
+                load8<G, true>(c.g, idx[u], rg[u]);
                 load8<S, false>(r.ptr[1], idx[u], rp[u]);
                 load8<S, false>(r.ptr[2], idx[u], rm[u]);
                 load8<S, false>(r.ptr[3], idx[u], rv[u]);
@@ -336,7 +340,7 @@ struct AdamOp {
     }
     static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
         float p = load1<S>(r.ptr[1], i), m = load1<S>(r.ptr[2], i), v = load1<S>(r.ptr[3], i);
-        adam_elem(load1<G>(r.ptr[0], i), p, m, v, c.k, c.s);
+        adam_elem(load1<G>(c.g, i), p, m, v, c.k, c.s);
         store1<S>(r.ptr[1], i, p);
         store1<S>(r.ptr[2], i, m);
         store1<S>(r.ptr[3], i, v);
@@ -359,6 +363,7 @@ struct SgdParams {
     const float* dev_inv_scale;
     const int32_t* dev_found_inf;
     StepSync sync;
+    PeerPull pull;
 };
 
 // torch.optim.SGD's order plus apex FusedSGD's extras (see oracle_sgd for the line references).
@@ -381,15 +386,18 @@ template <int G, int S, int C>
 struct SgdOp {
     using Params = SgdParams;
     static constexpr int kUnrollMul = 1;
-    struct Ctx { SgdConsts k; float s; };
+    struct Ctx { SgdConsts k; float s; const void* g; };
     static constexpr int kCopyCol = 3;
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
         const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
         if (skip) step_epilogue(p.sync, true);
         return skip;
     }
-    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win) {
-        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale};
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win, int64_t start) {
+        using GT = typename Elem<G>::type;
+        const char* g0 = reinterpret_cast<const char*>(r.ptr[0]);
+        const long long d = peer_delta(p.pull, reinterpret_cast<const GT*>(g0) + start);
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale, g0 + d};
     }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
@@ -401,7 +409,7 @@ struct SgdOp {
 #pragma unroll
         for (int u = 0; u < U; u++)
             if (act[u]) {
-                load8<G, true>(r.ptr[0], idx[u], rg[u]);
+                load8<G, true>(c.g, idx[u], rg[u]);
                 load8<S, false>(r.ptr[1], idx[u], rp[u]);
                 if (read_mom) load8<S, false>(r.ptr[2], idx[u], rm[u]);
             }
@@ -433,7 +441,7 @@ struct SgdOp {
         const bool has_mom = c.k.flags & 2u;
         float p = load1<S>(r.ptr[1], i);
         float m = (has_mom && !(c.k.flags & 8u)) ? load1<S>(r.ptr[2], i) : 0.0f;
-        sgd_elem<S>(load1<G>(r.ptr[0], i), p, m, c.k, c.s);
+        sgd_elem<S>(load1<G>(c.g, i), p, m, c.k, c.s);
         store1<S>(r.ptr[1], i, p);
         if (has_mom) store1<S>(r.ptr[2], i, m);
         if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
@@ -493,6 +501,89 @@ bucket_epilogue_kernel(void* __restrict__ buf, int64_t n, float factor, int read
         const float r = __fmul_rn(Elem<DT>::to_float(body[tail0 + gtid]), factor);
         bad |= !is_finite(round_through<DT>(r));
         if (!read_only) body[tail0 + gtid] = Elem<DT>::from_float(r);
+    }
+    if (flag) raise_flag(flag, bad);
+}
+
+// ============================================================================================
+// reduce-scatter + mean + overflow check over peer memory (one shard per rank)
+// ============================================================================================
+struct PeerBufs {
+    const void* p[B200_MAX_PEERS];
+};
+
+// value of one reduced element: fp32 sum in rank order, one rounding to the gradient dtype, then
+// x factor with a second rounding (oracle_peer_reduce in oracle/amp_step_oracle.c)
+template <int DT>
+__device__ __forceinline__ float peer_mean(const float (&x)[B200_MAX_PEERS], int world, float factor) {
+    float acc = x[0];
+#pragma unroll
+    for (int r = 1; r < B200_MAX_PEERS; r++)
+        if (r < world) acc = __fadd_rn(acc, x[r]);
+    return __fmul_rn(round_through<DT>(acc), factor);
+}
+
+template <int DT, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __restrict__ reduced, int64_t begin,
+                   int64_t end, float factor, int32_t* flag) {
+    using T = typename Elem<DT>::type;
+    constexpr int kU = (DT == B200_F32) ? 1 : 2;
+    bool bad = false;
+    T* out = reinterpret_cast<T*>(reduced);
+    const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
+    // every buffer starts 32-byte aligned, so element offsets that are multiples of 8 are vector-safe
+    int64_t head = (kVec - (begin % kVec)) % kVec;
+    if (head > end - begin) head = end - begin;
+    if (gtid < head) {
+        float x[B200_MAX_PEERS];
+#pragma unroll
+        for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? load1<DT>(bufs.p[r], begin + gtid) : 0.0f;
+        const float v = peer_mean<DT>(x, world, factor);
+        bad |= !is_finite(round_through<DT>(v));
+        store1<DT>(out, begin + gtid, v);
+    }
+    const int64_t body = begin + head;
+    const int64_t n_groups = (end - body) / kVec;
+    for (int64_t g0 = gtid; g0 < n_groups; g0 += stride * kU) {
+        Raw8<DT> raw[kU][B200_MAX_PEERS];
+        bool act[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const int64_t g = g0 + u * stride;
+            act[u] = g < n_groups;
+#pragma unroll
+            for (int r = 0; r < B200_MAX_PEERS; r++)
+                if (act[u] && r < world) load8<DT, false>(bufs.p[r], body + g * kVec, raw[u][r]);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            if (!act[u]) continue;
+            float f[B200_MAX_PEERS][kVec];
+#pragma unroll
+            for (int r = 0; r < B200_MAX_PEERS; r++)
+                if (r < world) unpack8<DT>(raw[u][r], f[r]);
+            float res[kVec];
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                float x[B200_MAX_PEERS];
+#pragma unroll
+                for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? f[r][i] : 0.0f;
+                res[i] = peer_mean<DT>(x, world, factor);
+                bad |= !is_finite(round_through<DT>(res[i]));
+            }
+            store8<DT>(out, body + (g0 + u * stride) * kVec, res);
+        }
+    }
+    const int64_t tail0 = body + n_groups * kVec;
+    if (gtid < end - tail0) {
+        float x[B200_MAX_PEERS];
+#pragma unroll
+        for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? load1<DT>(bufs.p[r], tail0 + gtid) : 0.0f;
+        const float v = peer_mean<DT>(x, world, factor);
+        bad |= !is_finite(round_through<DT>(v));
+        store1<DT>(out, tail0 + gtid, v);
     }
     if (flag) raise_flag(flag, bad);
 }
@@ -678,13 +769,47 @@ static StepSync to_sync(const b200_step_sync* s) {
     return r;
 }
 
+static int to_pull(const b200_peer_pull* p, PeerPull& out, const char* name) {
+    memset(&out, 0, sizeof(out));
+    out.world = 1;
+    out.elem_size = 2;
+    if (!p) return 0;
+    if (p->world < 1 || p->world > B200_MAX_PEERS) return set_error(B200_EINVAL, "%s: world must be 1..%d", name, B200_MAX_PEERS);
+    if (p->elem_size != 2 && p->elem_size != 4) return set_error(B200_EINVAL, "%s: elem_size must be 2 or 4", name);
+    if (p->world > 1 && !p->local_base) return set_error(B200_EINVAL, "%s: local_base is NULL", name);
+    out.local_base = static_cast<const char*>(p->local_base);
+    out.world = p->world;
+    out.elem_size = p->elem_size;
+    for (int r = 0; r <= p->world; r++) out.bounds[r] = p->bounds[r];
+    for (int r = 0; r < p->world; r++) out.delta[r] = p->delta[r];
+    for (int r = 0; r < p->world; r++)
+        if (p->bounds[r] > p->bounds[r + 1]) return set_error(B200_EINVAL, "%s: shard bounds must be non-decreasing", name);
+    return 0;
+}
+
 int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                         const b200_adam_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
                         const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
+    return b200_fused_adam_peer(dev_table, n_tiles, grad_dtype, state_dtype, copy_dtype, groups, n_groups, inv_scale,
+                                dev_inv_scale, dev_found_inf, sync, nullptr, stream);
+}
+
+int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                       const b200_sgd_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
+                       const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
+    return b200_fused_sgd_peer(dev_table, n_tiles, grad_dtype, state_dtype, copy_dtype, groups, n_groups, inv_scale,
+                               dev_inv_scale, dev_found_inf, sync, nullptr, stream);
+}
+
+int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                             int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
+                             const float* dev_inv_scale, const int32_t* dev_found_inf, const b200_step_sync* sync,
+                             const b200_peer_pull* pull, void* stream) {
     if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
         return set_error(B200_EINVAL, "fused_adam: n_groups must be 1..%d", B200_MAX_GROUPS);
     AdamParams prm;
     memset(&prm, 0, sizeof(prm));
+    if (int rc = to_pull(pull, prm.pull, "fused_adam")) return rc;
     for (int i = 0; i < n_groups; i++) {
         const b200_adam_group& h = groups[i];
         if (h.step < 1) return set_error(B200_EINVAL, "fused_adam: step must be >= 1");
@@ -714,13 +839,15 @@ int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dty
     return dispatch_step<AdamOp>("fused_adam", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
 }
 
-int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
-                       const b200_sgd_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
-                       const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
+int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                            int32_t copy_dtype, const b200_sgd_group* groups, int32_t n_groups, float inv_scale,
+                            const float* dev_inv_scale, const int32_t* dev_found_inf, const b200_step_sync* sync,
+                            const b200_peer_pull* pull, void* stream) {
     if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
         return set_error(B200_EINVAL, "fused_sgd: n_groups must be 1..%d", B200_MAX_GROUPS);
     SgdParams prm;
     memset(&prm, 0, sizeof(prm));
+    if (int rc = to_pull(pull, prm.pull, "fused_sgd")) return rc;
     for (int i = 0; i < n_groups; i++) {
         const b200_sgd_group& h = groups[i];
         if (h.step < 1) return set_error(B200_EINVAL, "fused_sgd: step must be >= 1");
@@ -740,6 +867,37 @@ int32_t b200_fused_sgd(const void* dev_table, int64_t n_tiles, int32_t grad_dtyp
     prm.dev_found_inf = dev_found_inf;
     prm.sync = to_sync(sync);
     return dispatch_step<SgdOp>("fused_sgd", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// b200_peer_reduce_shard: reduce-scatter + mean + overflow check over NVLink peer memory.
+// ------------------------------------------------------------------------------------------------
+int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced, int64_t begin, int64_t end,
+                               int32_t dtype, float factor, int32_t* dev_flag, void* stream) {
+    if (world < 1 || world > B200_MAX_PEERS) return set_error(B200_EINVAL, "peer_reduce_shard: world must be 1..%d", B200_MAX_PEERS);
+    if (!peer_bufs || !reduced) return set_error(B200_EINVAL, "peer_reduce_shard: NULL buffer");
+    if (begin < 0 || end < begin) return set_error(B200_EINVAL, "peer_reduce_shard: bad shard [%lld, %lld)",
+                                                   static_cast<long long>(begin), static_cast<long long>(end));
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "peer_reduce_shard: bad dtype");
+    if (end == begin) return 0;
+    PeerBufs pb;
+    for (int r = 0; r < B200_MAX_PEERS; r++) pb.p[r] = r < world ? peer_bufs[r] : nullptr;
+    for (int r = 0; r < world; r++)
+        if (!pb.p[r]) return set_error(B200_EINVAL, "peer_reduce_shard: peer buffer %d is NULL", r);
+    constexpr int kThreads = 256;
+    const int64_t groups = (end - begin) / kVec + 1;
+    const int64_t want = (groups + kThreads * 2 - 1) / (kThreads * 2);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B200_DISPATCH_DT(dtype, DT, {
+        auto kernel = peer_reduce_kernel<DT, kThreads>;
+        static int occ = 0;
+        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
+        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;
+        if (blocks > want) blocks = want;
+        if (blocks < 1) blocks = 1;
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag);
+    })
+    return after_launch("peer_reduce_shard");
 }
 
 // ------------------------------------------------------------------------------------------------

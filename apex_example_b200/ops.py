@@ -54,23 +54,52 @@ def multi_tensor_check(table: TensorTable, col: int, dtype, dev_flag):
 
 
 def fused_adam(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup],
-               inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None):
+               inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None,
+               pull=None):
     _require_cuda(table)
     arr = (AdamGroup * len(groups))(*groups)
-    _lib.check(_lib.load().b200_fused_adam(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
-                                           dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
-                                           _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
-                                           _stream()), "fused_adam")
+    _lib.check(_lib.load().b200_fused_adam_peer(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                                dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                                _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
+                                                ctypes.byref(pull) if pull is not None else None, _stream()),
+               "fused_adam")
 
 
 def fused_sgd(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[SgdGroup],
-              inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None):
+              inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None, sync: StepSync | None = None,
+              pull=None):
     _require_cuda(table)
     arr = (SgdGroup * len(groups))(*groups)
-    _lib.check(_lib.load().b200_fused_sgd(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
-                                          dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
-                                          _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
-                                          _stream()), "fused_sgd")
+    _lib.check(_lib.load().b200_fused_sgd_peer(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                               dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                               _addr(dev_found_inf), ctypes.byref(sync) if sync is not None else None,
+                                               ctypes.byref(pull) if pull is not None else None, _stream()),
+               "fused_sgd")
+
+
+PeerPull = _lib.PeerPull
+
+
+def peer_reduce_shard(peer_ptrs, reduced: torch.Tensor, begin: int, end: int, factor: float, dev_flag=None):
+    """Reduce-scatter + mean + overflow check for this rank's shard: peer_ptrs[r] is rank r's flat
+    gradient buffer as addressable from this process (device address, int)."""
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+    _lib.check(_lib.load().b200_peer_reduce_shard(arr, len(peer_ptrs), reduced.data_ptr(), begin, end,
+                                                  dtype_code(reduced.dtype), factor, _addr(dev_flag), _stream()),
+               "peer_reduce_shard")
+
+
+def make_peer_pull(local_base_ptr: int, bounds, reduced_ptrs, elem_size: int) -> "PeerPull":
+    world = len(reduced_ptrs)
+    pp = PeerPull()
+    pp.local_base = local_base_ptr
+    for r in range(world + 1):
+        pp.bounds[r] = int(bounds[r])
+    for r in range(world):
+        pp.delta[r] = int(reduced_ptrs[r]) - int(local_base_ptr)
+    pp.world = world
+    pp.elem_size = elem_size
+    return pp
 
 
 class StepCounter:

@@ -111,3 +111,22 @@ class TensorTable:
 def signature_of(columns) -> tuple:
     """Cheap identity of a list of columns: the device addresses (sizes are fixed per parameter)."""
     return tuple(tuple(0 if t is None else t.data_ptr() for t in col) for col in columns)
+
+
+def tile_aligned_shards(offsets: Sequence[int], sizes: Sequence[int], total: int, world: int,
+                        tile_elems: int = _lib.TILE_ELEMS):
+    """Split a flat buffer (tensor t at element offset offsets[t], sizes[t] long) into `world`
+    contiguous shards of roughly equal work whose boundaries never cut a tile of the optimizer's
+    table — the precondition of b200_fused_*_peer.  Returns world+1 element offsets."""
+    starts = []
+    for off, n in zip(offsets, sizes):
+        starts.extend(range(off, off + n, tile_elems))
+    starts.sort()
+    bounds = [0]
+    for r in range(1, world):
+        k = round(r * len(starts) / world)
+        bounds.append(starts[k] if k < len(starts) else total)
+    bounds.append(total)
+    for a, b in zip(bounds, bounds[1:]):
+        assert a <= b
+    return bounds

@@ -245,6 +245,53 @@ int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype,
                              float factor, int32_t* dev_flag, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * S3' — gradient mean over NVLink peer memory, fused with its neighbours (no counterpart in
+ * apex, which calls ncclAllReduce on a flattened copy and then multiplies by 1/world).
+ * Every rank keeps its gradients in one flat buffer G_r that all peers can address (CUDA IPC;
+ * NVSwitch gives every pair full bandwidth).  The all-reduce is split where the data flow splits:
+ *
+ *   b200_peer_reduce_shard  (reduce-scatter + mean + overflow check, ONE kernel):
+ *       rank r sums its shard [begin,end) of all `world` buffers — fp32 accumulation in rank
+ *       order 0..world-1, one rounding to the gradient dtype, then x factor with a second
+ *       rounding (apex: SUM in the gradient dtype, then mul_(1/world)) — writes the result at
+ *       the same offsets of its own `reduced` buffer and raises *dev_flag on inf/NaN.
+ *   b200_fused_adam_peer / b200_fused_sgd_peer  (all-gather fused INTO the optimizer):
+ *       the step kernels read each tile's gradient straight from the `reduced` buffer of the rank
+ *       that owns it (local HBM for the own shard, NVLink loads for the others), so the
+ *       "gather" overlaps the HBM-bound update tile by tile and is never materialised.
+ *
+ * Between the two the caller needs a cross-rank barrier that also ORs the overflow flags (a
+ * 4-byte NCCL all-reduce(MAX) on the stream does both), and one more before the next reduce.
+ * Shard bounds must not split a tile of the optimizer's table (tables.tile_aligned_shards()).
+ * ------------------------------------------------------------------------------------------ */
+#define B200_MAX_PEERS 8
+typedef struct b200_peer_pull {
+    const void* local_base;                 /* this rank's flat buffer: column 0 of the table points into it */
+    int64_t     bounds[B200_MAX_PEERS + 1]; /* rank r owns elements [bounds[r], bounds[r+1]) */
+    int64_t     delta[B200_MAX_PEERS];      /* bytes from local_base to rank r's reduced buffer (this process's view) */
+    int32_t     world;
+    int32_t     elem_size;                  /* bytes per gradient element (2 or 4) */
+} b200_peer_pull;
+
+int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced,
+                               int64_t begin, int64_t end, int32_t dtype, float factor,
+                               int32_t* dev_flag, void* stream);
+
+int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles,
+                             int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                             const b200_adam_group* groups, int32_t n_groups,
+                             float inv_scale, const float* dev_inv_scale,
+                             const int32_t* dev_found_inf, const b200_step_sync* sync,
+                             const b200_peer_pull* pull, void* stream);
+
+int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
+                            int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                            const b200_sgd_group* groups, int32_t n_groups,
+                            float inv_scale, const float* dev_inv_scale,
+                            const int32_t* dev_found_inf, const b200_step_sync* sync,
+                            const b200_peer_pull* pull, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * b200_fused_adam_noalloc — the fused Adam step for callers that must not allocate.
  * (No counterpart in the reference: apex always goes through the torch allocator.)
  *

@@ -240,3 +240,11 @@ def torch_update_scale(scale: float, growth_tracker: int, found_inf: int, window
     t = torch.tensor(growth_tracker, dtype=torch.int32)
     torch._amp_update_scale_(s, t, torch.tensor(float(found_inf)), 2.0, 0.5, window)
     return float(s), int(t)
+
+
+def peer_reduce(bufs, out, begin: int, end: int, factor: float) -> int:
+    """Mean of one shard over per-rank flat buffers (oracle_peer_reduce)."""
+    flag = ctypes.c_int(0)
+    lib().oracle_peer_reduce(_ptr_array(bufs), ctypes.c_int(len(bufs)), _p(out), _dt(out), ctypes.c_int64(begin),
+                             ctypes.c_int64(end), ctypes.c_float(factor), ctypes.byref(flag))
+    return flag.value

@@ -316,6 +316,27 @@ void oracle_bucket_epilogue(void* x, int dt, int64_t n, float factor, int* flag)
     if (f && flag) *flag = 1;
 }
 
+/* ---- gradient mean across ranks, restated for the peer-memory path ---------------------------------
+ * apex allreduce_bucket: all_reduce(SUM) in the gradient dtype, then mul_(1/world) (SURVEY.md
+ * App. B.7).  NCCL does not specify its summation order, so the restatement fixes one: fp32
+ * accumulation over ranks 0..world-1, ONE rounding to the gradient dtype (the "sum in the
+ * gradient dtype" result, where fp16 can overflow to inf although the mean would not), then
+ * x factor with a second rounding.  Flag on a non-finite result. */
+void oracle_peer_reduce(const void* const* bufs, int world, void* out, int dt, int64_t begin, int64_t end,
+                        float factor, int* flag) {
+    int f = 0;
+    #pragma omp parallel for reduction(|:f) schedule(static)
+    for (int64_t i = begin; i < end; i++) {
+        float acc = load_as_float(bufs[0], dt, i);
+        for (int r = 1; r < world; r++) acc = acc + load_as_float(bufs[r], dt, i);
+        store_from_float(out, dt, i, acc);                       /* rounding 1 */
+        float v = load_as_float(out, dt, i) * factor;
+        store_from_float(out, dt, i, v);                         /* rounding 2 */
+        f |= !finite_f(load_as_float(out, dt, i));
+    }
+    if (f && flag) *flag = 1;
+}
+
 /* ---- whole-list step, used as the timed CPU baseline ------------------------------------------
  * One O2 step over a tensor list the way the path runs it: check every gradient, and unless
  * an overflow was found, unscale + Adam + model copy.  Returns the flag. */

@@ -1,0 +1,173 @@
+"""-m gpu tests of the peer-memory gradient mean (b200_peer_reduce_shard + b200_fused_*_peer).
+
+On one GPU the ranks are emulated as separate buffers on the same device (the kernels only see
+pointers), which covers the arithmetic, the shard/tile ownership logic and the overflow flag.
+The CUDA-IPC plumbing and real NVLink loads need `gpurun --gpus 2` (skipped otherwise)."""
+import os
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle
+from apex_example_b200 import ops
+from apex_example_b200.tables import TensorTable, tile_aligned_shards
+from gpu_util import assert_lists_bit_equal, bit_equal
+from test_ddp_gloo import _free_port
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _layout(sizes):
+    offs, off = [], 0
+    for n in sizes:
+        off += (-off) % 16                       # keep every tensor 32-byte aligned inside the flat buffer
+        offs.append(off)
+        off += n
+    return offs, off
+
+
+@pytest.mark.parametrize("dt", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+def test_peer_reduce_shard_emulated_ranks_match_oracle(dt, world):
+    gen = torch.Generator().manual_seed(world)
+    n = 100_003
+    host = [(torch.randn(n, generator=gen) * 3000).to(dt) for _ in range(world)]
+    dev = [h.cuda() for h in host]
+    bounds = [0] + sorted(int(x) for x in torch.randint(1, n - 1, (world - 1,), generator=gen)) + [n]
+    out = torch.zeros(n, dtype=dt, device="cuda")
+    want = torch.zeros(n, dtype=dt)
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    wflag = 0
+    for r in range(world):                       # each emulated rank reduces its own shard
+        ops.peer_reduce_shard([d.data_ptr() for d in dev], out, bounds[r], bounds[r + 1], 1.0 / world, flag)
+        wflag |= oracle.peer_reduce(host, want, bounds[r], bounds[r + 1], 1.0 / world)
+    torch.cuda.synchronize()
+    assert bit_equal(out, want)
+    assert int(flag.item()) == wflag
+    if dt == torch.float16 and world >= 2:       # the SUM overflows although the mean would not
+        assert wflag == 1 or float(want.float().abs().max()) < 65504
+    host[-1][bounds[-2]] = float("nan")
+    dev[-1][bounds[-2]] = float("nan")
+    flag.zero_()
+    ops.peer_reduce_shard([d.data_ptr() for d in dev], out, bounds[-2], bounds[-1], 1.0 / world, flag)
+    assert int(flag.item()) == 1
+
+
+def test_fp16_sum_overflow_is_flagged_like_apex_sum_then_scale():
+    a = torch.full((64,), 40000.0).half().cuda()
+    b = torch.full((64,), 40000.0).half().cuda()
+    out = torch.zeros(64, dtype=torch.float16, device="cuda")
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ops.peer_reduce_shard([a.data_ptr(), b.data_ptr()], out, 0, 64, 0.5, flag)
+    assert int(flag.item()) == 1 and bool(torch.isinf(out).all())     # SUM = 80000 > fp16 max, as with NCCL fp16 SUM
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_fused_adam_pulls_each_tile_from_its_owner_emulated(world):
+    gen = torch.Generator().manual_seed(10 + world)
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
+    offs, total = _layout(sizes)
+    bounds = tile_aligned_shards(offs, sizes, total, world)
+    S = 256.0
+    host_g = [(torch.randn(total, generator=gen) * 1e-2 * S).half() for _ in range(world)]
+    dev_g = [h.cuda() for h in host_g]
+    reduced = [torch.full((total,), float("nan"), dtype=torch.float16, device="cuda") for _ in range(world)]
+    want_red = torch.zeros(total, dtype=torch.float16)
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    for r in range(world):                       # rank r writes ONLY its shard of its own `reduced` buffer
+        ops.peer_reduce_shard([d.data_ptr() for d in dev_g], reduced[r], bounds[r], bounds[r + 1], 1.0 / world, flag)
+        oracle.peer_reduce(host_g, want_red, bounds[r], bounds[r + 1], 1.0 / world)
+    hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+    hm = [torch.zeros(n) for n in sizes]
+    hv = [torch.zeros(n) for n in sizes]
+    hc = [torch.zeros(n, dtype=torch.float16) for n in sizes]
+    for rank in range(world):                    # every emulated rank must end with the same state
+        dp, dm, dv, dc = ([t.clone().cuda() for t in lst] for lst in (hp, hm, hv, hc))
+        gviews = [dev_g[rank][o:o + n] for o, n in zip(offs, sizes)]         # table column 0: the LOCAL flat buffer
+        table = TensorTable([gviews, dp, dm, dv, dc])
+        pull = ops.make_peer_pull(dev_g[rank].data_ptr(), bounds, [t.data_ptr() for t in reduced], 2)
+        ops.fused_adam(table, torch.float16, torch.float32, torch.float16,
+                       [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, 1, 1, 1)], inv_scale=1.0 / S, pull=pull)
+        op, om, ov, oc = ([t.clone() for t in lst] for lst in (hp, hm, hv, hc))
+        for i, (o, n) in enumerate(zip(offs, sizes)):
+            oracle.adam(want_red[o:o + n].clone(), op[i], om[i], ov[i], oc[i], lr=1e-3, weight_decay=0.01, step=1,
+                        inv_scale=1.0 / S)
+        torch.cuda.synchronize()
+        assert_lists_bit_equal(dp, op, f"p(rank {rank})")
+        assert_lists_bit_equal(dm, om, f"m(rank {rank})")
+        assert_lists_bit_equal(dc, oc, f"copy(rank {rank})")
+
+
+def test_tile_aligned_shards_never_cut_a_tile():
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
+    offs, total = _layout(sizes)
+    for world in (1, 2, 3, 8):
+        b = tile_aligned_shards(offs, sizes, total, world)
+        assert b[0] == 0 and b[-1] == total and len(b) == world + 1
+        for o, n in zip(offs, sizes):
+            for s in range(o, o + n, 4096):
+                e = min(s + 4096, o + n)
+                assert not any(s < x < e for x in b), (world, s, e, b)
+
+
+# ---- real peers over CUDA IPC / NVLink ----------------------------------------------------------------
+def _worker_ipc(rank, world, port):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
+    offs, total = _layout(sizes)
+    bounds = tile_aligned_shards(offs, sizes, total, world)
+    bufs = PeerBuffers(total, torch.float16)
+    red = PeerGradientReducer(bufs, bounds)
+    S = 256.0
+    host_all = [(torch.randn(total, generator=torch.Generator().manual_seed(100 + r)) * 1e-2 * S).half() for r in range(world)]
+    want_red = torch.zeros(total, dtype=torch.float16)
+    oracle.peer_reduce(host_all, want_red, 0, total, 1.0 / world)
+    gen = torch.Generator().manual_seed(7)
+    hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+    hm, hv = [torch.zeros(n) for n in sizes], [torch.zeros(n) for n in sizes]
+    hc = [torch.zeros(n, dtype=torch.float16) for n in sizes]
+    dp, dm, dv, dc = ([t.clone().cuda() for t in lst] for lst in (hp, hm, hv, hc))
+    g_local = bufs.local["grads"]
+    table = TensorTable([[g_local[o:o + n] for o, n in zip(offs, sizes)], dp, dm, dv, dc])
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    ops.scaler_init(state, S)
+    for step in (1, 2, 3):
+        if step == 2:
+            host_all[world - 1][total - 1] = float("inf")          # overflow on the LAST rank only
+        else:
+            host_all[world - 1][total - 1] = 1.0
+        g_local.copy_(host_all[rank])
+        red.reduce(state[ops.IDX_OVERFLOW_ACC:])
+        ops.scaler_update(state, True, 2000, 2.0, 0.0, 2.0 ** 24)
+        ops.fused_adam(table, torch.float16, torch.float32, torch.float16,
+                       [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, 1 if step == 1 else 2, 1, 1)],
+                       dev_inv_scale=state.view(torch.float32)[ops.IDX_INV_SCALE:], dev_found_inf=state[ops.IDX_FOUND_INF:],
+                       pull=red.pull)
+        torch.cuda.synchronize()
+        found = int(state.cpu()[ops.IDX_FOUND_INF])
+        assert found == (1 if step == 2 else 0), f"rank {rank}: skip decision {found} at step {step}"
+        if step != 2:
+            oracle.peer_reduce(host_all, want_red, 0, total, 1.0 / world)
+            for i, (o, n) in enumerate(zip(offs, sizes)):
+                oracle.adam(want_red[o:o + n].clone(), hp[i], hm[i], hv[i], hc[i], lr=1e-3, weight_decay=0.01,
+                            step=1 if step == 1 else 2, inv_scale=1.0 / S)
+        assert_lists_bit_equal(dp, hp, f"p(rank {rank}, step {step})")
+        assert_lists_bit_equal(dc, hc, f"copy(rank {rank}, step {step})")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_ipc_reduce_and_fused_pull():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
+    mp.spawn(_worker_ipc, args=(2, _free_port()), nprocs=2, join=True)
