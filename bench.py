@@ -193,6 +193,9 @@ def main():
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
+                    help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
+                         "'nccl' = ncclAllReduce per bucket + epilogue kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     sizes, desc = workload_sizes(args.workload)
@@ -218,7 +221,21 @@ def main():
     n = sum(sizes)
     gen = torch.Generator(device=dev).manual_seed(0)
     # gradients live in flat buckets (what apex DDP's flatten produces; at N=1 just contiguous storage)
-    gflat = (torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half()
+    use_peer = world > 1 and args.collective == "peer"
+    reducer = None
+    if use_peer:
+        from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
+        from apex_example_b200.tables import tile_aligned_shards
+        offs, acc = [], 0
+        for s_ in sizes:
+            offs.append(acc)
+            acc += s_
+        pbufs = PeerBuffers(n, torch.float16)
+        reducer = PeerGradientReducer(pbufs, tile_aligned_shards(offs, sizes, n, world))
+        gflat = pbufs.local["grads"]
+        gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
+    else:
+        gflat = (torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half()
     grads = list(torch.split(gflat, sizes))
     copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
     p = [c.float() for c in copy]
@@ -240,12 +257,23 @@ def main():
 
     def step(ev=None):
         step_no[0] += 1
-        if world > 1:
+        if use_peer:
+            # barrier -> ONE kernel: reduce-scatter + mean + overflow check over NVLink -> barrier + flag OR
+            if ev is not None:
+                ev[2].record()
+            reducer.reduce(acc_ref)
+            if ev is not None:
+                ev[3].record()
+        elif world > 1:
             # in-place SUM then x 1/N: after the first step every rank holds the mean, which the
             # following steps reproduce exactly (N equal addends / N), so values stay finite
+            if ev is not None:
+                ev[2].record()
             for b in buckets:
                 dist.all_reduce(b)
                 ops.bucket_epilogue(b, 1.0 / world, acc_ref)
+            if ev is not None:
+                ev[3].record()
         else:
             if ev is not None:
                 ev[2].record()
@@ -258,7 +286,7 @@ def main():
         grp = [ops.AdamGroup(HYPER["lr"], HYPER["beta1"], HYPER["beta2"], HYPER["eps"], HYPER["weight_decay"],
                              step_no[0], 1, 1)]
         ops.fused_adam(table, torch.float16, torch.float32, torch.float16, grp, dev_inv_scale=inv_ref,
-                       dev_found_inf=found_ref)
+                       dev_found_inf=found_ref, pull=reducer.pull if use_peer else None)
         if ev is not None:
             ev[1].record()
 
@@ -286,7 +314,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     total_ms = t_begin.elapsed_time(t_end)
     adam_ms = [e[0].elapsed_time(e[1]) for e in evs]
-    check_ms = [e[2].elapsed_time(e[3]) for e in evs] if world == 1 else None
+    check_ms = [e[2].elapsed_time(e[3]) for e in evs]
     if world > 1:
         t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -304,10 +332,22 @@ def main():
             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
             "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
-    if check_ms:
-        cm = sum(check_ms) / len(check_ms)
+    cm = sum(check_ms) / len(check_ms)
+    if world == 1:
         roof["other_kernels"] = {"multi_tensor_check": {"ms_avg": cm, "achieved_gbs": 2 * n / (cm * 1e-3) / 1e9,
                                                         "algorithmic_bytes_per_launch": 2 * n}}
+    else:
+        # gradient mean: every rank receives (N-1)/N of the buffer over NVLink in the reduce phase and
+        # again while the optimizer pulls the reduced shards; bus bandwidth as NCCL defines it
+        nbytes = n * 2
+        roof["gradient_mean"] = {"path": "peer reduce-scatter kernel + 2 flag/barrier all-reduces" if use_peer
+                                 else "ncclAllReduce per 10M-element bucket + epilogue kernel",
+                                 "ms_avg": cm, "bytes": nbytes,
+                                 "busbw_gbs": nbytes / (cm * 1e-3) * 2 * (world - 1) / world / 1e9 if not use_peer
+                                 else nbytes / (cm * 1e-3) * (world - 1) / world / 1e9,
+                                 "busbw_note": "nccl: bytes/t*2(n-1)/n; peer: reduce phase only, bytes/t*(n-1)/n "
+                                               "(the gather half is inside the optimizer kernel)",
+                                 "nvlink_peak_gbs_per_dir": 900.0}
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
@@ -359,7 +399,9 @@ def main():
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
                        "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
-                       "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS},
+                       "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS,
+                       "collective": ("peer-memory reduce-scatter + pull-in-optimizer" if use_peer else "nccl all-reduce")
+                       if world > 1 else "none"},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         }
         line.update(extra)

@@ -159,8 +159,9 @@ def _worker_ipc(rank, world, port):
         if step != 2:
             oracle.peer_reduce(host_all, want_red, 0, total, 1.0 / world)
             for i, (o, n) in enumerate(zip(offs, sizes)):
+                # the overflow at step 2 halved the loss scale, so step 3 is unscaled by 1/(S/2)
                 oracle.adam(want_red[o:o + n].clone(), hp[i], hm[i], hv[i], hc[i], lr=1e-3, weight_decay=0.01,
-                            step=1 if step == 1 else 2, inv_scale=1.0 / S)
+                            step=1 if step == 1 else 2, inv_scale=(1.0 / S) if step == 1 else (2.0 / S))
         assert_lists_bit_equal(dp, hp, f"p(rank {rank}, step {step})")
         assert_lists_bit_equal(dc, hc, f"copy(rank {rank}, step {step})")
     dist.barrier()
