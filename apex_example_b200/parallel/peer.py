@@ -56,6 +56,24 @@ class PeerBuffers:
         self._bar = torch.zeros(1, dtype=torch.int32, device=self.device)
         dist.barrier(group=group)
 
+    def close(self):
+        """Drop the mappings of the peers' memory (call on every rank before the process group is
+        destroyed; the owners' buffers must outlive everybody's mappings, hence the barrier)."""
+        if self.peers is None:
+            return
+        torch.cuda.synchronize(self.device)
+        try:
+            dist.barrier(group=self.group)
+        except Exception:
+            pass
+        self.peers = None
+        self._keep.clear()
+        torch.cuda.synchronize(self.device)
+        try:
+            dist.barrier(group=self.group)
+        except Exception:
+            pass
+
     def ptrs(self, name):
         return [t.data_ptr() for t in self.peers[name]]
 

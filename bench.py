@@ -406,6 +406,9 @@ def main():
         }
         line.update(extra)
         print(json.dumps(line), flush=True)
+    if use_peer:
+        del reducer
+        pbufs.close()
     if world > 1:
         dist.destroy_process_group()
 

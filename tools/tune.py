@@ -79,6 +79,25 @@ def main():
                         line += f"{k} {med*1e3:7.1f}us {nbytes/med/1e6:7.0f}GB/s | "
                     print(line, flush=True)
     ops.set_launch_config(0, 256, 2)
+    # peer pull emulated on one GPU: "reduced" shards live in two other local buffers
+    from apex_example_b200.tables import tile_aligned_shards
+    gflat = torch.randn(n, device=dev).mul_(64).half()
+    offs, acc = [], 0
+    for s_ in sizes:
+        offs.append(acc); acc += s_
+    for world in (2, 8):
+        red = [gflat.clone() for _ in range(world)]
+        t5 = TensorTable([list(torch.split(gflat, sizes)), p, m, v, c])
+        pull = ops.make_peer_pull(gflat.data_ptr(), tile_aligned_shards(offs, sizes, n, world), [r.data_ptr() for r in red], 2)
+        med, best = timeit(lambda: ops.fused_adam(t5, torch.float16, torch.float32, torch.float16,
+                                                  [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, 5, 1, 1)], inv_scale=1 / 64, pull=pull))
+        print(f"adam28 with pull emulated locally, world {world}: {med*1e3:.1f}us {28*n/med/1e6:.0f}GB/s")
+        out = torch.empty_like(gflat)
+        b = tile_aligned_shards(offs, sizes, n, world)
+        med, best = timeit(lambda: ops.peer_reduce_shard([r.data_ptr() for r in red], out, b[0], b[1], 1.0 / world, flag))
+        print(f"peer_reduce_shard emulated locally, world {world}: shard {b[1]-b[0]} elems {med*1e3:.1f}us "
+              f"{(world+1)*2*(b[1]-b[0])/med/1e6:.0f}GB/s (HBM bytes)")
+        del red, out
     med, best = timeit(lambda: ops.bucket_epilogue(flat, 0.125, flag))
     print(f"bucket_epilogue rw (4B/elem): {med*1e3:.1f}us {4*n/med/1e6:.0f}GB/s")
     med, best = timeit(lambda: ops.bucket_epilogue(flat, 1.0, flag))
