@@ -514,21 +514,24 @@ struct PeerBufs {
 
 // value of one reduced element: fp32 sum in rank order, one rounding to the gradient dtype, then
 // x factor with a second rounding (oracle_peer_reduce in oracle/amp_step_oracle.c)
-template <int DT>
-__device__ __forceinline__ float peer_mean(const float (&x)[B200_MAX_PEERS], int world, float factor) {
+template <int DT, int kWorld>
+__device__ __forceinline__ float peer_mean(const float (&x)[kWorld], int world, float factor) {
     float acc = x[0];
 #pragma unroll
-    for (int r = 1; r < B200_MAX_PEERS; r++)
+    for (int r = 1; r < kWorld; r++)
         if (r < world) acc = __fadd_rn(acc, x[r]);
     return __fmul_rn(round_through<DT>(acc), factor);
 }
 
-template <int DT, int kThreads>
+// kWorld = compile-time upper bound on the rank count (2, 4 or 8): the loads of every rank and of
+// kU groups are issued before the first use, so a thread keeps kWorld*kU 128/256-bit requests in
+// flight — NVLink round trips are 2-3x an HBM access, and this kernel is bound by them.
+template <int DT, int kThreads, int kWorld>
 __global__ void __launch_bounds__(kThreads)
 peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __restrict__ reduced, int64_t begin,
                    int64_t end, float factor, int32_t* flag) {
     using T = typename Elem<DT>::type;
-    constexpr int kU = (DT == B200_F32) ? 1 : 2;
+    constexpr int kU = (DT == B200_F32 ? 4 : 8) / kWorld > 0 ? (DT == B200_F32 ? 4 : 8) / kWorld : 1;
     bool bad = false;
     T* out = reinterpret_cast<T*>(reduced);
     const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
@@ -537,51 +540,54 @@ peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __res
     int64_t head = (kVec - (begin % kVec)) % kVec;
     if (head > end - begin) head = end - begin;
     if (gtid < head) {
-        float x[B200_MAX_PEERS];
+        float x[kWorld];
 #pragma unroll
-        for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? load1<DT>(bufs.p[r], begin + gtid) : 0.0f;
-        const float v = peer_mean<DT>(x, world, factor);
+        for (int r = 0; r < kWorld; r++) x[r] = r < world ? load1<DT>(bufs.p[r], begin + gtid) : 0.0f;
+        const float v = peer_mean<DT, kWorld>(x, world, factor);
         bad |= !is_finite(round_through<DT>(v));
         store1<DT>(out, begin + gtid, v);
     }
     const int64_t body = begin + head;
     const int64_t n_groups = (end - body) / kVec;
     for (int64_t g0 = gtid; g0 < n_groups; g0 += stride * kU) {
-        Raw8<DT> raw[kU][B200_MAX_PEERS];
+        Raw8<DT> raw[kU][kWorld];
         bool act[kU];
 #pragma unroll
         for (int u = 0; u < kU; u++) {
             const int64_t g = g0 + u * stride;
             act[u] = g < n_groups;
 #pragma unroll
-            for (int r = 0; r < B200_MAX_PEERS; r++)
+            for (int r = 0; r < kWorld; r++)
                 if (act[u] && r < world) load8<DT, false>(bufs.p[r], body + g * kVec, raw[u][r]);
         }
 #pragma unroll
         for (int u = 0; u < kU; u++) {
             if (!act[u]) continue;
-            float f[B200_MAX_PEERS][kVec];
+            float acc[kVec];
+            unpack8<DT>(raw[u][0], acc);
 #pragma unroll
-            for (int r = 0; r < B200_MAX_PEERS; r++)
-                if (r < world) unpack8<DT>(raw[u][r], f[r]);
-            float res[kVec];
+            for (int r = 1; r < kWorld; r++) {
+                if (r < world) {
+                    float f[kVec];
+                    unpack8<DT>(raw[u][r], f);
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
+                }
+            }
 #pragma unroll
             for (int i = 0; i < kVec; i++) {
-                float x[B200_MAX_PEERS];
-#pragma unroll
-                for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? f[r][i] : 0.0f;
-                res[i] = peer_mean<DT>(x, world, factor);
-                bad |= !is_finite(round_through<DT>(res[i]));
+                acc[i] = __fmul_rn(round_through<DT>(acc[i]), factor);
+                bad |= !is_finite(round_through<DT>(acc[i]));
             }
-            store8<DT>(out, body + (g0 + u * stride) * kVec, res);
+            store8<DT>(out, body + (g0 + u * stride) * kVec, acc);
         }
     }
     const int64_t tail0 = body + n_groups * kVec;
     if (gtid < end - tail0) {
-        float x[B200_MAX_PEERS];
+        float x[kWorld];
 #pragma unroll
-        for (int r = 0; r < B200_MAX_PEERS; r++) x[r] = r < world ? load1<DT>(bufs.p[r], tail0 + gtid) : 0.0f;
-        const float v = peer_mean<DT>(x, world, factor);
+        for (int r = 0; r < kWorld; r++) x[r] = r < world ? load1<DT>(bufs.p[r], tail0 + gtid) : 0.0f;
+        const float v = peer_mean<DT, kWorld>(x, world, factor);
         bad |= !is_finite(round_through<DT>(v));
         store1<DT>(out, tail0 + gtid, v);
     }
@@ -886,17 +892,24 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
         if (!pb.p[r]) return set_error(B200_EINVAL, "peer_reduce_shard: peer buffer %d is NULL", r);
     constexpr int kThreads = 256;
     const int64_t groups = (end - begin) / kVec + 1;
-    const int64_t want = (groups + kThreads * 2 - 1) / (kThreads * 2);
+    const int64_t want = (groups + kThreads - 1) / kThreads;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+#define B200_LAUNCH_REDUCE(W_)                                                                                    \
+    {                                                                                                             \
+        auto kernel = peer_reduce_kernel<DT, kThreads, W_>;                                                       \
+        static int occ = 0;                                                                                       \
+        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);                                               \
+        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                                  \
+        if (blocks > want) blocks = want;                                                                         \
+        if (blocks < 1) blocks = 1;                                                                               \
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag); \
+    }
     B200_DISPATCH_DT(dtype, DT, {
-        auto kernel = peer_reduce_kernel<DT, kThreads>;
-        static int occ = 0;
-        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
-        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;
-        if (blocks > want) blocks = want;
-        if (blocks < 1) blocks = 1;
-        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag);
+        if (world <= 2) B200_LAUNCH_REDUCE(2)
+        else if (world <= 4) B200_LAUNCH_REDUCE(4)
+        else B200_LAUNCH_REDUCE(8)
     })
+#undef B200_LAUNCH_REDUCE
     return after_launch("peer_reduce_shard");
 }
 
