@@ -82,6 +82,10 @@ SIGNATURES = {
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_fused_sgd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
                                  c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
+    "b200_peer_alloc": (c_int32, [c_int64, ctypes.POINTER(c_void_p), c_void_p]),
+    "b200_peer_open": (c_int32, [c_void_p, ctypes.POINTER(c_void_p)]),
+    "b200_peer_close": (c_int32, [c_void_p]),
+    "b200_peer_free": (c_int32, [c_void_p]),
     "b200_peer_reduce_shard": (c_int32, [ctypes.POINTER(c_void_p), c_int32, c_void_p, c_int64, c_int64, c_int32, c_float,
                                          c_void_p, c_void_p]),
     "b200_fused_adam_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),

@@ -876,6 +876,49 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles, int32_t grad
 }
 
 // ------------------------------------------------------------------------------------------------
+// peer buffer set-up (CUDA IPC).  Not part of the step: called once when the wrapper is built.
+// ------------------------------------------------------------------------------------------------
+static_assert(sizeof(cudaIpcMemHandle_t) == B200_IPC_HANDLE_BYTES, "IPC handle size is part of the ABI");
+
+int32_t b200_peer_alloc(int64_t bytes, void** dev_ptr, void* handle_out) {
+    if (bytes <= 0 || !dev_ptr || !handle_out) return set_error(B200_EINVAL, "peer_alloc: bad argument");
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, static_cast<size_t>(bytes));
+    if (e != cudaSuccess) return cuda_fail(e, "peer_alloc: cudaMalloc");
+    e = cudaMemset(p, 0, static_cast<size_t>(bytes));
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(static_cast<cudaIpcMemHandle_t*>(handle_out), p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return cuda_fail(e, "peer_alloc: cudaIpcGetMemHandle");
+    }
+    *dev_ptr = p;
+    return 0;
+}
+
+int32_t b200_peer_open(const void* handle, void** dev_ptr) {
+    if (!handle || !dev_ptr) return set_error(B200_EINVAL, "peer_open: bad argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return cuda_fail(e, "peer_open: cudaIpcOpenMemHandle (are the GPUs peer-accessible?)");
+    *dev_ptr = p;
+    return 0;
+}
+
+int32_t b200_peer_close(void* dev_ptr) {
+    if (!dev_ptr) return 0;
+    cudaError_t e = cudaIpcCloseMemHandle(dev_ptr);
+    return e == cudaSuccess ? 0 : cuda_fail(e, "peer_close");
+}
+
+int32_t b200_peer_free(void* dev_ptr) {
+    if (!dev_ptr) return 0;
+    cudaError_t e = cudaFree(dev_ptr);
+    return e == cudaSuccess ? 0 : cuda_fail(e, "peer_free");
+}
+
+// ------------------------------------------------------------------------------------------------
 // b200_peer_reduce_shard: reduce-scatter + mean + overflow check over NVLink peer memory.
 // ------------------------------------------------------------------------------------------------
 int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced, int64_t begin, int64_t end,

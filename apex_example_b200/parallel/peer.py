@@ -1,94 +1,127 @@
 """Peer-addressable gradient buffers for the fused reduce-scatter / optimizer path (S3').
 
-Plumbing only: every rank allocates its flat buffers with torch, exports them with CUDA IPC
-(torch's own storage-sharing mechanism), gathers the handles over the process group and opens
-its peers' buffers into its own address space with peer access enabled.  The arithmetic is in
-libapex_b200 (b200_peer_reduce_shard, b200_fused_*_peer); NCCL is used for two 4-byte
-all-reduces per step that act as cross-rank barriers and OR the overflow flags.
+Plumbing only: every rank allocates its flat buffers through the library (cudaMalloc + a CUDA IPC
+handle), the 64-byte handles are gathered over the process group, and every rank maps its peers'
+buffers into its own address space with peer access enabled.  The arithmetic is in libapex_b200
+(b200_peer_reduce_shard, b200_fused_*_peer); NCCL carries two 4-byte all-reduces per step that act
+as cross-rank barriers and OR the overflow flags.
 
 Single node only (NVLink / NVSwitch): every pair of GPUs must be peer-accessible.
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 import torch.distributed as dist
 
-from .. import ops
+from .. import _lib, ops
+
+_TYPESTR = {torch.float16: "<f2", torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}
+
+
+class _RawDeviceArray:
+    """Lets torch wrap a raw device pointer without copying (``__cuda_array_interface__``)."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2,
+                                         "strides": None}
+
+
+def _wrap(ptr: int, numel: int, dtype: torch.dtype, device) -> torch.Tensor:
+    if dtype == torch.bfloat16:       # no numpy typestr for bf16: wrap as int16 and reinterpret
+        t = torch.as_tensor(_RawDeviceArray(ptr, numel, "<i2"), device=device)
+        return t.view(torch.bfloat16)
+    return torch.as_tensor(_RawDeviceArray(ptr, numel, _TYPESTR[dtype]), device=device)
 
 
 class PeerBuffers:
-    """``names`` flat buffers of ``numel`` elements per rank, each addressable from every rank."""
+    """``names`` flat buffers of ``numel`` elements per rank, each addressable from every rank.
+
+    ``local[name]`` is this rank's buffer as a torch tensor (gradient views are carved out of it);
+    ``ptrs(name)[r]`` is rank r's buffer as a device address valid in THIS process.
+    Call :meth:`close` on every rank before the process group goes away."""
 
     def __init__(self, numel: int, dtype: torch.dtype, names=("grads", "reduced"), group=None, device=None):
         if not dist.is_initialized():
             raise RuntimeError("PeerBuffers needs an initialised process group")
+        lib = _lib.load()
         self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
+        if self.world > _lib.MAX_PEERS:
+            raise RuntimeError(f"the peer-memory path supports up to {_lib.MAX_PEERS} ranks (one NVSwitch domain)")
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.numel, self.dtype = numel, dtype
-        self.local = {n: torch.zeros(numel, dtype=dtype, device=self.device) for n in names}
-        self.peers = {}
-        self._keep = []
-        exported = {}
-        for n, t in self.local.items():
-            st = t.untyped_storage()
-            exported[n] = (st._share_cuda_(), t.storage_offset() * t.element_size())
-        gathered = [None] * self.world
-        dist.all_gather_object(gathered, exported, group=group)
-        for n in names:
-            views = []
-            for r in range(self.world):
-                if r == self.rank:
-                    views.append(self.local[n])
-                    continue
-                handle, extra_off = gathered[r][n]
-                # open in THIS device's address space: the storage then lives on the peer GPU but is
-                # addressable from kernels running here (peer access is enabled lazily by the runtime)
-                args = (self.device.index,) + tuple(handle[1:])
-                storage = torch.UntypedStorage._new_shared_cuda(*args)
-                t = torch.empty(0, dtype=dtype, device=self.device).set_(storage, extra_off // self.local[n].element_size(),
-                                                                          (numel,))
-                self._keep.append(storage)
-                views.append(t)
-            self.peers[n] = views
-        # tiny tensors for the two per-step barriers
+        self.names = tuple(names)
+        esize = torch.empty(0, dtype=dtype).element_size()
+        nbytes = (numel * esize + 255) // 256 * 256
+        self._own, self._opened = {}, []
+        handles = {}
+        with torch.cuda.device(self.device):
+            torch.cuda.current_stream().synchronize()
+            for n in self.names:
+                ptr = ctypes.c_void_p()
+                h = (ctypes.c_ubyte * 64)()
+                _lib.check(lib.b200_peer_alloc(nbytes, ctypes.byref(ptr), h), "peer_alloc")
+                self._own[n] = ptr.value
+                handles[n] = bytes(h)
+            gathered = [None] * self.world
+            dist.all_gather_object(gathered, handles, group=group)
+            self._ptrs = {}
+            for n in self.names:
+                row = []
+                for r in range(self.world):
+                    if r == self.rank:
+                        row.append(self._own[n])
+                        continue
+                    ptr = ctypes.c_void_p()
+                    hb = (ctypes.c_ubyte * 64).from_buffer_copy(gathered[r][n])
+                    _lib.check(lib.b200_peer_open(hb, ctypes.byref(ptr)), "peer_open")
+                    self._opened.append(ptr.value)
+                    row.append(ptr.value)
+                self._ptrs[n] = row
+        self.local = {n: _wrap(self._own[n], numel, dtype, self.device) for n in self.names}
         self._bar = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._closed = False
         dist.barrier(group=group)
 
-    def close(self):
-        """Drop the mappings of the peers' memory (call on every rank before the process group is
-        destroyed; the owners' buffers must outlive everybody's mappings, hence the barrier)."""
-        if self.peers is None:
-            return
-        torch.cuda.synchronize(self.device)
-        try:
-            dist.barrier(group=self.group)
-        except Exception:
-            pass
-        self.peers = None
-        self._keep.clear()
-        torch.cuda.synchronize(self.device)
-        try:
-            dist.barrier(group=self.group)
-        except Exception:
-            pass
-
     def ptrs(self, name):
-        return [t.data_ptr() for t in self.peers[name]]
+        return list(self._ptrs[name])
 
     def barrier(self, flag: torch.Tensor | None = None):
-        """Stream-ordered cross-rank barrier.  With ``flag`` (int32[1]) it also ORs the ranks' overflow
-        flags in place (all-reduce MAX) — 4 bytes over NCCL, no host sync."""
-        t = flag if flag is not None else self._bar
+        """Stream-ordered cross-rank barrier.  With ``flag`` (int32) it also ORs the ranks' overflow
+        flags in place (all-reduce MAX of one word) — 4 bytes over NCCL, no host sync."""
+        t = flag[:1] if flag is not None else self._bar
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+
+    def close(self):
+        """Unmap the peers' buffers, wait for everybody, then free our own.  The tensors in
+        ``local`` (and every view of them) must not be used afterwards."""
+        if self._closed:
+            return
+        self._closed = True
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            torch.cuda.synchronize()
+            for p in self._opened:
+                lib.b200_peer_close(p)
+            self._opened = []
+            try:
+                dist.barrier(group=self.group)
+            except Exception:
+                pass
+            self.local = {}
+            for p in self._own.values():
+                lib.b200_peer_free(p)
+            self._own = {}
 
 
 class PeerGradientReducer:
     """reduce-scatter + mean + check (one kernel) followed by a flag-OR barrier; hands the optimizer a
     b200_peer_pull so its step kernel gathers the reduced shards on the fly."""
 
-    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True, predivide: float = 1.0):
+    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True):
         self.buf = buffers
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1

@@ -273,6 +273,16 @@ typedef struct b200_peer_pull {
     int32_t     elem_size;                  /* bytes per gradient element (2 or 4) */
 } b200_peer_pull;
 
+/* Set-up / tear-down of the peer-addressable buffers (the only entry points that allocate; call
+ * them once, outside the step).  b200_peer_alloc: cudaMalloc + cudaIpcGetMemHandle (64-byte
+ * handle to ship to the other ranks).  b200_peer_open: map a peer's buffer into this process with
+ * peer access enabled.  Close every mapping (all ranks, then a barrier) before the owner frees. */
+#define B200_IPC_HANDLE_BYTES 64
+int32_t b200_peer_alloc(int64_t bytes, void** dev_ptr, void* handle_out);
+int32_t b200_peer_open(const void* handle, void** dev_ptr);
+int32_t b200_peer_close(void* dev_ptr);
+int32_t b200_peer_free(void* dev_ptr);
+
 int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced,
                                int64_t begin, int64_t end, int32_t dtype, float factor,
                                int32_t* dev_flag, void* stream);

@@ -164,7 +164,8 @@ def _worker_ipc(rank, world, port):
                             step=1 if step == 1 else 2, inv_scale=(1.0 / S) if step == 1 else (2.0 / S))
         assert_lists_bit_equal(dp, hp, f"p(rank {rank}, step {step})")
         assert_lists_bit_equal(dc, hc, f"copy(rank {rank}, step {step})")
-    dist.barrier()
+    del table
+    bufs.close()
     dist.destroy_process_group()
 
 
