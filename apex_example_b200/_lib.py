@@ -42,7 +42,7 @@ MAX_PEERS = 8
 
 class PeerPull(ctypes.Structure):            # b200_peer_pull
     _fields_ = [("local_base", c_void_p), ("bounds", c_int64 * (MAX_PEERS + 1)), ("delta", c_int64 * MAX_PEERS),
-                ("world", c_int32), ("elem_size", c_int32)]
+                ("world", c_int32), ("elem_size", c_int32), ("first_tile", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
 
 NOALLOC_TABLE_BYTES = 256 * 1024
 

@@ -226,6 +226,7 @@ struct PeerPull {
     long long delta[B200_MAX_PEERS];
     int world;
     int elem_size;
+    unsigned first_tile;
 };
 
 // byte offset to add to a column-0 pointer for the tile that starts at `tile_ptr`
@@ -273,7 +274,8 @@ struct RowSlot {
 };
 
 template <class Op, int kThreads, int kUnroll>
-__device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, int win, bool& bad) {
+__device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, int win, uint32_t rot,
+                                           bool& bad) {
     __shared__ __align__(16) RowSlot s_slot[2];
     __shared__ uint32_t s_tile[2];
     const TableView tv = open_table(table);
@@ -281,13 +283,21 @@ __device__ __forceinline__ void walk_tiles(const void* table, const typename Op:
     uint32_t t = blockIdx.x;
     if (t >= tv.n_tiles) return;
     const bool loader = threadIdx.x < 4;
+    // `rot` rotates the traversal: logical tile i is list entry (i + rot) mod n_tiles.  The peer path
+    // starts every rank at its OWN shard, so at any moment the ranks pull from different owners.
+    if (rot >= tv.n_tiles) rot = 0;
+    auto entry = [&](uint32_t i) {
+        uint32_t j = i + rot;
+        if (j >= tv.n_tiles) j -= tv.n_tiles;
+        return __ldg(reinterpret_cast<const uint2*>(tv.tiles + j));
+    };
     uint2 tl_next = make_uint2(0u, 0u);          // tile entry of iteration i+1 (loader threads only)
     if (loader) {
-        const uint2 tl0 = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
+        const uint2 tl0 = entry(t);
         cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
                    reinterpret_cast<const char*>(tv.rows + tl0.x) + threadIdx.x * 16);
         if (threadIdx.x == 0) s_tile[0] = tl0.y;
-        if (t + G < tv.n_tiles) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t + G));
+        if (t + G < tv.n_tiles) tl_next = entry(t + G);
         cp_async_wait_all();
     }
     __syncthreads();
@@ -299,7 +309,7 @@ __device__ __forceinline__ void walk_tiles(const void* table, const typename Op:
                        reinterpret_cast<const char*>(tv.rows + tl_next.x) + threadIdx.x * 16);
             if (threadIdx.x == 0) s_tile[slot ^ 1] = tl_next.y;
             const uint32_t t2 = t + 2 * G;
-            if (t2 < tv.n_tiles && t2 > t) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t2));
+            if (t2 < tv.n_tiles && t2 > t) tl_next = entry(t2);
         }
         const b200_table_row row = s_slot[slot].row;
         const uint32_t tile_idx = s_tile[slot];

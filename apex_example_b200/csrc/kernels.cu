@@ -88,7 +88,7 @@ tile_kernel(const void* __restrict__ table, const __grid_constant__ typename Op:
     int win = 0;
     if (Op::prologue(prm, win)) return;
     bool bad = false;
-    walk_tiles<Op, kThreads, kUnroll * Op::kUnrollMul>(table, prm, win, bad);
+    walk_tiles<Op, kThreads, kUnroll * Op::kUnrollMul>(table, prm, win, Op::rotation(prm), bad);
     Op::finish(prm, bad);
 }
 
@@ -136,6 +136,7 @@ struct ScaleOp {
     static constexpr int kUnrollMul = 2;     // 1-2 light columns: keep more groups in flight
     struct Ctx { float s; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) {
         return Ctx{p.dev_scale ? __ldg(p.dev_scale) : p.scale};
     }
@@ -181,6 +182,7 @@ struct AxpbyOp {
     static constexpr int kUnrollMul = 1;
     struct Ctx { float a, b; int32_t chk; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) {
         return Ctx{p.a, p.b, p.arg_to_check};
     }
@@ -231,6 +233,7 @@ struct CheckOp {
     static constexpr int kUnrollMul = 4;     // read-only, one column: 4-8 loads in flight per thread
     struct Ctx { int32_t col; };
     static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
     static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) { return Ctx{p.col}; }
     template <int U>
     static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
@@ -292,6 +295,7 @@ struct AdamOp {
     static constexpr int kUnrollMul = 1;
     struct Ctx { AdamConsts k; float s; const void* g; };     // g: the tile's gradient column (local or a peer's)
     static constexpr int kCopyCol = 4;
+    static __device__ __forceinline__ uint32_t rotation(const Params& p) { return p.pull.first_tile; }
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
         const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
         if (skip) step_epilogue(p.sync, true);
@@ -388,6 +392,7 @@ struct SgdOp {
     static constexpr int kUnrollMul = 1;
     struct Ctx { SgdConsts k; float s; const void* g; };
     static constexpr int kCopyCol = 3;
+    static __device__ __forceinline__ uint32_t rotation(const Params& p) { return p.pull.first_tile; }
     static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
         const bool skip = step_prologue(p.dev_found_inf, p.sync, win);
         if (skip) step_epilogue(p.sync, true);
@@ -786,6 +791,7 @@ static int to_pull(const b200_peer_pull* p, PeerPull& out, const char* name) {
     out.local_base = static_cast<const char*>(p->local_base);
     out.world = p->world;
     out.elem_size = p->elem_size;
+    out.first_tile = p->first_tile;
     for (int r = 0; r <= p->world; r++) out.bounds[r] = p->bounds[r];
     for (int r = 0; r < p->world; r++) out.delta[r] = p->delta[r];
     for (int r = 0; r < p->world; r++)

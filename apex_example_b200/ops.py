@@ -89,7 +89,7 @@ def peer_reduce_shard(peer_ptrs, reduced: torch.Tensor, begin: int, end: int, fa
                "peer_reduce_shard")
 
 
-def make_peer_pull(local_base_ptr: int, bounds, reduced_ptrs, elem_size: int) -> "PeerPull":
+def make_peer_pull(local_base_ptr: int, bounds, reduced_ptrs, elem_size: int, first_tile: int = 0) -> "PeerPull":
     world = len(reduced_ptrs)
     pp = PeerPull()
     pp.local_base = local_base_ptr
@@ -99,6 +99,7 @@ def make_peer_pull(local_base_ptr: int, bounds, reduced_ptrs, elem_size: int) ->
         pp.delta[r] = int(reduced_ptrs[r]) - int(local_base_ptr)
     pp.world = world
     pp.elem_size = elem_size
+    pp.first_tile = int(first_tile)
     return pp
 
 

@@ -121,7 +121,7 @@ class PeerGradientReducer:
     """reduce-scatter + mean + check (one kernel) followed by a flag-OR barrier; hands the optimizer a
     b200_peer_pull so its step kernel gathers the reduced shards on the fly."""
 
-    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True):
+    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True, first_tiles=None):
         self.buf = buffers
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1
@@ -129,7 +129,8 @@ class PeerGradientReducer:
         self._grad_ptrs = buffers.ptrs("grads")
         self._red_ptrs = buffers.ptrs("reduced")
         self.pull = ops.make_peer_pull(buffers.local["grads"].data_ptr(), self.bounds, self._red_ptrs,
-                                       buffers.local["grads"].element_size())
+                                       buffers.local["grads"].element_size(),
+                                       first_tile=first_tiles[buffers.rank] if first_tiles else 0)
 
     def reduce(self, overflow_flag: torch.Tensor):
         """Enqueue on the current stream: barrier -> shard reduction -> barrier + flag OR."""

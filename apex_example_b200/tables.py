@@ -114,19 +114,24 @@ def signature_of(columns) -> tuple:
 
 
 def tile_aligned_shards(offsets: Sequence[int], sizes: Sequence[int], total: int, world: int,
-                        tile_elems: int = _lib.TILE_ELEMS):
+                        tile_elems: int = _lib.TILE_ELEMS, return_first_tiles: bool = False):
     """Split a flat buffer (tensor t at element offset offsets[t], sizes[t] long) into `world`
     contiguous shards of roughly equal work whose boundaries never cut a tile of the optimizer's
-    table — the precondition of b200_fused_*_peer.  Returns world+1 element offsets."""
+    table — the precondition of b200_fused_*_peer.  Returns world+1 element offsets and, on
+    request, each rank's first tile index (valid when the table lists the tensors in flat order)."""
     starts = []
     for off, n in zip(offsets, sizes):
         starts.extend(range(off, off + n, tile_elems))
-    starts.sort()
-    bounds = [0]
+    if starts != sorted(starts):
+        if return_first_tiles:
+            raise RuntimeError("tile_aligned_shards: tensors must be listed in flat-buffer order")
+        starts.sort()
+    bounds, first = [0], [0]
     for r in range(1, world):
         k = round(r * len(starts) / world)
         bounds.append(starts[k] if k < len(starts) else total)
+        first.append(min(k, max(len(starts) - 1, 0)))
     bounds.append(total)
-    for a, b in zip(bounds, bounds[1:]):
-        assert a <= b
-    return bounds
+    for a_, b_ in zip(bounds, bounds[1:]):
+        assert a_ <= b_
+    return (bounds, first) if return_first_tiles else bounds

@@ -231,7 +231,8 @@ def main():
             offs.append(acc)
             acc += s_
         pbufs = PeerBuffers(n, torch.float16)
-        reducer = PeerGradientReducer(pbufs, tile_aligned_shards(offs, sizes, n, world))
+        bounds, first_tiles = tile_aligned_shards(offs, sizes, n, world, return_first_tiles=True)
+        reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles)
         gflat = pbufs.local["grads"]
         gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
     else:

@@ -271,6 +271,10 @@ typedef struct b200_peer_pull {
     int64_t     delta[B200_MAX_PEERS];      /* bytes from local_base to rank r's reduced buffer (this process's view) */
     int32_t     world;
     int32_t     elem_size;                  /* bytes per gradient element (2 or 4) */
+    uint32_t    first_tile;                 /* index (in the table's tile list) of this rank's first own tile: the
+                                               kernel starts its sweep there, so that at any moment the ranks pull
+                                               from DIFFERENT owners instead of all from the same one */
+    uint32_t    reserved;
 } b200_peer_pull;
 
 /* Set-up / tear-down of the peer-addressable buffers (the only entry points that allocate; call

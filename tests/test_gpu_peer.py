@@ -71,7 +71,7 @@ def test_fused_adam_pulls_each_tile_from_its_owner_emulated(world):
     gen = torch.Generator().manual_seed(10 + world)
     sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
     offs, total = _layout(sizes)
-    bounds = tile_aligned_shards(offs, sizes, total, world)
+    bounds, first = tile_aligned_shards(offs, sizes, total, world, return_first_tiles=True)
     S = 256.0
     host_g = [(torch.randn(total, generator=gen) * 1e-2 * S).half() for _ in range(world)]
     dev_g = [h.cuda() for h in host_g]
@@ -89,7 +89,8 @@ def test_fused_adam_pulls_each_tile_from_its_owner_emulated(world):
         dp, dm, dv, dc = ([t.clone().cuda() for t in lst] for lst in (hp, hm, hv, hc))
         gviews = [dev_g[rank][o:o + n] for o, n in zip(offs, sizes)]         # table column 0: the LOCAL flat buffer
         table = TensorTable([gviews, dp, dm, dv, dc])
-        pull = ops.make_peer_pull(dev_g[rank].data_ptr(), bounds, [t.data_ptr() for t in reduced], 2)
+        pull = ops.make_peer_pull(dev_g[rank].data_ptr(), bounds, [t.data_ptr() for t in reduced], 2,
+                                  first_tile=first[rank])           # rotated sweep: same result, other order
         ops.fused_adam(table, torch.float16, torch.float32, torch.float16,
                        [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, 1, 1, 1)], inv_scale=1.0 / S, pull=pull)
         op, om, ov, oc = ([t.clone() for t in lst] for lst in (hp, hm, hv, hc))
@@ -125,9 +126,9 @@ def _worker_ipc(rank, world, port):
     from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
     sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
     offs, total = _layout(sizes)
-    bounds = tile_aligned_shards(offs, sizes, total, world)
+    bounds, first = tile_aligned_shards(offs, sizes, total, world, return_first_tiles=True)
     bufs = PeerBuffers(total, torch.float16)
-    red = PeerGradientReducer(bufs, bounds)
+    red = PeerGradientReducer(bufs, bounds, first_tiles=first)
     S = 256.0
     host_all = [(torch.randn(total, generator=torch.Generator().manual_seed(100 + r)) * 1e-2 * S).half() for r in range(world)]
     want_red = torch.zeros(total, dtype=torch.float16)
