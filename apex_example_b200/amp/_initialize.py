@@ -32,7 +32,16 @@ def applier(value, fn):
     if isinstance(value, (str, bytes)):
         return value
     if isinstance(value, Mapping):
-        return {applier(k, fn): applier(v, fn) for k, v in value.items()}
+        mapped = {applier(k, fn): applier(v, fn) for k, v in value.items()}
+        if type(value) is dict:
+            return mapped
+        try:                                    # dict subclasses (e.g. dataclass-style model outputs) keep their type
+            return type(value)(mapped)
+        except Exception:
+            try:
+                return type(value)(**mapped)
+            except Exception:
+                return mapped
     if isinstance(value, tuple) and hasattr(value, "_fields"):       # namedtuple
         return type(value)(*(applier(v, fn) for v in value))
     if isinstance(value, Sequence):

@@ -190,6 +190,9 @@ def main():
     ap.add_argument("--workload", default="gpt2_small", choices=["gpt2_small", "gpt2_medium"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--train", action="store_true",
+                    help="also measure GPT-2 medium training samples/s (amp O2 + FusedAdam + apex DDP), reported under 'train'")
+    ap.add_argument("--train-batch", type=int, default=4, help="per-GPU micro-batch of 1024-token sequences")
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
@@ -383,6 +386,14 @@ def main():
         del table, check_table
         e2e = run_e2e(sizes, dev, world, max(3, min(args.steps, 20)), args.warmup, barrier)
 
+    # ---- the second half of BASELINE.json's metric: train samples/s (GPT-2 medium, amp O2, FusedAdam, apex DDP) ----
+    train = None
+    if args.train:
+        try:
+            train = run_train(dev, world, rank, barrier, args.train_batch)
+        except Exception as exc:                    # reported, never fatal for the headline line
+            train = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
     # ---- CPU baseline (rank 0, N = 1 only) ----
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -404,6 +415,7 @@ def main():
                        "collective": ("peer-memory reduce-scatter + pull-in-optimizer" if use_peer else "nccl all-reduce")
                        if world > 1 else "none"},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "train": train,
         }
         line.update(extra)
         print(json.dumps(line), flush=True)
@@ -412,6 +424,81 @@ def main():
         pbufs.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmup=3):
+    """GPT-2 medium (24 x 1024, 354.8M parameters, random init) on synthetic tokens through the
+    drop-in API exactly as the reference drives it: amp.initialize(O2) -> apex DDP -> scale_loss /
+    backward / FusedAdam.step.  The transformer's forward/backward is torch/transformers library
+    code; what is under test is everything between backward and the next forward."""
+    import torch.distributed as dist
+    from transformers import GPT2Config, GPT2LMHeadModel
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    from apex.parallel import DistributedDataParallel
+    from apex_example_b200 import ops
+
+    amp._amp_state.reset()
+    torch.manual_seed(0)
+    cfg = GPT2Config(n_embd=1024, n_layer=24, n_head=16)
+    try:
+        cfg._attn_implementation = "sdpa"
+    except Exception:
+        pass
+    model = GPT2LMHeadModel(cfg).to(dev)
+    n_params = sum(p.numel() for p in model.parameters())
+    opt = FusedAdam(model.parameters(), lr=1e-4, weight_decay=0.01)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    if world > 1:
+        model = DistributedDataParallel(model)
+    host_tokens = torch.randint(0, 50257, (micro_batch, seq), generator=torch.Generator().manual_seed(rank)).pin_memory()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+
+    def one(e=None):
+        tokens = host_tokens.to(dev, non_blocking=True)
+        out = model(input_ids=tokens, labels=tokens)
+        loss = out["loss"] if isinstance(out, dict) else out.loss
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+            if e is not None:
+                e[0].record()
+        if e is not None:
+            e[1].record()
+        opt.step()
+        if e is not None:
+            e[2].record()
+        return loss
+
+    for _ in range(warmup):
+        one()
+    barrier()
+    l0 = ops.launch_count()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for k in range(steps):
+        loss = one(ev[k])
+    t1.record()
+    barrier()
+    ms = t0.elapsed_time(t1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    post_bwd = sum(e[0].elapsed_time(e[1]) for e in ev) / steps      # scale_loss exit: (DDP join) + check + scaler update
+    step_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / steps       # FusedAdam.step: one launch per dtype set
+    scaler = amp._amp_state.loss_scalers[0]
+    res = {"model": "GPT-2 medium (GPT2Config(n_embd=1024, n_layer=24, n_head=16)), amp O2, FusedAdam, "
+                    + ("apex DistributedDataParallel" if world > 1 else "single GPU"),
+           "params": n_params, "micro_batch_per_gpu": micro_batch, "seq_len": seq, "n_gpus": world,
+           "samples_per_s": micro_batch * world / (ms * 1e-3), "tokens_per_s": micro_batch * seq * world / (ms * 1e-3),
+           "ms_per_step": ms, "ms_scale_loss_exit": post_bwd, "ms_optimizer_step": step_ms,
+           "optimizer_step_gbs": BYTES_PER_PARAM * n_params / (step_ms * 1e-3) / 1e9,
+           "b200_kernel_launches_per_step": (ops.launch_count() - l0) / steps,
+           "final_loss": float(loss.item()), "loss_scale": scaler.loss_scale(), "steps": steps}
+    del model, opt
+    torch.cuda.empty_cache()
+    return res
 
 
 def run_e2e(sizes, dev, world, steps, warmup, barrier):
