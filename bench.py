@@ -190,8 +190,8 @@ def main():
     ap.add_argument("--workload", default="gpt2_small", choices=["gpt2_small", "gpt2_medium"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--train", action="store_true",
-                    help="also measure GPT-2 medium training samples/s (amp O2 + FusedAdam + apex DDP), reported under 'train'")
+    ap.add_argument("--no-train", dest="train", action="store_false",
+                    help="skip the GPT-2 medium training measurement (amp O2 + FusedAdam + apex DDP) reported under 'train'")
     ap.add_argument("--train-batch", type=int, default=4, help="per-GPU micro-batch of 1024-token sequences")
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
