@@ -374,3 +374,41 @@ def test_amp_c_compat_through_multi_tensor_applier():
     out = [torch.zeros(64, device="cuda")]
     multi_tensor_applier(amp_C.multi_tensor_axpby, flag, [g, p, out], 2.0, 1.0, -1)
     assert torch.allclose(out[0], torch.full((64,), 2.9, device="cuda"))
+
+
+def test_resnet50_o2_fused_sgd_two_dtype_sets():
+    """BASELINE config 3 in miniature: ResNet-50 at O2 keeps its 106 BatchNorm tensors in fp32, so the
+    optimizer runs two launch sets — (fp16 grad, fp32 master, fp16 copy) and (fp32, fp32, none)."""
+    torchvision = pytest.importorskip("torchvision")
+    from apex import amp
+    from apex.optimizers import FusedSGD
+    from apex_example_b200 import ops
+    torch.manual_seed(0)
+    model = torchvision.models.resnet50().cuda()
+    opt = FusedSGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, materialize_master_grads=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    n16 = sum(p.numel() for p in model.parameters() if p.dtype == torch.float16)
+    n32 = sum(p.numel() for p in model.parameters() if p.dtype == torch.float32)
+    assert n16 + n32 == 25_557_032 and n32 == 53_120                     # SURVEY.md §8 sizes
+    x = torch.randn(8, 3, 64, 64, device="cuda")
+    y = torch.randint(0, 1000, (8,), device="cuda")
+    bn_before = model.bn1.weight.detach().clone()
+    conv_before = model.conv1.weight.detach().clone()
+    launches = []
+    for _ in range(3):
+        loss = torch.nn.functional.cross_entropy(model(x), y)
+        opt.zero_grad()
+        l0 = ops.launch_count()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+        launches.append(ops.launch_count() - l0)
+    torch.cuda.synchronize()
+    assert torch.isfinite(loss)
+    assert launches == [5, 5, 5]            # check fp16 + check fp32 + scaler update + one SGD launch per dtype set
+    assert not torch.equal(model.bn1.weight, bn_before) and model.bn1.weight.dtype == torch.float32
+    assert not torch.equal(model.conv1.weight, conv_before) and model.conv1.weight.dtype == torch.float16
+    stash = opt._amp_stash
+    for master, model_p in stash.model_of.items():
+        assert master.dtype == torch.float32 and torch.equal(model_p, master.half())
+        assert "momentum_buffer" in opt.state[master] and opt.state[master]["momentum_buffer"].dtype == torch.float32
