@@ -13,6 +13,7 @@ Two paths:
 """
 from __future__ import annotations
 
+import operator
 import types
 
 import torch
@@ -23,6 +24,7 @@ from ..tables import TensorTable, signature_of
 from ._amp_state import _amp_state, maybe_print
 
 _HALF_TYPES = (torch.float16, torch.bfloat16)
+_GRAD_OF = operator.attrgetter("grad")
 
 
 def _is_fused(optimizer) -> bool:
@@ -69,23 +71,37 @@ def _prepare_amp_backward(self):
 def _post_amp_backward(self, scaler):
     stash = self._amp_stash
     stash.scaler = scaler
-    model16 = [p for p in stash.all_fp16_params if p.grad is not None]
-    fp32 = [p for p in stash.all_fp32_params if p.grad is not None]
 
     if _lazy(self):
+        # Only an overflow CHECK happens here (the unscale is fused into the step kernel).  The list of
+        # gradient tensors is cached and re-validated with one C-level identity pass, so the steady
+        # state costs no per-tensor Python work (matters for lists of tens of thousands of tensors).
+        plan = stash.__dict__.get("_check_plan")
+        if plan is None or not all(map(operator.is_, map(_GRAD_OF, plan["holders"]), plan["grads"])):
+            holders = stash.all_fp16_params + stash.all_fp32_params
+            grads = [p.grad for p in holders]
+            by_dtype = {}
+            for g in grads:
+                if g is not None:
+                    by_dtype.setdefault(g.dtype, []).append(g)
+            scaler._ensure_state()
+            plan = {"holders": holders, "grads": grads,
+                    "calls": [(TensorTable([gs]), dt) for dt, gs in by_dtype.items()],
+                    "ids": frozenset(id(p) for p, g in zip(holders, grads) if g is not None)}
+            stash._check_plan = plan
         checked = _amp_state.ddp_checked_backward
         if checked:
             # DDP's bucket epilogue raised the flag already — provided it saw every gradient we own
-            ids = getattr(_amp_state, "ddp_checked_ids", frozenset())
-            checked = all(id(p) in ids for p in model16) and all(id(p) in ids for p in fp32)
+            checked = plan["ids"] <= getattr(_amp_state, "ddp_checked_ids", frozenset())
         if not checked:
-            for dt in _HALF_TYPES:
-                scaler.check([p.grad for p in model16 if p.grad.dtype == dt])
-            scaler.check([p.grad for p in fp32 if p.grad.dtype == torch.float32])
-            for dt in _HALF_TYPES:          # O3: "fp32" list holds the half params themselves
-                scaler.check([p.grad for p in fp32 if p.grad.dtype == dt])
+            flag = scaler.overflow_ref()
+            for tbl, dt in plan["calls"]:
+                ops.multi_tensor_check(tbl, 0, dt, flag)
         stash.grads_scaled = True
         return
+
+    model16 = [p for p in stash.all_fp16_params if p.grad is not None]
+    fp32 = [p for p in stash.all_fp32_params if p.grad is not None]
 
     # materialised path -------------------------------------------------------------------------
     stash.grads_scaled = False

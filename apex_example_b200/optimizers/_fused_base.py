@@ -8,12 +8,23 @@ typical O2 model needs one launch for the fp16 parameters and one for the fp32 B
 """
 from __future__ import annotations
 
+import operator
+
 import torch
 
 from .. import _lib, ops
 from ..tables import TensorTable
 
 _SUPPORTED = (torch.float16, torch.bfloat16, torch.float32)
+_GRAD_OF = operator.attrgetter("grad")
+
+
+class _Never:
+    """Holder whose .grad never matches: marks plans that must not be replayed."""
+    grad = object()
+
+
+_NEVER = _Never()
 
 
 class AmpStash:
@@ -38,7 +49,7 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         self._tables = {}               # launch-set key -> TensorTable
         self._counter = None            # ops.StepCounter once device-side skipping is in play
         self._step_offsets = {}         # group index -> offset of the group's step from the counter
-        self._plain_state = None
+        self._plan = None               # cached launch plan (see _replay_plan)
 
     # ---- subclass interface ----------------------------------------------------------------------
     def _state_columns(self, p, group):
@@ -106,6 +117,7 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         self._counter = None
         self._step_offsets = {}
         self._tables = {}
+        self._plan = None
 
     def zero_grad(self, set_to_none=None):
         if set_to_none is None:
@@ -118,12 +130,58 @@ class FusedOptimizerBase(torch.optim.Optimizer):
             super().zero_grad(set_to_none=False)
 
     # ---- the step ------------------------------------------------------------------------------------
+    def _replay_plan(self):
+        """Steady-state fast path.  When every gradient is the very tensor object the plan was built
+        from (gradients accumulate in place, or live in DDP buckets) and no parameter storage moved,
+        the cached tables are still right and the step is launched without touching the parameters
+        one by one again.  With tens of thousands of small tensors the per-tensor Python work of
+        the slow path costs ~100 ms a step (apex has the same loop); this check is one C-level pass."""
+        plan = self._plan
+        if plan is None:
+            return False
+        holders, grads, n_groups, device = plan["holders"], plan["grads"], plan["n_groups"], plan["device"]
+        if n_groups != len(self.param_groups) or plan["grads_scaled"] != self._grads_scaled_now():
+            return False
+        if not all(map(operator.is_, map(_GRAD_OF, holders), grads)):
+            return False
+        if plan["n_params"] != sum(len(g["params"]) for g in self.param_groups):
+            return False
+        plan["age"] += 1
+        if plan["age"] % 64 == 0:          # storages that moved without the grad object changing (model.to(), .data = ...)
+            if plan["ptrs"] != tuple(t.data_ptr() for t in plan["watch"]):
+                return False
+        inv_scale, dev_inv, dev_found = self._scale_args()
+        steps, sync = self._next_steps(device, dev_found is not None)
+        first = True
+        with torch.cuda.device(device):
+            for key, table, gids in plan["launches"]:
+                this_sync = None
+                if sync is not None:
+                    this_sync = sync if first else ops.StepSync(sync.dev_counters, sync.mirror, sync.known_skips, 1)
+                self._launch(table, key, gids, steps, (inv_scale, dev_inv, dev_found), this_sync)
+                first = False
+        return True
+
+    def _grads_scaled_now(self):
+        st = self._amp_stash
+        return bool(st is not None and st.grads_scaled)
+
     def _fused_step(self):
+        if self._replay_plan():
+            return
+        self._plan = None
         sets = {}
         device = None
+        holders, grad_objs, watch = [], [], []
         for gi, group in enumerate(self.param_groups):
             for p in group["params"]:
                 g, copy = self._grad_and_copy(p)
+                holder = p
+                st_ = self._amp_stash
+                if st_ is not None and p in st_.model_of and p.grad is None:
+                    holder = st_.model_of[p]                 # the gradient lives on the fp16 model parameter
+                holders.append(holder)
+                grad_objs.append(g)
                 if g is None:
                     continue
                 if g.is_sparse:
@@ -141,8 +199,15 @@ class FusedOptimizerBase(torch.optim.Optimizer):
                 cols = self._state_columns(p, group)
                 if s["state"] is None:
                     s["state"] = [[] for _ in cols]
-                s["g"].append(g if g.is_contiguous() else g.contiguous())
+                if not g.is_contiguous():
+                    g = g.contiguous()
+                    grad_objs[-1] = None                     # a temporary copy: never replay this plan
+                    holders[-1] = _NEVER
+                s["g"].append(g)
                 s["p"].append(p.data)
+                watch.append(p)
+                if copy is not None:
+                    watch.append(copy)
                 for lst, t in zip(s["state"], cols):
                     lst.append(t)
                 if copy is not None:
@@ -154,6 +219,7 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         inv_scale, dev_inv, dev_found = self._scale_args()
         steps, sync = self._next_steps(device, dev_found is not None)
         first = True
+        launches = []
         with torch.cuda.device(device):
             for key, s in sets.items():
                 columns = [s["g"], s["p"]] + s["state"] + ([s["c"]] if s["c"] else [])
@@ -169,4 +235,9 @@ class FusedOptimizerBase(torch.optim.Optimizer):
                 if sync is not None:
                     this_sync = sync if first else ops.StepSync(sync.dev_counters, sync.mirror, sync.known_skips, 1)
                 self._launch(table, key, s["gids"], steps, (inv_scale, dev_inv, dev_found), this_sync)
+                launches.append((key, table, s["gids"]))
                 first = False
+        self._plan = {"holders": holders, "grads": grad_objs, "launches": launches, "device": device,
+                      "n_groups": len(self.param_groups), "n_params": sum(len(g["params"]) for g in self.param_groups),
+                      "grads_scaled": self._grads_scaled_now(), "watch": watch,
+                      "ptrs": tuple(t.data_ptr() for t in watch), "age": 0}

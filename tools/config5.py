@@ -35,8 +35,15 @@ def main():
     dev = torch.device("cuda", 0)
     sizes = many_small(total=args.total, seed=0)
     n = sum(sizes)
+    # every tensor starts 32-byte aligned inside the flat gradient buffer (as in the DDP buckets and as
+    # separately allocated gradients are); the ragged sizes still exercise the scalar tail path
+    offs, acc = [], 0
+    for s_ in sizes:
+        acc += (-acc) % 16
+        offs.append(acc)
+        acc += s_
     flat_p = (torch.randn(n, device=dev) * 0.02)
-    flat_g = torch.zeros(n, dtype=torch.float16, device=dev)
+    flat_g = torch.zeros(acc, dtype=torch.float16, device=dev)
 
     class Holder(torch.nn.Module):
         def __init__(self):
@@ -48,8 +55,8 @@ def main():
     model, opt = amp.initialize(model, opt, opt_level="O3", loss_scale="dynamic", verbosity=0)
     params = list(model.parameters())
     assert all(p.dtype == torch.float16 for p in params)
-    for p, g in zip(params, torch.split(flat_g, sizes)):
-        p.grad = g
+    for p, o, s_ in zip(params, offs, sizes):
+        p.grad = flat_g[o:o + s_]
     setup_s = time.time() - t0
     rng = random.Random(1)
     sc = oracle.LossScaler()
@@ -58,7 +65,7 @@ def main():
     normal_ms, skip_ms, host_ms = [], [], []
     gen = torch.Generator(device=dev).manual_seed(0)
     for it in range(args.steps):
-        flat_g.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * sc.loss_scale).half())
+        flat_g.copy_((torch.randn(flat_g.numel(), device=dev, generator=gen) * 1e-3 * sc.loss_scale).half())
         inject = rng.random() < 0.1 or it in (0, 1)
         if inject:
             t = rng.randrange(len(sizes))
