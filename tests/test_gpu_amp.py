@@ -395,7 +395,7 @@ def test_resnet50_o2_fused_sgd_two_dtype_sets():
     bn_before = model.bn1.weight.detach().clone()
     conv_before = model.conv1.weight.detach().clone()
     launches = []
-    for _ in range(3):
+    for _ in range(14):                     # the first steps overflow at scale 2**16 and are skipped: the usual warm-up
         loss = torch.nn.functional.cross_entropy(model(x), y)
         opt.zero_grad()
         l0 = ops.launch_count()
@@ -406,7 +406,8 @@ def test_resnet50_o2_fused_sgd_two_dtype_sets():
     torch.cuda.synchronize()
     assert torch.isfinite(loss)
     # check fp16 + check fp32 + scaler update + one SGD launch per dtype set (+ the scaler's one-time init)
-    assert launches[0] in (5, 6) and launches[1:] == [5, 5]
+    assert launches[0] in (5, 6) and set(launches[1:]) == {5}
+    assert opt.state_dict()["param_groups"][0]["step"] >= 1          # counts only the steps that really ran
     assert not torch.equal(model.bn1.weight, bn_before) and model.bn1.weight.dtype == torch.float32
     assert not torch.equal(model.conv1.weight, conv_before) and model.conv1.weight.dtype == torch.float16
     stash = opt._amp_stash
