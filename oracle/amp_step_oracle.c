@@ -111,6 +111,13 @@ void oracle_convert(const void* in, int in_dt, void* out, int out_dt, int64_t n)
  * same rule as torch._amp_foreach_non_finite_check_and_unscale_ (TORCH/amp/grad_scaler.py:292-298). */
 int oracle_check(const void* g, int dt, int64_t n) {
     int flag = 0;
+    if (dt == DT_F16 || dt == DT_BF16) {            /* same predicate on the raw bits (exponent all ones) */
+        const uint16_t* h = (const uint16_t*)g;
+        const uint16_t mask = dt == DT_F16 ? 0x7c00u : 0x7f80u;
+        #pragma omp parallel for reduction(|:flag) schedule(static)
+        for (int64_t i = 0; i < n; i++) flag |= (h[i] & mask) == mask;
+        return flag;
+    }
     #pragma omp parallel for reduction(|:flag) schedule(static)
     for (int64_t i = 0; i < n; i++) flag |= !finite_f(load_as_float(g, dt, i));
     return flag;
@@ -163,6 +170,44 @@ typedef struct {
  * inv_scale (the unscale of LossScaler.unscale), and the fp16/bf16 model copy is written from
  * the new fp32 master (apex _master_params_to_model_params).  State may be fp16/bf16 (O3):
  * values are widened to float, updated, and rounded back. */
+#if defined(__x86_64__) && defined(__GNUC__)
+/* Same arithmetic as the generic loop below for the O2 layout (fp16 grad, fp32 state, fp16 copy),
+ * written so that gcc can vectorise it: hardware fp16 conversions (F16C, round-to-nearest-even),
+ * IEEE vsqrtps / vdivps, and no FMA contraction (-ffp-contract=off).  Used only so that the timed
+ * CPU baseline is not handicapped by the software conversions; tests/test_oracle.py checks that it
+ * gives bit-identical results to the generic path. */
+__attribute__((target("avx2,f16c"), optimize("O3")))
+static void adam_o2_f16c(const uint16_t* g16, float* p, float* m, float* v, uint16_t* c16, int64_t n,
+                         float inv_scale, float w1, float b2, float w2, float neg_step, float bc2_sqrt, float eps,
+                         float wd, float decay, int has_wd, int adamw) {
+    const _Float16* g = (const _Float16*)g16;
+    _Float16* c = (_Float16*)c16;
+    const float om_w1 = 1.0f - w1;
+    const int lerp_hi = !(w1 < 0.5f);
+    #pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float gi = (float)g[i] * inv_scale;
+        float pi = p[i], mi = m[i], vi = v[i];
+        if (has_wd) {
+            if (adamw) pi = pi * decay;
+            else gi = gi + wd * pi;
+        }
+        float d = gi - mi;
+        mi = lerp_hi ? gi - d * om_w1 : mi + w1 * d;
+        vi = vi * b2 + (w2 * gi) * gi;
+        float denom = sqrtf(vi) / bc2_sqrt + eps;
+        pi = pi + neg_step * (mi / denom);
+        p[i] = pi; m[i] = mi; v[i] = vi;
+        if (c) c[i] = (_Float16)pi;
+    }
+}
+static int have_f16c(void) { return __builtin_cpu_supports("avx2") && __builtin_cpu_supports("f16c"); }
+#else
+static int have_f16c(void) { return 0; }
+#endif
+
+int oracle_force_generic = 0;       /* tests flip this to compare the two paths */
+
 void oracle_adam(const void* g, int g_dt, void* p, void* m, void* v, int s_dt,
                  void* copy, int c_dt, int64_t n,
                  const oracle_adam_group* grp, float inv_scale) {
@@ -179,6 +224,13 @@ void oracle_adam(const void* g, int g_dt, void* p, void* m, void* v, int s_dt,
     const int has_wd = grp->weight_decay != 0.0;
     const int adamw = grp->adam_w_mode;
 
+#if defined(__x86_64__) && defined(__GNUC__)
+    if (!oracle_force_generic && g_dt == DT_F16 && s_dt == DT_F32 && (!copy || c_dt == DT_F16) && have_f16c()) {
+        adam_o2_f16c((const uint16_t*)g, (float*)p, (float*)m, (float*)v, (uint16_t*)copy, n, inv_scale, w1, b2, w2,
+                     neg_step, bc2_sqrt, eps, wd, decay, has_wd, adamw);
+        return;
+    }
+#endif
     #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
         float gi = load_as_float(g, g_dt, i) * inv_scale;

@@ -246,3 +246,29 @@ def test_list_step_skips_everything_on_overflow():
     gs[2][-1] = 1.0
     assert oracle.adam_list(gs, ps, ms, vs, cs, inv_scale=1 / 64, lr=1e-3, step=1) == 0
     assert not torch.equal(ps[0], before[0]) and torch.equal(cs[1], ps[1].half())
+
+
+def test_vectorised_o2_path_is_bit_identical_to_the_generic_loop():
+    """The timed CPU baseline uses an F16C/AVX2-vectorisable loop for the O2 layout; it must give
+    exactly the generic scalar loop's bits (including inf / NaN / subnormal inputs)."""
+    import ctypes
+    force = ctypes.c_int.in_dll(oracle.lib(), "oracle_force_generic")
+    N = 1 << 16
+    for adamw, wd, b1 in ((True, 0.01, 0.9), (False, 0.01, 0.9), (True, 0.0, 0.3)):
+        outs = []
+        for f in (0, 1):
+            force.value = f
+            try:
+                gen = torch.Generator().manual_seed(5)
+                p = torch.randn(N, generator=gen) * 0.05
+                m = torch.randn(N, generator=gen) * 1e-3
+                v = (torch.randn(N, generator=gen) * 1e-3) ** 2
+                c = torch.zeros(N, dtype=torch.float16)
+                g = (torch.randn(N, generator=gen) * 64).half()
+                g[5], g[6], g[7], g[8] = float("inf"), float("nan"), 6e-8, -0.0
+                oracle.adam(g, p, m, v, c, lr=1e-3, beta1=b1, weight_decay=wd, step=3, adam_w_mode=adamw, inv_scale=1 / 64)
+                outs.append((p, m, v, c))
+            finally:
+                force.value = 0
+        for a, b in zip(*outs):
+            assert _bits_equal_or_both_nan(a, b)
