@@ -70,6 +70,8 @@ def lib():
     if _lib is None:
         _lib = ctypes.CDLL(build())
         _lib.oracle_check.restype = ctypes.c_int
+        if os.environ.get("ORACLE_FORCE_GENERIC"):
+            ctypes.c_int.in_dll(_lib, "oracle_force_generic").value = 1
     return _lib
 
 
