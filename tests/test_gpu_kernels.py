@@ -295,3 +295,47 @@ def test_error_paths_raise():
     with pytest.raises(RuntimeError):
         ops.bucket_epilogue(torch.zeros(8), 1.0)
     assert ops.launch_count() > 0
+
+
+def test_no_kernel_writes_outside_its_tensors_canaries():
+    """compute-sanitizer is closed on this GPU pool, so out-of-bounds writes are hunted directly: every
+    tensor sits between 64-element sentinel regions that must survive all kernels untouched."""
+    gen = torch.Generator().manual_seed(77)
+    sizes = [1, 7, 8, 9, 15, 4095, 4096, 4097, 65535, 70001]
+    PAD = 64
+
+    def guarded(n, dtype, fill):
+        store = torch.full((n + 2 * PAD,), fill, dtype=dtype, device="cuda")
+        return store, store[PAD:PAD + n]
+
+    def intact(store, n, fill):
+        return bool((store[:PAD] == fill).all()) and bool((store[PAD + n:] == fill).all())
+
+    stores, cols = {k: [] for k in "gpmvc"}, {k: [] for k in "gpmvc"}
+    fills = {"g": 3.0, "p": 5.0, "m": 7.0, "v": 9.0, "c": 11.0}
+    dts = {"g": torch.float16, "p": torch.float32, "m": torch.float32, "v": torch.float32, "c": torch.float16}
+    for n in sizes:
+        for k in "gpmvc":
+            s, view = guarded(n, dts[k], fills[k])
+            view.copy_((torch.randn(n, generator=gen) * 0.01).abs().to(dts[k]))
+            stores[k].append(s)
+            cols[k].append(view)
+    flag = _flag()
+    table = TensorTable([cols[k] for k in "gpmvc"])
+    ops.multi_tensor_check(TensorTable([cols["g"]]), 0, torch.float16, flag)
+    ops.fused_adam(table, torch.float16, torch.float32, torch.float16, [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, 1, 1, 1)])
+    ops.fused_sgd(TensorTable([cols["g"], cols["p"], cols["m"], cols["c"]]), torch.float16, torch.float32, torch.float16,
+                  [ops.SgdGroup(0.1, 0.9, 0.0, 1e-4, 1, 1, 0)])
+    ops.multi_tensor_scale(TensorTable([cols["g"], cols["v"]]), torch.float16, torch.float32, scale=0.5, dev_flag=flag)
+    ops.multi_tensor_axpby(TensorTable([cols["g"], cols["m"], cols["m"]]), torch.float16, torch.float32, torch.float32,
+                           1.0, 1.0, -1, flag)
+    for view in cols["g"]:
+        ops.bucket_epilogue(view, 0.5, flag)
+    out = [guarded(n, torch.float16, 13.0) for n in sizes]
+    for (s, view), g in zip(out, cols["g"]):
+        ops.peer_reduce_shard([g.data_ptr(), g.data_ptr()], view, 0, g.numel(), 0.5, flag)
+    torch.cuda.synchronize()
+    for i, n in enumerate(sizes):
+        for k in "gpmvc":
+            assert intact(stores[k][i], n, fills[k]), f"column {k}, tensor {i} (numel {n}): sentinel overwritten"
+        assert intact(out[i][0], n, 13.0), f"peer_reduce output {i}: sentinel overwritten"
