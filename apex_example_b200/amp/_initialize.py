@@ -207,6 +207,28 @@ def _initialize(models, optimizers, properties, num_losses=1, cast_model_outputs
     for i, optimizer in enumerate(optimizers):
         optimizers[i] = _process_optimizer(optimizer, properties)
 
+    if properties.master_weights:
+        # model.load_state_dict(fp32 checkpoint) would only reach the fp16 weights (rounded); hand the
+        # exact fp32 values to the masters as well, so a restored run continues bit-exactly
+        master_of = {}
+        for optimizer in optimizers:
+            for master, model_p in optimizer._amp_stash.model_of.items():
+                master_of[id(model_p)] = master
+
+        def _masters_from_checkpoint(module, state_dict, prefix, *unused):
+            with torch.no_grad():
+                for name, param in module._parameters.items():
+                    if param is None:
+                        continue
+                    master = master_of.get(id(param))
+                    src = state_dict.get(prefix + name)
+                    if master is not None and src is not None and src.shape == master.shape:
+                        master.copy_(src.to(device=master.device, dtype=torch.float32))
+
+        for model in models:
+            for module in model.modules():
+                module._register_load_state_dict_pre_hook(_masters_from_checkpoint, with_module=True)
+
     _amp_state.loss_scalers = []
     for idx in range(num_losses):
         scaler = LossScaler(properties.loss_scale, min_loss_scale=_amp_state.min_loss_scale,

@@ -463,11 +463,10 @@ def test_checkpoint_round_trip_continues_bit_exactly(which):
     model_c.load_state_dict(ckpt["model"])
     opt_c.load_state_dict(ckpt["opt"])
     amp.load_state_dict(ckpt["amp"])
-    # the masters are part of the optimizer state only implicitly: restore them from the saved fp32 weights
-    # exactly as apex users do (masters = the optimizer's params; here they are re-derived from the fp32 checkpoint)
-    with torch.no_grad():
-        for m_c, m_b in zip(amp.master_params(opt_c), amp.master_params(opt_b)):
-            m_c.copy_(m_b)
+    # model.load_state_dict() handed the checkpoint's exact fp32 values to the masters (pre-hook installed by
+    # amp.initialize): nothing else to restore
+    for m_c, m_b in zip(amp.master_params(opt_c), amp.master_params(opt_b)):
+        assert torch.equal(m_c.detach(), m_b.detach())
     _run_steps(model_c, opt_c, xs, 6, 10, overflow)
     torch.cuda.synchronize()
     for a, c in zip(ref, amp.master_params(opt_c)):
