@@ -139,15 +139,24 @@ def _patch_forward(model, input_caster, output_caster, autocast_dtype=None):
 
 
 class _O2StateDictHook:
-    """model.state_dict() returns fp32 copies of the fp16 weights (apex O2StateDictHook)."""
+    """model.state_dict() hands out fp32 weights so checkpoints do not depend on the opt_level (apex
+    O2StateDictHook).  apex casts the fp16 weights up, which drops the masters' extra bits; here a
+    parameter that has an fp32 master is saved AS its master, so a restored run continues exactly."""
 
-    def __init__(self, fn):
-        self.fn = fn
+    def __init__(self, master_of):
+        self.master_of = master_of          # id(model param) -> fp32 master, filled by _initialize
 
     def __call__(self, module, state_dict, prefix, local_metadata):
+        for name, param in module._parameters.items():
+            key = prefix + name
+            if param is None or key not in state_dict:
+                continue
+            master = self.master_of.get(id(param))
+            if master is not None:
+                state_dict[key] = master.detach().clone()
         for key in state_dict:
             param = state_dict[key]
-            if "Half" in param.type() or param.dtype in _HALF_TYPES:
+            if param.dtype in _HALF_TYPES:
                 state_dict[key] = param.to(torch.float32)
 
 
@@ -174,6 +183,7 @@ def _initialize(models, optimizers, properties, num_losses=1, cast_model_outputs
     else:
         raise TypeError("models must be either a single model or a list of models.")
 
+    master_of = {}                          # id(model param) -> fp32 master (O2), shared with the state_dict hooks
     check_models(models)
     if not getattr(_amp_state, "allow_incoming_model_not_fp32", False):
         check_params_fp32(models)
@@ -192,7 +202,7 @@ def _initialize(models, optimizers, properties, num_losses=1, cast_model_outputs
         if dtype in _HALF_TYPES:
             for model in models:
                 for module in model.modules():
-                    module._register_state_dict_hook(_O2StateDictHook(functools.partial(to_type, torch.float32)))
+                    module._register_state_dict_hook(_O2StateDictHook(master_of))
     elif cast_model_outputs is not None:
         output_caster = functools.partial(to_type, cast_model_outputs)
         for model in models:
@@ -210,7 +220,6 @@ def _initialize(models, optimizers, properties, num_losses=1, cast_model_outputs
     if properties.master_weights:
         # model.load_state_dict(fp32 checkpoint) would only reach the fp16 weights (rounded); hand the
         # exact fp32 values to the masters as well, so a restored run continues bit-exactly
-        master_of = {}
         for optimizer in optimizers:
             for master, model_p in optimizer._amp_stash.model_of.items():
                 master_of[id(model_p)] = master
