@@ -45,6 +45,7 @@ class PeerPull(ctypes.Structure):            # b200_peer_pull
                 ("world", c_int32), ("elem_size", c_int32), ("first_tile", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
 
 NOALLOC_TABLE_BYTES = 256 * 1024
+NORM_SCRATCH_BYTES = 16384
 
 
 class TableHeader(ctypes.Structure):         # b200_table_header
@@ -78,6 +79,9 @@ SIGNATURES = {
     "b200_multi_tensor_axpby": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, c_float, c_float,
                                           c_int32, c_void_p, c_void_p]),
     "b200_multi_tensor_check": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
+    "b200_multi_tensor_l2norm": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p, c_int64, c_void_p,
+                                           c_void_p]),
+    "b200_clip_scale": (c_int32, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "b200_fused_adam": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),
     "b200_fused_sgd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),

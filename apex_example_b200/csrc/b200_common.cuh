@@ -273,9 +273,9 @@ struct RowSlot {
     b200_table_row row;      // 64 B, filled by 4 x cp.async(16 B)
 };
 
-template <class Op, int kThreads, int kUnroll>
+template <class Op, int kThreads, int kUnroll, class Acc>
 __device__ __forceinline__ void walk_tiles(const void* table, const typename Op::Params& prm, int win, uint32_t rot,
-                                           bool& bad) {
+                                           Acc& bad) {
     __shared__ __align__(16) RowSlot s_slot[2];
     __shared__ uint32_t s_tile[2];
     const TableView tv = open_table(table);

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <type_traits>
 
 #include "b200_common.cuh"
 
@@ -82,43 +83,48 @@ static int after_launch(const char* name) {
 // ============================================================================================
 // generic tile kernel
 // ============================================================================================
+// per-thread accumulator carried through the walk: a bool ("saw inf/NaN") unless the Op declares its own
+template <class Op, class = void> struct AccOf { using type = bool; };
+template <class Op> struct AccOf<Op, std::void_t<typename Op::Acc>> { using type = typename Op::Acc; };
+
 template <class Op, int kThreads, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
 tile_kernel(const void* __restrict__ table, const __grid_constant__ typename Op::Params prm) {
     int win = 0;
     if (Op::prologue(prm, win)) return;
-    bool bad = false;
-    walk_tiles<Op, kThreads, kUnroll * Op::kUnrollMul>(table, prm, win, Op::rotation(prm), bad);
-    Op::finish(prm, bad);
+    typename AccOf<Op>::type acc{};
+    walk_tiles<Op, kThreads, kUnroll * Op::kUnrollMul>(table, prm, win, Op::rotation(prm), acc);
+    Op::finish(prm, acc);
 }
 
 template <class Op, int kThreads, int kUnroll>
 static int launch_one(const char* name, const void* dev_table, int64_t n_tiles, const typename Op::Params& prm,
-                      cudaStream_t st) {
+                      cudaStream_t st, unsigned max_grid) {
     auto kernel = tile_kernel<Op, kThreads, kUnroll>;
     static int occ[64];                       // per device; one static per instantiation
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
     if (occ[dev] == 0) occ[dev] = resident_ctas_per_sm(kernel, kThreads);
-    const unsigned grid = grid_for(n_tiles, occ[dev]);
+    unsigned grid = grid_for(n_tiles, occ[dev]);
+    if (max_grid && grid > max_grid) grid = max_grid;
     kernel<<<grid, kThreads, 0, st>>>(dev_table, prm);
     return after_launch(name);
 }
 
 template <class Op>
 static int launch_tiles(const char* name, const void* dev_table, int64_t n_tiles,
-                        const typename Op::Params& prm, void* stream) {
+                        const typename Op::Params& prm, void* stream, unsigned max_grid = 0) {
     if (n_tiles <= 0) return 0;
     if (dev_table == nullptr) return set_error(B200_EINVAL, "%s: dev_table is NULL", name);
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int threads = g_threads.load(), unroll = g_unroll.load();
     if (threads == 512) {
-        if (unroll == 1) return launch_one<Op, 512, 1>(name, dev_table, n_tiles, prm, st);
-        return launch_one<Op, 512, 2>(name, dev_table, n_tiles, prm, st);
+        if (unroll == 1) return launch_one<Op, 512, 1>(name, dev_table, n_tiles, prm, st, max_grid);
+        return launch_one<Op, 512, 2>(name, dev_table, n_tiles, prm, st, max_grid);
     }
-    if (unroll == 1) return launch_one<Op, 256, 1>(name, dev_table, n_tiles, prm, st);
-    return launch_one<Op, 256, 2>(name, dev_table, n_tiles, prm, st);
+    if (unroll == 1) return launch_one<Op, 256, 1>(name, dev_table, n_tiles, prm, st, max_grid);
+    return launch_one<Op, 256, 2>(name, dev_table, n_tiles, prm, st, max_grid);
 }
 
 // ============================================================================================
@@ -256,6 +262,107 @@ struct CheckOp {
     }
     static __device__ __forceinline__ void finish(const Params& p, bool bad) { raise_flag(p.flag, bad); }
 };
+
+// ============================================================================================
+// multi_tensor_l2norm fused with the overflow check (one read-only pass over the gradients)
+// ============================================================================================
+struct NormParams {
+    int32_t col;
+    int32_t* flag;          // may be NULL
+    float* scratch;         // [0] ticket (as uint32), [1] pad, [2 + b] partial sum of squares of block b
+    float* out;             // out[0] += sum of squares of this list (the caller zeroes it once per step)
+};
+
+struct NormAcc {
+    float ss;
+    bool bad;
+};
+
+template <int I>
+struct NormCheckOp {
+    using Params = NormParams;
+    using Acc = NormAcc;
+    static constexpr int kUnrollMul = 4;
+    struct Ctx { int32_t col; };
+    static __device__ __forceinline__ bool prologue(const Params&, int&) { return false; }
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row&, int, int64_t) { return Ctx{p.col}; }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], Acc& acc) {
+        Raw8<I> in[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) load8<I, true>(r.ptr[c.col], idx[u], in[u]);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec];
+            unpack8<I>(in[u], x);
+            float s = 0.0f;
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                acc.bad |= !is_finite(x[i]);
+                s = __fmaf_rn(x[i], x[i], s);
+            }
+            acc.ss += s;
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, Acc& acc) {
+        const float x = load1<I>(r.ptr[c.col], i);
+        acc.bad |= !is_finite(x);
+        acc.ss = __fmaf_rn(x, x, acc.ss);
+    }
+    // Deterministic for a given grid: block partials are written to scratch and summed in index order
+    // by the last block to arrive (ticket), never with floating-point atomics.
+    static __device__ __forceinline__ void finish(const Params& p, const Acc& acc) {
+        if (p.flag) raise_flag(p.flag, acc.bad);
+        __shared__ float s_warp[32];
+        __shared__ bool s_last;
+        float v = acc.ss;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+        if (lane == 0) s_warp[warp] = v;
+        __syncthreads();
+        if (warp == 0) {
+            float t = lane < n_warps ? s_warp[lane] : 0.0f;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == 0) {
+                p.scratch[2 + blockIdx.x] = t;
+                __threadfence();
+                const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(p.scratch), 1u);
+                s_last = ticket == gridDim.x - 1;
+            }
+        }
+        __syncthreads();
+        if (s_last && warp == 0) {
+            __threadfence();
+            float t = 0.0f;
+            for (unsigned b = lane; b < gridDim.x; b += 32) t += *(reinterpret_cast<volatile float*>(p.scratch) + 2 + b);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == 0) {
+                p.out[0] += t;
+                *reinterpret_cast<unsigned*>(p.scratch) = 0u;       // ready for the next launch
+            }
+        }
+    }
+};
+
+// clip coefficient on the device: scale_out = inv_scale * min(1, max_norm / (||g|| * inv_scale + 1e-6))
+// (torch.nn.utils.clip_grad_norm_'s rule), norm_out = ||g|| * inv_scale.  One thread.
+__global__ void clip_scale_kernel(float* sumsq, const float* dev_inv_scale, float inv_scale, float max_norm,
+                                  float* scale_out, float* norm_out) {
+    const float inv = dev_inv_scale ? *dev_inv_scale : inv_scale;
+    const float norm = __fmul_rn(__fsqrt_rn(*sumsq), inv);
+    *sumsq = 0.0f;                                   // consumed: the accumulator is ready for the next step
+    float coef = __fdiv_rn(max_norm, __fadd_rn(norm, 1e-6f));
+    if (coef > 1.0f) coef = 1.0f;
+    *scale_out = __fmul_rn(inv, coef);
+    if (norm_out) *norm_out = norm;
+}
 
 // ============================================================================================
 // fused unscale + Adam + master->model copy
@@ -797,6 +904,28 @@ static int to_pull(const b200_peer_pull* p, PeerPull& out, const char* name) {
     for (int r = 0; r < p->world; r++)
         if (p->bounds[r] > p->bounds[r + 1]) return set_error(B200_EINVAL, "%s: shard bounds must be non-decreasing", name);
     return 0;
+}
+
+int32_t b200_multi_tensor_l2norm(const void* dev_table, int64_t n_tiles, int32_t col, int32_t dtype, float* dev_sumsq,
+                                 void* dev_scratch, int64_t scratch_bytes, int32_t* dev_flag, void* stream) {
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "multi_tensor_l2norm: bad dtype");
+    if (col < 0 || col >= B200_MAX_DEPTH) return set_error(B200_EINVAL, "multi_tensor_l2norm: bad column");
+    if (!dev_sumsq || !dev_scratch) return set_error(B200_EINVAL, "multi_tensor_l2norm: NULL output or scratch");
+    if (scratch_bytes < B200_NORM_SCRATCH_BYTES)
+        return set_error(B200_ESIZE, "multi_tensor_l2norm: scratch must be at least %d bytes (zeroed once)", B200_NORM_SCRATCH_BYTES);
+    NormParams prm{col, dev_flag, static_cast<float*>(dev_scratch), dev_sumsq};
+    const unsigned cap = B200_NORM_SCRATCH_BYTES / 4 - 2;
+    B200_DISPATCH_DT(dtype, I, return launch_tiles<NormCheckOp<I>>("multi_tensor_l2norm", dev_table, n_tiles, prm, stream, cap))
+    return 0;
+}
+
+int32_t b200_clip_scale(float* dev_sumsq, const float* dev_inv_scale, float inv_scale, float max_norm, float* dev_scale_out,
+                        float* dev_norm_out, void* stream) {
+    if (!dev_sumsq || !dev_scale_out) return set_error(B200_EINVAL, "clip_scale: NULL argument");
+    if (!(max_norm > 0.0f)) return set_error(B200_EINVAL, "clip_scale: max_norm must be > 0");
+    clip_scale_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(dev_sumsq, dev_inv_scale, inv_scale, max_norm,
+                                                                     dev_scale_out, dev_norm_out);
+    return after_launch("clip_scale");
 }
 
 int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,

@@ -105,3 +105,26 @@ def multi_tensor_adam(chunk_size, noop_flag, tensor_lists, lr, beta1, beta2, eps
                         int(bool(bias_correction)), int(mode))
     ops.fused_adam(table_for(tensor_lists), tensor_lists[0][0].dtype, tensor_lists[1][0].dtype, cdt, [grp],
                    dev_found_inf=noop_flag)
+
+
+_NORM_SCRATCH = {}
+
+
+def multi_tensor_l2norm(chunk_size, noop_flag, tensor_lists, per_tensor=False):
+    """amp_C.multi_tensor_l2norm(chunk_size, noop_flag, [tensors], per_tensor) -> (norm, per_tensor_norms).
+    One read-only pass; the flag is raised on inf/NaN like apex's.  ``per_tensor=True`` (LAMB's
+    trust ratios) is outside this path's scope."""
+    if per_tensor:
+        raise RuntimeError("multi_tensor_l2norm(per_tensor=True) is not provided by libapex_b200")
+    if len(tensor_lists) != 1:
+        raise RuntimeError("multi_tensor_l2norm expects tensor_lists = [tensors]")
+    tensors = tensor_lists[0]
+    device = tensors[0].device if tensors else noop_flag.device
+    sumsq = torch.zeros(1, device=device)
+    if tensors:
+        _check_flag(noop_flag)
+        scratch = _NORM_SCRATCH.get(device)
+        if scratch is None:
+            scratch = _NORM_SCRATCH[device] = ops.new_norm_scratch(device)
+        ops.multi_tensor_l2norm(table_for(tensor_lists), 0, tensors[0].dtype, sumsq, scratch, noop_flag)
+    return sumsq.sqrt_(), torch.empty(0, device=device)

@@ -163,3 +163,21 @@ def set_launch_config(ctas_per_sm: int = 0, threads: int = 256, unroll: int = 2)
 
 def launch_count() -> int:
     return int(_lib.load().b200_launch_count())
+
+
+def multi_tensor_l2norm(table: TensorTable, col: int, dtype, sumsq: torch.Tensor, scratch: torch.Tensor, dev_flag=None):
+    """Adds the list's sum of squares to ``sumsq`` (fp32[1]) in one read-only pass; also the overflow check."""
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_multi_tensor_l2norm(table.ptr, table.n_tiles, col, dtype_code(dtype), sumsq.data_ptr(),
+                                                    scratch.data_ptr(), scratch.numel() * scratch.element_size(),
+                                                    _addr(dev_flag), _stream()), "multi_tensor_l2norm")
+
+
+def new_norm_scratch(device) -> torch.Tensor:
+    return torch.zeros(_lib.NORM_SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
+
+
+def clip_scale(sumsq: torch.Tensor, max_norm: float, scale_out: torch.Tensor, norm_out=None, inv_scale: float = 1.0,
+               dev_inv_scale=None):
+    _lib.check(_lib.load().b200_clip_scale(sumsq.data_ptr(), _addr(dev_inv_scale), inv_scale, float(max_norm),
+                                           scale_out.data_ptr(), _addr(norm_out), _stream()), "clip_scale")

@@ -49,7 +49,9 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         self._tables = {}               # launch-set key -> TensorTable
         self._counter = None            # ops.StepCounter once device-side skipping is in play
         self._step_offsets = {}         # group index -> offset of the group's step from the counter
-        self._plan = None               # cached launch plan (see _replay_plan)
+        self._plan = None               # cached launch plan (see _plan_is_current)
+        self._clip = None               # pending (unscale x clip) factor from clip_grad_norm_
+        self._norm_buf = None
 
     # ---- subclass interface ----------------------------------------------------------------------
     def _state_columns(self, p, group):
@@ -130,7 +132,11 @@ class FusedOptimizerBase(torch.optim.Optimizer):
             super().zero_grad(set_to_none=False)
 
     # ---- the step ------------------------------------------------------------------------------------
-    def _replay_plan(self):
+    def _grads_scaled_now(self):
+        st = self._amp_stash
+        return bool(st is not None and st.grads_scaled)
+
+    def _plan_is_current(self):
         """Steady-state fast path.  When every gradient is the very tensor object the plan was built
         from (gradients accumulate in place, or live in DDP buckets) and no parameter storage moved,
         the cached tables are still right and the step is launched without touching the parameters
@@ -139,10 +145,9 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         plan = self._plan
         if plan is None:
             return False
-        holders, grads, n_groups, device = plan["holders"], plan["grads"], plan["n_groups"], plan["device"]
-        if n_groups != len(self.param_groups) or plan["grads_scaled"] != self._grads_scaled_now():
+        if plan["n_groups"] != len(self.param_groups) or plan["grads_scaled"] != self._grads_scaled_now():
             return False
-        if not all(map(operator.is_, map(_GRAD_OF, holders), grads)):
+        if not all(map(operator.is_, map(_GRAD_OF, plan["holders"]), plan["grads"])):
             return False
         if plan["n_params"] != sum(len(g["params"]) for g in self.param_groups):
             return False
@@ -150,25 +155,11 @@ class FusedOptimizerBase(torch.optim.Optimizer):
         if plan["age"] % 64 == 0:          # storages that moved without the grad object changing (model.to(), .data = ...)
             if plan["ptrs"] != tuple(t.data_ptr() for t in plan["watch"]):
                 return False
-        inv_scale, dev_inv, dev_found = self._scale_args()
-        steps, sync = self._next_steps(device, dev_found is not None)
-        first = True
-        with torch.cuda.device(device):
-            for key, table, gids in plan["launches"]:
-                this_sync = None
-                if sync is not None:
-                    this_sync = sync if first else ops.StepSync(sync.dev_counters, sync.mirror, sync.known_skips, 1)
-                self._launch(table, key, gids, steps, (inv_scale, dev_inv, dev_found), this_sync)
-                first = False
         return True
 
-    def _grads_scaled_now(self):
-        st = self._amp_stash
-        return bool(st is not None and st.grads_scaled)
-
-    def _fused_step(self):
-        if self._replay_plan():
-            return
+    def _ensure_plan(self):
+        if self._plan_is_current():
+            return self._plan
         self._plan = None
         sets = {}
         device = None
@@ -215,29 +206,63 @@ class FusedOptimizerBase(torch.optim.Optimizer):
                 s["grp"].append(gi % _lib.MAX_GROUPS)
                 s["gids"][gi % _lib.MAX_GROUPS] = gi
         if not sets:
-            return
-        inv_scale, dev_inv, dev_found = self._scale_args()
-        steps, sync = self._next_steps(device, dev_found is not None)
-        first = True
+            return None
         launches = []
-        with torch.cuda.device(device):
-            for key, s in sets.items():
-                columns = [s["g"], s["p"]] + s["state"] + ([s["c"]] if s["c"] else [])
-                # m / v / momentum are owned by this object (stable); grads, params and model copies
-                # can be re-allocated behind our back, so their addresses form the cache key
-                sig = (tuple(t.data_ptr() for t in s["g"]), tuple(t.data_ptr() for t in s["p"]),
-                       tuple(t.data_ptr() for t in s["c"]))
-                table = self._tables.get(key)
-                if table is None or table.signature != sig:
-                    table = TensorTable(columns, groups=s["grp"], signature=sig)
-                    self._tables[key] = table
-                this_sync = None
-                if sync is not None:
-                    this_sync = sync if first else ops.StepSync(sync.dev_counters, sync.mirror, sync.known_skips, 1)
-                self._launch(table, key, s["gids"], steps, (inv_scale, dev_inv, dev_found), this_sync)
-                launches.append((key, table, s["gids"]))
-                first = False
+        for key, s in sets.items():
+            columns = [s["g"], s["p"]] + s["state"] + ([s["c"]] if s["c"] else [])
+            # m / v / momentum are owned by this object (stable); grads, params and model copies
+            # can be re-allocated behind our back, so their addresses form the cache key
+            sig = (tuple(t.data_ptr() for t in s["g"]), tuple(t.data_ptr() for t in s["p"]),
+                   tuple(t.data_ptr() for t in s["c"]))
+            table = self._tables.get(key)
+            if table is None or table.signature != sig:
+                table = TensorTable(columns, groups=s["grp"], signature=sig)
+                self._tables[key] = table
+            launches.append((key, table, s["gids"]))
         self._plan = {"holders": holders, "grads": grad_objs, "launches": launches, "device": device,
                       "n_groups": len(self.param_groups), "n_params": sum(len(g["params"]) for g in self.param_groups),
                       "grads_scaled": self._grads_scaled_now(), "watch": watch,
                       "ptrs": tuple(t.data_ptr() for t in watch), "age": 0}
+        return self._plan
+
+    def _fused_step(self):
+        plan = self._ensure_plan()
+        if plan is None:
+            return
+        device = plan["device"]
+        inv_scale, dev_inv, dev_found = self._scale_args()
+        if self._clip is not None:                      # clip_grad_norm_ left a combined (unscale x clip) factor
+            dev_inv = self._clip["scale"]
+            self._clip = None
+        steps, sync = self._next_steps(device, dev_found is not None)
+        first = True
+        with torch.cuda.device(device):
+            for key, table, gids in plan["launches"]:
+                this_sync = None
+                if sync is not None:
+                    this_sync = sync if first else ops.StepSync(sync.dev_counters, sync.mirror, sync.known_skips, 1)
+                self._launch(table, key, gids, steps, (inv_scale, dev_inv, dev_found), this_sync)
+                first = False
+
+    # ---- gradient clipping fused into the step ---------------------------------------
+    def clip_grad_norm_(self, max_norm: float):
+        """Clip the global gradient norm like ``torch.nn.utils.clip_grad_norm_(amp.master_params(opt), max_norm)``
+        — without materialising fp32 master gradients and without a scaling pass: ONE read-only pass
+        over the (still loss-scaled) gradients computes the norm on the device, and the clip
+        coefficient is folded into the factor the next ``step()`` kernel multiplies every gradient by.
+        Returns the total (unscaled) norm as a 0-d device tensor; nothing synchronises."""
+        plan = self._ensure_plan()
+        if plan is None:
+            return torch.zeros((), device="cuda")
+        device = plan["device"]
+        if self._norm_buf is None or self._norm_buf["sumsq"].device != device:
+            self._norm_buf = {"sumsq": torch.zeros(1, device=device), "scratch": ops.new_norm_scratch(device),
+                              "scale": torch.ones(1, device=device), "norm": torch.zeros(1, device=device)}
+        nb = self._norm_buf
+        inv_scale, dev_inv, _ = self._scale_args()
+        with torch.cuda.device(device):
+            for key, table, _gids in plan["launches"]:
+                ops.multi_tensor_l2norm(table, 0, key[0], nb["sumsq"], nb["scratch"])
+            ops.clip_scale(nb["sumsq"], max_norm, nb["scale"], nb["norm"], inv_scale=inv_scale, dev_inv_scale=dev_inv)
+        self._clip = {"scale": nb["scale"], "max_norm": float(max_norm)}
+        return nb["norm"][0]

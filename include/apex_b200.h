@@ -172,6 +172,24 @@ int32_t b200_multi_tensor_check(const void* dev_table, int64_t n_tiles,
                                 int32_t col, int32_t dtype,
                                 int32_t* dev_flag, void* stream);
 
+/* amp_C.multi_tensor_l2norm fused with the overflow check: ONE read-only
+ * pass over column `col` adds the list's sum of squares to *dev_sumsq and raises *dev_flag on
+ * inf/NaN.  Block partials go through `dev_scratch` (>= B200_NORM_SCRATCH_BYTES, zeroed once by
+ * the caller) and are summed in block order by the last block to finish — deterministic for a given
+ * grid, no floating-point atomics.  Several lists (dtypes) accumulate into the same *dev_sumsq.
+ *
+ * b200_clip_scale turns the accumulated sum of squares into the factor the step kernels take as
+ * `dev_inv_scale`:  norm = sqrt(sumsq) * inv;  scale_out = inv * min(1, max_norm / (norm + 1e-6))
+ * (torch.nn.utils.clip_grad_norm_'s rule), with inv = dev_inv_scale ? *dev_inv_scale : inv_scale.
+ * It zeroes *dev_sumsq for the next step.  Clipping therefore costs no extra pass over the
+ * gradients and no fp32 master gradients: the unscale, the clip and the update share one kernel. */
+#define B200_NORM_SCRATCH_BYTES 16384
+int32_t b200_multi_tensor_l2norm(const void* dev_table, int64_t n_tiles, int32_t col, int32_t dtype,
+                                 float* dev_sumsq, void* dev_scratch, int64_t scratch_bytes,
+                                 int32_t* dev_flag, void* stream);
+int32_t b200_clip_scale(float* dev_sumsq, const float* dev_inv_scale, float inv_scale, float max_norm,
+                        float* dev_scale_out, float* dev_norm_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * S2 — fused optimizer step: unscale + Adam/SGD + master->model cast in ONE pass.
  * Replaces the three passes apex makes per step: multi_tensor_scale

@@ -512,3 +512,63 @@ def test_gradient_accumulation_with_delay_unscale(which):
         # gradient (2^-11 relative), which Adam/SGD turn into at most lr * 2^-10 here
         torch.testing.assert_close(a.detach(), b.detach(), rtol=0, atol=2e-5)
     assert any(not torch.equal(a.detach(), p.detach().float()) or True for a, p in zip(amp.master_params(opt_a), model_a.parameters()))
+
+
+# ------------------------------------------------------------------------------------------------
+# l2norm + gradient clipping, fused
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dt", [torch.float16, torch.bfloat16, torch.float32])
+def test_multi_tensor_l2norm_matches_torch(dt):
+    import amp_C
+    from apex.multi_tensor_apply import multi_tensor_applier
+    gen = torch.Generator().manual_seed(3)
+    tensors = [(torch.randn(n, generator=gen) * 3).to(dt).cuda() for n in (1, 7, 4096, 70001, 123457, 9)]
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    norm, _ = multi_tensor_applier(amp_C.multi_tensor_l2norm, flag, [tensors], False)
+    want = torch.linalg.vector_norm(torch.cat([t.double() for t in tensors]))
+    # fp32 accumulation in a fixed tree vs an fp64 reference: 1e-6 relative
+    assert abs(float(norm) - float(want)) <= 1e-6 * float(want) and int(flag.item()) == 0
+    again, _ = multi_tensor_applier(amp_C.multi_tensor_l2norm, flag, [tensors], False)
+    assert float(again) == float(norm)                      # deterministic: ordered partial sums, no float atomics
+    tensors[3][-1] = float("inf")
+    multi_tensor_applier(amp_C.multi_tensor_l2norm, flag, [tensors], False)
+    assert int(flag.item()) == 1
+
+
+@pytest.mark.parametrize("max_norm", [0.05, 1e6])
+def test_fused_clip_grad_norm_matches_torch_clip_on_master_grads(max_norm):
+    """opt.clip_grad_norm_(max_norm) + step() == clip_grad_norm_(amp.master_params(opt), max_norm) + step()."""
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    from apex_example_b200.amp._amp_state import _amp_state
+    torch.manual_seed(12)
+    x = torch.randn(32, 32, device="cuda")
+
+    def run(fused_clip):
+        _amp_state.reset()
+        model = _mlp(44)
+        opt = FusedAdam(model.parameters(), lr=1e-2, weight_decay=0.01)
+        model, opt = amp.initialize(model, opt, opt_level="O2", loss_scale=4096.0, verbosity=0)
+        norms = []
+        for _ in range(3):
+            loss = model(x).float().pow(2).mean()
+            opt.zero_grad()
+            with amp.scale_loss(loss, opt) as scaled:
+                scaled.backward()
+            if fused_clip:
+                norms.append(float(opt.clip_grad_norm_(max_norm)))
+            else:
+                norms.append(float(torch.nn.utils.clip_grad_norm_(list(amp.master_params(opt)), max_norm)))
+            opt.step()
+        torch.cuda.synchronize()
+        return [m.detach().clone() for m in amp.master_params(opt)], norms
+
+    a, na = run(True)
+    b, nb = run(False)
+    for x_, y_ in zip(na, nb):
+        assert abs(x_ - y_) <= 1e-5 * abs(y_)
+    if max_norm < 1:
+        assert na[0] > max_norm                          # the clip is actually active
+    for p, q in zip(a, b):
+        # same gradients, same clip rule; the fused path multiplies by (inv_scale*coef) once instead of twice
+        torch.testing.assert_close(p, q, rtol=0, atol=2e-6)
