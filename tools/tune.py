@@ -98,6 +98,10 @@ def main():
         print(f"peer_reduce_shard emulated locally, world {world}: shard {b[1]-b[0]} elems {med*1e3:.1f}us "
               f"{(world+1)*2*(b[1]-b[0])/med/1e6:.0f}GB/s (HBM bytes)")
         del red, out
+    tn = TensorTable([g])
+    sumsq, scratch = torch.zeros(1, device=dev), ops.new_norm_scratch(dev)
+    med, best = timeit(lambda: ops.multi_tensor_l2norm(tn, 0, torch.float16, sumsq, scratch, flag))
+    print(f"l2norm+check (2B/elem): {med*1e3:.1f}us {2*n/med/1e6:.0f}GB/s")
     med, best = timeit(lambda: ops.bucket_epilogue(flat, 0.125, flag))
     print(f"bucket_epilogue rw (4B/elem): {med*1e3:.1f}us {4*n/med/1e6:.0f}GB/s")
     med, best = timeit(lambda: ops.bucket_epilogue(flat, 1.0, flag))
