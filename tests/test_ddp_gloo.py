@@ -120,6 +120,33 @@ def test_ddp_two_ranks_gloo(kwargs, expect_buckets):
         assert all(s >= kwargs["message_size"] for s in sizes[:-1])
 
 
+def _worker_options(rank, world, port):
+    _init(rank, world, port)
+    from apex_example_b200.parallel import DistributedDataParallel
+    model = _model(5)
+    params = list(model.parameters())
+    # a bucket closes at each trigger parameter (reverse order: [4,120] | [30,1500,50] | [1000])
+    ddp = DistributedDataParallel(model, allreduce_trigger_params=[params[4], params[1]], retain_allreduce_buffers=True,
+                                  _bucket_ops=OracleBucketOps())
+    assert [sum(p.numel() for p in b.params) for b in ddp.buckets] == [124, 1580, 1000]
+    assert len(ddp.allreduce_buffers) == 3 and all(buf is b.flat for buf, b in zip(ddp.allreduce_buffers, ddp.buckets))
+    x = torch.randn(8, 20, generator=torch.Generator().manual_seed(rank))
+    ddp(x).pow(2).sum().backward()
+    flat = torch.cat([b.flat for b in ddp.buckets])
+    lo, hi = flat.clone(), flat.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    assert torch.equal(lo, hi)                              # the retained buffers hold the same mean on every rank
+    with pytest.raises(ValueError, match="delay_allreduce"):
+        DistributedDataParallel(_model(5), allreduce_trigger_params=[params[0]], delay_allreduce=True,
+                                _bucket_ops=OracleBucketOps())
+    dist.destroy_process_group()
+
+
+def test_ddp_trigger_params_and_retained_buffers():
+    mp.spawn(_worker_options, args=(2, _free_port()), nprocs=2, join=True)
+
+
 def _worker_mismatch(rank, world, port):
     _init(rank, world, port)
     from apex_example_b200.parallel import DistributedDataParallel

@@ -572,3 +572,26 @@ def test_fused_clip_grad_norm_matches_torch_clip_on_master_grads(max_norm):
     for p, q in zip(a, b):
         # same gradients, same clip rule; the fused path multiplies by (inv_scale*coef) once instead of twice
         torch.testing.assert_close(p, q, rtol=0, atol=2e-6)
+
+
+def test_bf16_o2_training_runs_with_bf16_model_and_fp32_masters():
+    """north_star's addition to apex: cast_model_type=torch.bfloat16 (static scale 1 is the usual choice)."""
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    model = _mlp(55)
+    opt = FusedAdam(model.parameters(), lr=1e-2)
+    model, opt = amp.initialize(model, opt, opt_level="O2", cast_model_type=torch.bfloat16, loss_scale=1.0, verbosity=0)
+    assert all(p.dtype == torch.bfloat16 for p in model.parameters())
+    x = torch.randn(32, 32, device="cuda")
+    first = None
+    for _ in range(20):
+        loss = model(x).float().pow(2).mean()
+        first = first if first is not None else float(loss)
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+    torch.cuda.synchronize()
+    assert float(loss) < first
+    for master, model_p in opt._amp_stash.model_of.items():
+        assert master.dtype == torch.float32 and torch.equal(model_p, master.bfloat16())
