@@ -544,8 +544,26 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
     dummy = torch.zeros((), device=dev)
     scaler = amp._amp_state.loss_scalers[0]
 
+    # A caller whose gradients live in host memory overlaps the transfer of step k+1 with the work of
+    # step k: the H2D copy runs on its own stream into a staging buffer, the step's stream waits for it,
+    # moves it into the gradient buffer (device-to-device) and steps.  Every step still pays one full
+    # H2D of its gradients and one D2H read of its result inside the timed region.
+    staging = torch.empty(n, dtype=torch.float16, device=dev)
+    copy_stream = torch.cuda.Stream(device=dev)
+    arrived, consumed = torch.cuda.Event(), torch.cuda.Event()
+
+    def upload():
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed)                   # staging may be overwritten only after the D2D read it
+            staging.copy_(host_g, non_blocking=True)           # H2D: the NEXT step's gradients
+            arrived.record(copy_stream)
+
     def one():
-        dev_g.copy_(host_g, non_blocking=True)                 # H2D: this step's gradients
+        main = torch.cuda.current_stream()
+        main.wait_event(arrived)
+        dev_g.copy_(staging, non_blocking=True)
+        consumed.record(main)
+        upload()                                               # overlaps with everything below
         if world > 1:
             dist.all_reduce(dev_g)
             dev_g.mul_(1.0 / world)
@@ -554,6 +572,8 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
         opt.step()
         return scaler.loss_scale()                             # D2H: the step's result (scale / skip state)
 
+    consumed.record(torch.cuda.current_stream())
+    upload()
     for _ in range(warmup):
         one()
     barrier()
@@ -570,7 +590,9 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
         ms = float(t.item())
     return {"value": BYTES_PER_PARAM * n * world / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms,
             "h2d_bytes_per_step": n * 2, "d2h_bytes_per_step": 32, "steps": steps,
-            "api": "apex.amp.scale_loss + apex.optimizers.FusedAdam.step (O2)"}
+            "api": "apex.amp.scale_loss + apex.optimizers.FusedAdam.step (O2)",
+            "note": "bound by the host link: 248.9 MB of fp16 gradients per step over PCIe, uploaded on a side stream "
+                    "while the previous step runs"}
 
 
 if __name__ == "__main__":
