@@ -10,11 +10,15 @@ Workload (BASELINE.json configs[1]): the 148-tensor / 1
 GPT-2-small parameter list at amp O2 — fp16 gradients carrying the loss scale, fp32 master / m / v,
 fp16 model copy.  One *step* = everything between backward and the next forward:
   N = 1 : overflow check over the gradients -> loss-scaler update -> fused unscale+AdamW+copy
-  N > 1 : per gradient bucket NCCL all-reduce + epilogue (x 1/N and overflow check) -> loss-scaler
-          update -> fused unscale+AdamW+copy           (weak scaling: every rank owns a full replica)
+  N > 1 : gradient mean across ranks -> loss-scaler update -> fused unscale+AdamW+copy
+          (weak scaling: every rank owns a full replica).  The mean runs over NVLink peer memory by
+          default (--collective peer: one reduce-scatter+mean+check kernel, then the optimizer
+          kernel pulls each tile's reduced gradient from its owner); --collective nccl selects
+          ncclAllReduce per 10M-element bucket + the epilogue kernel.
 `value` = 28 B/param x params x ranks / step time, inputs resident in HBM.  `e2e` = the same step
 through the public API (apex.amp + apex.optimizers.FusedAdam) with the step's gradients copied in
-from pinned host memory and the scaler state read back, every step.
+from pinned host memory and the scaler state read back, every step.  `train` = GPT-2 medium
+samples/s through amp O2 + FusedAdam + apex DistributedDataParallel (the metric's second half).
 """
 from __future__ import annotations
 
