@@ -40,6 +40,14 @@ STEP_WINDOW = 4
 MAX_PEERS = 8
 
 
+class PeerSync(ctypes.Structure):            # b200_peer_sync
+    _fields_ = [("pads", ctypes.POINTER(c_void_p)), ("world", c_int32), ("rank", c_int32), ("epoch", c_int32),
+                ("reserved", c_int32)]
+
+
+SIGNAL_PAD_BYTES = 128
+
+
 class PeerPull(ctypes.Structure):            # b200_peer_pull
     _fields_ = [("local_base", c_void_p), ("bounds", c_int64 * (MAX_PEERS + 1)), ("delta", c_int64 * MAX_PEERS),
                 ("world", c_int32), ("elem_size", c_int32), ("first_tile", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
@@ -91,7 +99,8 @@ SIGNATURES = {
     "b200_peer_close": (c_int32, [c_void_p]),
     "b200_peer_free": (c_int32, [c_void_p]),
     "b200_peer_reduce_shard": (c_int32, [ctypes.POINTER(c_void_p), c_int32, c_void_p, c_int64, c_int64, c_int32, c_float,
-                                         c_void_p, c_void_p]),
+                                         c_void_p, ctypes.POINTER(PeerSync), c_void_p]),
+    "b200_peer_wait_flags": (c_int32, [ctypes.POINTER(PeerSync), c_void_p, c_void_p]),
     "b200_fused_adam_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
                                        c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                        ctypes.POINTER(PeerPull), c_void_p]),

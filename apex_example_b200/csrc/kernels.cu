@@ -638,14 +638,53 @@ __device__ __forceinline__ float peer_mean(const float (&x)[kWorld], int world, 
 // kWorld = compile-time upper bound on the rank count (2, 4 or 8): the loads of every rank and of
 // kU groups are issued before the first use, so a thread keeps kWorld*kU 128/256-bit requests in
 // flight — NVLink round trips are 2-3x an HBM access, and this kernel is bound by them.
+// Cross-GPU hand-shake through signal pads in peer memory (b200_peer_sync).  Every rank owns one
+// pad; peers write into it with system-scope release stores and the owner polls it with acquire
+// loads.  Epochs only grow, so nothing has to be cleared between steps.
+struct PeerSync {
+    b200_peer_signal_pad* pad[B200_MAX_PEERS];      // pad[r]: rank r's pad as addressable from this GPU; NULL = no sync
+    int world, rank, epoch;
+};
+
+__device__ __forceinline__ void st_release_sys(int32_t* p, int32_t v) {
+    asm volatile("st.release.sys.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
+    int32_t v;
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Spin until *p >= want (as seen with acquire/system scope).  Bounded: after ~4e9 cycles (seconds) the
+// pad's error word is set and the wait gives up, so a missing peer shows up as an error, not a hung GPU.
+__device__ __forceinline__ void wait_at_least(const int32_t* p, int32_t want, int32_t* error) {
+    const long long t0 = clock64();
+    while (ld_acquire_sys(p) < want) {
+        __nanosleep(64);
+        if (clock64() - t0 > 4000000000ll) {
+            *error = 1;
+            break;
+        }
+    }
+}
+
 template <int DT, int kThreads, int kWorld>
 __global__ void __launch_bounds__(kThreads)
 peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __restrict__ reduced, int64_t begin,
-                   int64_t end, float factor, int32_t* flag) {
+                   int64_t end, float factor, int32_t* flag, const __grid_constant__ PeerSync sync) {
     using T = typename Elem<DT>::type;
     constexpr int kU = (DT == B200_F32 ? 4 : 8) / kWorld > 0 ? (DT == B200_F32 ? 4 : 8) / kWorld : 1;
     bool bad = false;
     T* out = reinterpret_cast<T*>(reduced);
+    const bool synced = sync.pad[0] != nullptr;
+    if (synced) {
+        // head: tell every rank "my gradients of this epoch are in place (and I am done with last epoch's
+        // reduced buffers)", then wait until every rank has said so before reading anybody's gradients
+        b200_peer_signal_pad* mine = sync.pad[sync.rank];
+        if (blockIdx.x == 0 && threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->ready[sync.rank], sync.epoch);
+        if (threadIdx.x < sync.world) wait_at_least(&mine->ready[threadIdx.x], sync.epoch, &mine->error);
+        __syncthreads();
+    }
     const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
     // every buffer starts 32-byte aligned, so element offsets that are multiples of 8 are vector-safe
@@ -703,7 +742,45 @@ peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __res
         bad |= !is_finite(round_through<DT>(v));
         store1<DT>(out, tail0 + gtid, v);
     }
-    if (flag) raise_flag(flag, bad);
+    if (!synced) {
+        if (flag) raise_flag(flag, bad);
+        return;
+    }
+    // tail: the last block to finish publishes "my shard of this epoch is written" together with this
+    // rank's overflow bit to every rank's pad; b200_peer_wait_flags (next on the stream) collects them
+    b200_peer_signal_pad* mine = sync.pad[sync.rank];
+    raise_flag(&mine->local_flag, bad);
+    __shared__ bool s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        s_last = atomicAdd(reinterpret_cast<unsigned*>(&mine->ticket), 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence_system();
+        const int32_t bit = *reinterpret_cast<volatile int32_t*>(&mine->local_flag) != 0 ? 1 : 0;
+        if (threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->done[sync.rank], (sync.epoch << 1) | bit);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mine->local_flag = 0;
+            mine->ticket = 0;
+        }
+    }
+}
+
+// Waits until every rank has published its shard of `epoch`, then ORs the ranks' overflow bits into *flag.
+__global__ void peer_wait_flags_kernel(const __grid_constant__ PeerSync sync, int32_t* flag) {
+    b200_peer_signal_pad* mine = sync.pad[sync.rank];
+    __shared__ int s_any;
+    if (threadIdx.x == 0) s_any = 0;
+    __syncthreads();
+    if (threadIdx.x < sync.world) {
+        wait_at_least(&mine->done[threadIdx.x], sync.epoch << 1, &mine->error);
+        if (ld_acquire_sys(&mine->done[threadIdx.x]) & 1) atomicOr(&s_any, 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && s_any && flag) *flag = 1;
 }
 
 // ============================================================================================
@@ -1056,14 +1133,41 @@ int32_t b200_peer_free(void* dev_ptr) {
 // ------------------------------------------------------------------------------------------------
 // b200_peer_reduce_shard: reduce-scatter + mean + overflow check over NVLink peer memory.
 // ------------------------------------------------------------------------------------------------
+static int to_peer_sync(const b200_peer_sync* s, PeerSync& out, const char* name) {
+    memset(&out, 0, sizeof(out));
+    if (!s) return 0;
+    if (s->world < 1 || s->world > B200_MAX_PEERS || s->rank < 0 || s->rank >= s->world || !s->pads)
+        return set_error(B200_EINVAL, "%s: bad b200_peer_sync (world %d, rank %d)", name, s->world, s->rank);
+    if (s->epoch < 1 || s->epoch >= (1 << 30)) return set_error(B200_EINVAL, "%s: epoch must be in [1, 2^30)", name);
+    for (int r = 0; r < s->world; r++) {
+        if (!s->pads[r]) return set_error(B200_EINVAL, "%s: signal pad %d is NULL", name, r);
+        out.pad[r] = s->pads[r];
+    }
+    out.world = s->world;
+    out.rank = s->rank;
+    out.epoch = s->epoch;
+    return 0;
+}
+
+int32_t b200_peer_wait_flags(const b200_peer_sync* sync, int32_t* dev_flag, void* stream) {
+    if (!sync) return set_error(B200_EINVAL, "peer_wait_flags: sync is NULL");
+    PeerSync ps;
+    if (int rc = to_peer_sync(sync, ps, "peer_wait_flags")) return rc;
+    peer_wait_flags_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(ps, dev_flag);
+    return after_launch("peer_wait_flags");
+}
+
 int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced, int64_t begin, int64_t end,
-                               int32_t dtype, float factor, int32_t* dev_flag, void* stream) {
+                               int32_t dtype, float factor, int32_t* dev_flag, const b200_peer_sync* sync, void* stream) {
+    PeerSync ps;
+    if (int rc = to_peer_sync(sync, ps, "peer_reduce_shard")) return rc;
+    if (sync && sync->world != world) return set_error(B200_EINVAL, "peer_reduce_shard: sync->world != world");
     if (world < 1 || world > B200_MAX_PEERS) return set_error(B200_EINVAL, "peer_reduce_shard: world must be 1..%d", B200_MAX_PEERS);
     if (!peer_bufs || !reduced) return set_error(B200_EINVAL, "peer_reduce_shard: NULL buffer");
     if (begin < 0 || end < begin) return set_error(B200_EINVAL, "peer_reduce_shard: bad shard [%lld, %lld)",
                                                    static_cast<long long>(begin), static_cast<long long>(end));
     if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "peer_reduce_shard: bad dtype");
-    if (end == begin) return 0;
+    if (end == begin && !sync) return 0;              // with sync even an empty shard must take part in the hand-shake
     PeerBufs pb;
     for (int r = 0; r < B200_MAX_PEERS; r++) pb.p[r] = r < world ? peer_bufs[r] : nullptr;
     for (int r = 0; r < world; r++)
@@ -1080,7 +1184,7 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                                  \
         if (blocks > want) blocks = want;                                                                         \
         if (blocks < 1) blocks = 1;                                                                               \
-        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag); \
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag, ps); \
     }
     B200_DISPATCH_DT(dtype, DT, {
         if (world <= 2) B200_LAUNCH_REDUCE(2)

@@ -80,13 +80,27 @@ def fused_sgd(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: S
 PeerPull = _lib.PeerPull
 
 
-def peer_reduce_shard(peer_ptrs, reduced: torch.Tensor, begin: int, end: int, factor: float, dev_flag=None):
+def peer_reduce_shard(peer_ptrs, reduced: torch.Tensor, begin: int, end: int, factor: float, dev_flag=None, sync=None):
     """Reduce-scatter + mean + overflow check for this rank's shard: peer_ptrs[r] is rank r's flat
-    gradient buffer as addressable from this process (device address, int)."""
+    gradient buffer as addressable from this process (device address, int).  ``sync`` (a PeerSync)
+    adds the in-kernel hand-shake; the flag is then delivered by :func:`peer_wait_flags`."""
     arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
     _lib.check(_lib.load().b200_peer_reduce_shard(arr, len(peer_ptrs), reduced.data_ptr(), begin, end,
-                                                  dtype_code(reduced.dtype), factor, _addr(dev_flag), _stream()),
+                                                  dtype_code(reduced.dtype), factor, _addr(dev_flag),
+                                                  ctypes.byref(sync) if sync is not None else None, _stream()),
                "peer_reduce_shard")
+
+
+def peer_wait_flags(sync, dev_flag):
+    _lib.check(_lib.load().b200_peer_wait_flags(ctypes.byref(sync), _addr(dev_flag), _stream()), "peer_wait_flags")
+
+
+def make_peer_sync(pad_ptrs, rank: int, epoch: int):
+    """b200_peer_sync for this step; keeps the pointer array alive on the returned struct."""
+    arr = (ctypes.c_void_p * len(pad_ptrs))(*pad_ptrs)
+    ps = _lib.PeerSync(ctypes.cast(arr, ctypes.POINTER(ctypes.c_void_p)), len(pad_ptrs), rank, epoch, 0)
+    ps._keep = arr
+    return ps
 
 
 def make_peer_pull(local_base_ptr: int, bounds, reduced_ptrs, elem_size: int, first_tile: int = 0) -> "PeerPull":

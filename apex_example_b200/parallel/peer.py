@@ -82,12 +82,45 @@ class PeerBuffers:
                     row.append(ptr.value)
                 self._ptrs[n] = row
         self.local = {n: _wrap(self._own[n], numel, dtype, self.device) for n in self.names}
+        self.signal_ptrs = None
         self._bar = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._closed = False
         dist.barrier(group=group)
 
     def ptrs(self, name):
         return list(self._ptrs[name])
+
+    def signal_pads(self):
+        """Allocate (once) the 128-byte signal pad of every rank and return their addresses as seen from
+        this process (b200_peer_signal_pad, zero-initialised by the allocator)."""
+        if self.signal_ptrs is None:
+            lib = _lib.load()
+            with torch.cuda.device(self.device):
+                ptr = ctypes.c_void_p()
+                h = (ctypes.c_ubyte * 64)()
+                _lib.check(lib.b200_peer_alloc(256, ctypes.byref(ptr), h), "peer_alloc")
+                self._own["__signal__"] = ptr.value
+                gathered = [None] * self.world
+                dist.all_gather_object(gathered, bytes(h), group=self.group)
+                row = []
+                for r in range(self.world):
+                    if r == self.rank:
+                        row.append(ptr.value)
+                        continue
+                    q = ctypes.c_void_p()
+                    hb = (ctypes.c_ubyte * 64).from_buffer_copy(gathered[r])
+                    _lib.check(lib.b200_peer_open(hb, ctypes.byref(q)), "peer_open")
+                    self._opened.append(q.value)
+                    row.append(q.value)
+                self.signal_ptrs = row
+                self._signal_view = _wrap(ptr.value, 32, torch.int32, self.device)
+            dist.barrier(group=self.group)
+        return list(self.signal_ptrs)
+
+    def check_signals(self):
+        """Raise if a bounded in-kernel wait gave up (synchronises)."""
+        if self.signal_ptrs is not None and int(self._signal_view[16].item()) != 0:
+            raise RuntimeError("libapex_b200: a cross-GPU wait timed out (a rank did not reach the step)")
 
     def barrier(self, flag: torch.Tensor | None = None):
         """Stream-ordered cross-rank barrier.  With ``flag`` (int32) it also ORs the ranks' overflow
@@ -112,6 +145,7 @@ class PeerBuffers:
             except Exception:
                 pass
             self.local = {}
+            self._signal_view = None
             for p in self._own.values():
                 lib.b200_peer_free(p)
             self._own = {}
@@ -121,8 +155,12 @@ class PeerGradientReducer:
     """reduce-scatter + mean + check (one kernel) followed by a flag-OR barrier; hands the optimizer a
     b200_peer_pull so its step kernel gathers the reduced shards on the fly."""
 
-    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True, first_tiles=None):
+    def __init__(self, buffers: PeerBuffers, bounds, gradient_average: bool = True, first_tiles=None,
+                 barrier: str = "signal"):
         self.buf = buffers
+        self.barrier = barrier
+        self.epoch = 0
+        self._pads = buffers.signal_pads() if barrier == "signal" else None
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1
         self.factor = (1.0 / buffers.world) if gradient_average else 1.0
@@ -133,8 +171,18 @@ class PeerGradientReducer:
                                        first_tile=first_tiles[buffers.rank] if first_tiles else 0)
 
     def reduce(self, overflow_flag: torch.Tensor):
-        """Enqueue on the current stream: barrier -> shard reduction -> barrier + flag OR."""
+        """Enqueue on the current stream: barrier -> shard reduction -> barrier + flag OR.
+
+        barrier="signal": both hand-shakes happen inside the kernels through signal pads in peer memory
+        (no NCCL call in the step); barrier="nccl": two 4-byte NCCL all-reduces."""
         b = self.buf
+        if self.barrier == "signal":
+            self.epoch += 1
+            sync = ops.make_peer_sync(self._pads, b.rank, self.epoch)
+            ops.peer_reduce_shard(self._grad_ptrs, b.local["reduced"], self.bounds[b.rank], self.bounds[b.rank + 1],
+                                  self.factor, None, sync)
+            ops.peer_wait_flags(sync, overflow_flag)
+            return
         b.barrier()                                     # every rank's gradients are in its `grads` buffer,
         #                                                 and every rank is done reading last step's `reduced`
         ops.peer_reduce_shard(self._grad_ptrs, b.local["reduced"], self.bounds[b.rank], self.bounds[b.rank + 1],

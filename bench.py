@@ -200,6 +200,8 @@ def main():
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
+    ap.add_argument("--peer-barrier", default="signal", choices=["signal", "nccl"],
+                    help="peer path: in-kernel signal-pad hand-shake (default) or two 4-byte NCCL all-reduces")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
                          "'nccl' = ncclAllReduce per bucket + epilogue kernel")
@@ -239,7 +241,7 @@ def main():
             acc += s_
         pbufs = PeerBuffers(n, torch.float16)
         bounds, first_tiles = tile_aligned_shards(offs, sizes, n, world, return_first_tiles=True)
-        reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles)
+        reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles, barrier=args.peer_barrier)
         gflat = pbufs.local["grads"]
         gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
     else:

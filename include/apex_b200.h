@@ -305,9 +305,31 @@ int32_t b200_peer_open(const void* handle, void** dev_ptr);
 int32_t b200_peer_close(void* dev_ptr);
 int32_t b200_peer_free(void* dev_ptr);
 
+/* In-kernel cross-GPU hand-shake (optional; replaces the two NCCL barrier all-reduces).
+ * Every rank owns one 128-byte signal pad in peer-addressable memory, zeroed at set-up.  With a
+ * b200_peer_sync, b200_peer_reduce_shard (a) tells every rank "my gradients of `epoch` are in
+ * place" and waits until every rank has said so before it reads their buffers, and (b) has its
+ * last block publish "my shard of `epoch` is written" plus this rank's overflow bit to every pad;
+ * b200_peer_wait_flags (one tiny kernel, next on the stream) waits for all ranks' (b) and ORs the
+ * overflow bits into *dev_flag.  `epoch` starts at 1 and grows by one per step on every rank.
+ * Waits are bounded (seconds): a rank that never arrives sets pad->error instead of hanging the GPU. */
+typedef struct b200_peer_signal_pad {
+    int32_t ready[B200_MAX_PEERS];          /* ready[r]: highest epoch rank r has announced */
+    int32_t done[B200_MAX_PEERS];           /* done[r]:  (epoch << 1) | overflow bit of rank r */
+    int32_t error;                          /* set when a bounded wait gave up */
+    int32_t local_flag, ticket;             /* kernel-internal */
+    int32_t reserved[13];
+} b200_peer_signal_pad;                     /* 128 bytes */
+
+typedef struct b200_peer_sync {
+    b200_peer_signal_pad* const* pads;      /* [world]: rank r's pad as addressable from this process */
+    int32_t world, rank, epoch, reserved;
+} b200_peer_sync;
+
 int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void* reduced,
                                int64_t begin, int64_t end, int32_t dtype, float factor,
-                               int32_t* dev_flag, void* stream);
+                               int32_t* dev_flag, const b200_peer_sync* sync, void* stream);
+int32_t b200_peer_wait_flags(const b200_peer_sync* sync, int32_t* dev_flag, void* stream);
 
 int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles,
                              int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,

@@ -116,7 +116,7 @@ def test_tile_aligned_shards_never_cut_a_tile():
 
 
 # ---- real peers over CUDA IPC / NVLink ----------------------------------------------------------------
-def _worker_ipc(rank, world, port):
+def _worker_ipc(rank, world, port, barrier="nccl", repeats=1):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -128,7 +128,7 @@ def _worker_ipc(rank, world, port):
     offs, total = _layout(sizes)
     bounds, first = tile_aligned_shards(offs, sizes, total, world, return_first_tiles=True)
     bufs = PeerBuffers(total, torch.float16)
-    red = PeerGradientReducer(bufs, bounds, first_tiles=first)
+    red = PeerGradientReducer(bufs, bounds, first_tiles=first, barrier=barrier)
     S = 256.0
     host_all = [(torch.randn(total, generator=torch.Generator().manual_seed(100 + r)) * 1e-2 * S).half() for r in range(world)]
     want_red = torch.zeros(total, dtype=torch.float16)
@@ -165,12 +165,25 @@ def _worker_ipc(rank, world, port):
                             step=1 if step == 1 else 2, inv_scale=(1.0 / S) if step == 1 else (2.0 / S))
         assert_lists_bit_equal(dp, hp, f"p(rank {rank}, step {step})")
         assert_lists_bit_equal(dc, hc, f"copy(rank {rank}, step {step})")
+    # hammer the hand-shake: many back-to-back steps without any host synchronisation in between
+    for _ in range(repeats):
+        red.reduce(state[ops.IDX_OVERFLOW_ACC:])
+        ops.scaler_update(state, True, 2000, 2.0, 0.0, 2.0 ** 24)
+        ops.fused_adam(table, torch.float16, torch.float32, torch.float16,
+                       [ops.AdamGroup(0.0, 0.9, 0.999, 1e-8, 0.0, 3, 1, 1)],      # lr 0: state moves, weights do not
+                       dev_inv_scale=state.view(torch.float32)[ops.IDX_INV_SCALE:], dev_found_inf=state[ops.IDX_FOUND_INF:],
+                       pull=red.pull)
+    torch.cuda.synchronize()
+    bufs.check_signals()
+    red_now = bufs.local["reduced"][bounds[rank]:bounds[rank + 1]].cpu()
+    assert torch.equal(red_now, want_red[bounds[rank]:bounds[rank + 1]])
     del table
     bufs.close()
     dist.destroy_process_group()
 
 
-def test_two_rank_ipc_reduce_and_fused_pull():
+@pytest.mark.parametrize("barrier,repeats", [("nccl", 1), ("signal", 200)])
+def test_two_rank_ipc_reduce_and_fused_pull(barrier, repeats):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
-    mp.spawn(_worker_ipc, args=(2, _free_port()), nprocs=2, join=True)
+    mp.spawn(_worker_ipc, args=(2, _free_port(), barrier, repeats), nprocs=2, join=True)
