@@ -101,6 +101,9 @@ SIGNATURES = {
     "b200_peer_reduce_shard": (c_int32, [ctypes.POINTER(c_void_p), c_int32, c_void_p, c_int64, c_int64, c_int32, c_float,
                                          c_void_p, ctypes.POINTER(PeerSync), c_void_p]),
     "b200_peer_wait_flags": (c_int32, [ctypes.POINTER(PeerSync), c_void_p, c_void_p]),
+    "b200_peer_gather": (c_int32, [ctypes.POINTER(c_void_p), c_int32, c_void_p, ctypes.POINTER(c_int64), c_int32, c_void_p,
+                                   ctypes.POINTER(PeerSync), c_void_p]),
+    "b200_set_peer_grid": (c_int32, [c_int32]),
     "b200_fused_adam_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
                                        c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                        ctypes.POINTER(PeerPull), c_void_p]),

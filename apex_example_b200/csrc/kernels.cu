@@ -27,6 +27,7 @@ static std::atomic<long long> g_launches{0};
 static std::atomic<int> g_ctas_per_sm{0};     // 0: per-kernel default
 static std::atomic<int> g_threads{256};
 static std::atomic<int> g_unroll{2};
+static std::atomic<int> g_peer_max_ctas{0};   // 0: fill the GPU; >0: run the peer kernels as a small "communication" grid
 
 int set_error(int code, const char* fmt, ...) {
     va_list ap;
@@ -783,6 +784,66 @@ __global__ void peer_wait_flags_kernel(const __grid_constant__ PeerSync sync, in
     if (threadIdx.x == 0 && s_any && flag) *flag = 1;
 }
 
+// All-gather half as a kernel of its own (used where the averaged gradient must be materialised, i.e.
+// inside apex.parallel.DistributedDataParallel): wait for every rank's shard, OR the overflow bits,
+// then copy each 8-element group from its owner's `reduced` buffer into the local bucket.
+struct ShardBounds {
+    long long b[B200_MAX_PEERS + 1];
+};
+
+template <int DT, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __restrict__ local_out,
+                   const __grid_constant__ ShardBounds bounds, int32_t* flag, const __grid_constant__ PeerSync sync) {
+    using T = typename Elem<DT>::type;
+    constexpr int kU = 4;
+    if (sync.pad[0] != nullptr) {
+        b200_peer_signal_pad* mine = sync.pad[sync.rank];
+        __shared__ int s_any;
+        if (threadIdx.x == 0) s_any = 0;
+        __syncthreads();
+        if (threadIdx.x < sync.world) {
+            wait_at_least(&mine->done[threadIdx.x], sync.epoch << 1, &mine->error);
+            if (ld_acquire_sys(&mine->done[threadIdx.x]) & 1) atomicOr(&s_any, 1);
+        }
+        __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x == 0 && s_any && flag) *flag = 1;
+    }
+    T* out = reinterpret_cast<T*>(local_out);
+    const long long n = bounds.b[world];
+    const long long n_groups = n / kVec;
+    const long long gtid = static_cast<long long>(blockIdx.x) * kThreads + threadIdx.x;
+    const long long stride = static_cast<long long>(gridDim.x) * kThreads;
+    auto owner_of = [&](long long elem) {
+        int o = 0;
+#pragma unroll
+        for (int k = 1; k < B200_MAX_PEERS; k++) o += (k < world && elem >= bounds.b[k]) ? 1 : 0;
+        return o;
+    };
+    for (long long g0 = gtid; g0 < n_groups; g0 += stride * kU) {
+        Raw8<DT> raw[kU];
+        bool act[kU];
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            const long long g = g0 + u * stride;
+            act[u] = g < n_groups;
+            if (act[u]) load8<DT, false>(reduced.p[owner_of(g * kVec)], g * kVec, raw[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < kU; u++) {
+            if (!act[u]) continue;
+            T* dst = out + (g0 + u * stride) * kVec;
+            if constexpr (DT == B200_F32) stg256(dst, raw[u].r);
+            else stg128(dst, raw[u].r);
+        }
+    }
+    const long long tail0 = n_groups * kVec;
+    if (gtid < n - tail0) {
+        const long long i = tail0 + gtid;
+        out[i] = reinterpret_cast<const T*>(reduced.p[owner_of(i)])[i];
+    }
+}
+
 // ============================================================================================
 // loss-scaler state machine (one thread; the whole point is that it runs on the device)
 // ============================================================================================
@@ -1183,6 +1244,8 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
         if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);                                               \
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                                  \
         if (blocks > want) blocks = want;                                                                         \
+        const int cap = g_peer_max_ctas.load();                                                                   \
+        if (cap > 0 && blocks > cap) blocks = cap;                                                                \
         if (blocks < 1) blocks = 1;                                                                               \
         kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, reduced, begin, end, factor, dev_flag, ps); \
     }
@@ -1193,6 +1256,46 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
     })
 #undef B200_LAUNCH_REDUCE
     return after_launch("peer_reduce_shard");
+}
+
+int32_t b200_set_peer_grid(int32_t max_ctas) {
+    if (max_ctas < 0) return set_error(B200_EINVAL, "set_peer_grid: max_ctas must be >= 0");
+    g_peer_max_ctas.store(max_ctas);
+    return 0;
+}
+
+int32_t b200_peer_gather(const void* const* peer_reduced, int32_t world, void* local_out, const int64_t* bounds, int32_t dtype,
+                         int32_t* dev_flag, const b200_peer_sync* sync, void* stream) {
+    PeerSync ps;
+    if (int rc = to_peer_sync(sync, ps, "peer_gather")) return rc;
+    if (world < 1 || world > B200_MAX_PEERS || !peer_reduced || !local_out || !bounds)
+        return set_error(B200_EINVAL, "peer_gather: bad argument");
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "peer_gather: bad dtype");
+    PeerBufs pb;
+    ShardBounds sb;
+    for (int r = 0; r < B200_MAX_PEERS; r++) pb.p[r] = r < world ? peer_reduced[r] : nullptr;
+    for (int r = 0; r <= B200_MAX_PEERS; r++) sb.b[r] = r <= world ? bounds[r] : bounds[world];
+    if (sb.b[0] != 0) return set_error(B200_EINVAL, "peer_gather: bounds[0] must be 0");
+    for (int r = 0; r < world; r++) {
+        if (!pb.p[r]) return set_error(B200_EINVAL, "peer_gather: peer buffer %d is NULL", r);
+        if (sb.b[r] > sb.b[r + 1] || (r > 0 && sb.b[r] % kVec)) return set_error(B200_EINVAL, "peer_gather: bounds must be non-decreasing multiples of 8");
+    }
+    constexpr int kThreads = 256;
+    const int64_t groups = sb.b[world] / kVec + 1;
+    const int64_t want = (groups + kThreads * 4 - 1) / (kThreads * 4);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B200_DISPATCH_DT(dtype, DT, {
+        auto kernel = peer_gather_kernel<DT, kThreads>;
+        static int occ = 0;
+        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
+        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;
+        if (blocks > want) blocks = want;
+        const int cap = g_peer_max_ctas.load();
+        if (cap > 0 && blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(pb, world, local_out, sb, dev_flag, ps);
+    })
+    return after_launch("peer_gather");
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -195,3 +195,16 @@ def clip_scale(sumsq: torch.Tensor, max_norm: float, scale_out: torch.Tensor, no
                dev_inv_scale=None):
     _lib.check(_lib.load().b200_clip_scale(sumsq.data_ptr(), _addr(dev_inv_scale), inv_scale, float(max_norm),
                                            scale_out.data_ptr(), _addr(norm_out), _stream()), "clip_scale")
+
+
+def peer_gather(reduced_ptrs, local_out: torch.Tensor, bounds, dev_flag=None, sync=None):
+    """All-gather half: pull every shard of the mean from its owner into ``local_out``."""
+    arr = (ctypes.c_void_p * len(reduced_ptrs))(*reduced_ptrs)
+    b = (ctypes.c_int64 * len(bounds))(*bounds)
+    _lib.check(_lib.load().b200_peer_gather(arr, len(reduced_ptrs), local_out.data_ptr(), b, dtype_code(local_out.dtype),
+                                            _addr(dev_flag), ctypes.byref(sync) if sync is not None else None, _stream()),
+               "peer_gather")
+
+
+def set_peer_grid(max_ctas: int = 0):
+    _lib.check(_lib.load().b200_set_peer_grid(max_ctas), "set_peer_grid")

@@ -70,7 +70,7 @@ class _CudaBucketOps:
 
 class _Bucket:
     __slots__ = ("index", "dtype", "params", "offsets", "flat", "flat32", "views", "ready", "launched", "stream",
-                 "ready_event", "done_event")
+                 "ready_event", "done_event", "numel", "reduced", "grad_ptrs", "red_ptrs", "pads", "epoch", "bounds")
 
     def __init__(self, index, dtype):
         self.index = index
@@ -102,7 +102,8 @@ class DistributedDataParallel(Module):
     def __init__(self, module, message_size=10000000, delay_allreduce=False, shared_param=None,
                  allreduce_trigger_params=None, retain_allreduce_buffers=False, allreduce_always_fp32=False,
                  num_allreduce_streams=1, allreduce_communicators=None, gradient_average=True,
-                 gradient_predivide_factor=1.0, gradient_average_split_factor=None, prof=False, _bucket_ops=None):
+                 gradient_predivide_factor=1.0, gradient_average_split_factor=None, prof=False,
+                 allreduce_backend=None, _bucket_ops=None):
         super().__init__()
         if not dist.is_available() or not dist.is_initialized():
             raise RuntimeError("apex.parallel.DistributedDataParallel requires torch.distributed to be initialized "
@@ -132,6 +133,13 @@ class DistributedDataParallel(Module):
         if self.custom_allreduce_triggers and self.delay_allreduce:
             raise ValueError("Setting allreduce_trigger_params is only valid if delay_allreduce=False.")
         self._ops = _bucket_ops
+        # "nccl" (default, as apex) or "peer": the bucket all-reduce runs as two kernels of this library
+        # over NVLink peer memory (reduce-scatter + mean + overflow check, then gather), no NCCL call
+        import os
+        self.allreduce_backend = (allreduce_backend or os.environ.get("APEX_B200_DDP_BACKEND") or "nccl").lower()
+        if self.allreduce_backend not in ("nccl", "peer"):
+            raise ValueError("allreduce_backend must be 'nccl' or 'peer'")
+        self._peer = {}
         self._enabled = True
         self._armed = False
         self._callback_queued = False
@@ -222,18 +230,72 @@ class DistributedDataParallel(Module):
                 b.offsets.append(off)
                 off += p.numel()
             device = b.params[0].device
-            b.flat = torch.zeros(off, dtype=b.dtype, device=device)
-            b.views = [b.flat[o:o + p.numel()].view_as(p) for o, p in zip(b.offsets, b.params)]
-            if self.allreduce_always_fp32 and b.dtype != torch.float32:
+            b.numel = off
+            b.flat = None if self._use_peer() else torch.zeros(off, dtype=b.dtype, device=device)
+            if b.flat is not None:
+                b.views = [b.flat[o:o + p.numel()].view_as(p) for o, p in zip(b.offsets, b.params)]
+            if self.allreduce_always_fp32 and b.dtype != torch.float32 and not self._use_peer():
                 b.flat32 = torch.zeros(off, dtype=torch.float32, device=device)
             slot = b.index % self.num_allreduce_streams
             b.stream = self.bucket_streams[slot]
             if self._on_cuda:
                 b.ready_event = torch.cuda.Event()
                 b.done_event = torch.cuda.Event()
+        if self._use_peer():
+            self._build_peer_buckets()
+            # the peer kernels overlap with backward and spin while slower ranks catch up: keep them a
+            # small "communication" grid (process-wide knob of the library)
+            import os
+            ops.set_peer_grid(int(os.environ.get("APEX_B200_PEER_CTAS", "32")))
         if self.retain_allreduce_buffers:
             self.allreduce_buffers = [b.flat for b in self.buckets]
         self._checked_ids = frozenset(self._bucket_of)
+
+    def _use_peer(self):
+        return self.allreduce_backend == "peer" and self._on_cuda and self.world_size > 1
+
+    def _build_peer_buckets(self):
+        """Peer backend: all buckets of one dtype are slices of ONE peer-addressable buffer pair (gradients,
+        reduced shards); every bucket has its own signal pad and its own epoch counter."""
+        from .peer import PeerBuffers
+        world = int(self.world_size)
+        by_dtype = {}
+        for b in self.buckets:
+            by_dtype.setdefault(b.dtype, []).append(b)
+        for dtype, group in by_dtype.items():
+            starts, total = [], 0
+            for b in group:
+                total += (-total) % 64                         # 128-byte aligned bucket starts
+                starts.append(total)
+                total += b.numel
+            bufs = PeerBuffers(max(total, 64), dtype, names=("grads", "reduced"))
+            bufs.signal_pads(count=len(group))
+            self._peer[dtype] = bufs
+            esize = bufs.local["grads"].element_size()
+            for i, (b, st) in enumerate(zip(group, starts)):
+                b.flat = bufs.local["grads"][st:st + b.numel]
+                b.reduced = bufs.local["reduced"][st:st + b.numel]
+                b.views = [b.flat[o:o + p.numel()].view_as(p) for o, p in zip(b.offsets, b.params)]
+                b.grad_ptrs = [ptr + st * esize for ptr in bufs.ptrs("grads")]
+                b.red_ptrs = [ptr + st * esize for ptr in bufs.ptrs("reduced")]
+                b.pads = bufs.signal_pads(index=i)
+                b.epoch = 0
+                shard = -(-b.numel // world)
+                shard += (-shard) % 8
+                b.bounds = [min(r * shard, b.numel) for r in range(world)] + [b.numel]
+        self._rank = dist.get_rank()
+
+    def close(self):
+        """Release the peer-addressable buffers (peer backend; call on every rank before the process
+        group is destroyed).  Gradients that are views of the buckets must not be used afterwards."""
+        for p in self.module.parameters():
+            p.grad = None
+        for b in self.buckets:
+            b.flat = b.reduced = None
+            b.views = []
+        for bufs in self._peer.values():
+            bufs.close()
+        self._peer = {}
 
     def _sync_bucket_structure(self):
         """C2: rank 0 broadcasts [num_buckets] + bucket sizes + parameter sizes; all ranks must agree."""
@@ -319,34 +381,54 @@ class DistributedDataParallel(Module):
                 # gradients that already live in the bucket (accumulated in place) still need the predivide
                 raise RuntimeError("gradient_predivide_factor != 1 cannot be combined with accumulating into "
                                    "bucket views across iterations; call zero_grad() between reductions.")
-            buf = b.flat
-            if b.flat32 is not None:
-                self._ops.gather([b.flat], [b.flat32], 1.0, self._table_cache, ("up", b.index))
-                buf = b.flat32
-            pg = self.bucket_pgs[b.index % self.num_allreduce_streams]
-            if self.world_size > 1:
-                if pg is not None:
-                    dist.all_reduce(buf, group=pg)
-                else:
-                    dist.all_reduce(buf)
-            factor = 1.0
-            if self.gradient_average:
-                factor = self.gradient_predivide_factor / self.world_size
-            elif self.gradient_predivide_factor != 1.0:
-                factor = self.gradient_predivide_factor
-            flag = self._overflow_flag()
-            if b.flat32 is not None:
-                self._ops.epilogue(buf, factor, None)
-                self._ops.gather([b.flat32], [b.flat], 1.0, self._table_cache, ("down", b.index))
-                self._ops.epilogue(b.flat, 1.0, flag)
+            if self._use_peer():
+                self._peer_allreduce(b)
             else:
-                self._ops.epilogue(buf, factor, flag)
+                self._nccl_allreduce(b)
             if self._on_cuda:
                 b.done_event.record(side)
         for p, view in zip(b.params, b.views):
             p.grad = view
         if self.prof:
             torch.cuda.nvtx.range_pop()
+
+    def _averaging_factor(self):
+        if self.gradient_average:
+            return self.gradient_predivide_factor / self.world_size
+        if self.gradient_predivide_factor != 1.0:
+            return self.gradient_predivide_factor
+        return 1.0
+
+    def _nccl_allreduce(self, b):
+        buf = b.flat
+        if b.flat32 is not None:
+            self._ops.gather([b.flat], [b.flat32], 1.0, self._table_cache, ("up", b.index))
+            buf = b.flat32
+        pg = self.bucket_pgs[b.index % self.num_allreduce_streams]
+        if self.world_size > 1:
+            if pg is not None:
+                dist.all_reduce(buf, group=pg)
+            else:
+                dist.all_reduce(buf)
+        factor = self._averaging_factor()
+        flag = self._overflow_flag()
+        if b.flat32 is not None:
+            self._ops.epilogue(buf, factor, None)
+            self._ops.gather([b.flat32], [b.flat], 1.0, self._table_cache, ("down", b.index))
+            self._ops.epilogue(b.flat, 1.0, flag)
+        else:
+            self._ops.epilogue(buf, factor, flag)
+
+    def _peer_allreduce(self, b):
+        """All-reduce of one bucket in two launches over NVLink peer memory: (1) reduce-scatter + mean +
+        overflow bit of this rank's shard, with the cross-GPU hand-shake inside the kernel; (2) gather of
+        every shard from its owner into the local bucket, which first waits for all shards and ORs the
+        overflow bits into the loss scaler's flag.  The sum is accumulated in fp32 in rank order."""
+        b.epoch += 1
+        sync = ops.make_peer_sync(b.pads, self._rank, b.epoch)
+        ops.peer_reduce_shard(b.grad_ptrs, b.reduced, b.bounds[self._rank], b.bounds[self._rank + 1],
+                              self._averaging_factor(), None, sync)
+        ops.peer_gather(b.red_ptrs, b.flat, b.bounds, self._overflow_flag(), sync)
 
     def _finalize(self):
         """End of backward: flush what has not been reduced yet and make the main stream wait."""

@@ -90,15 +90,16 @@ class PeerBuffers:
     def ptrs(self, name):
         return list(self._ptrs[name])
 
-    def signal_pads(self):
-        """Allocate (once) the 128-byte signal pad of every rank and return their addresses as seen from
-        this process (b200_peer_signal_pad, zero-initialised by the allocator)."""
+    def signal_pads(self, count: int = 1, index: int = 0):
+        """Allocate (once) ``count`` 128-byte signal pads per rank and return pad ``index`` of every rank
+        as addresses valid in this process (b200_peer_signal_pad, zero-initialised by the allocator)."""
         if self.signal_ptrs is None:
+            self._n_pads = count
             lib = _lib.load()
             with torch.cuda.device(self.device):
                 ptr = ctypes.c_void_p()
                 h = (ctypes.c_ubyte * 64)()
-                _lib.check(lib.b200_peer_alloc(256, ctypes.byref(ptr), h), "peer_alloc")
+                _lib.check(lib.b200_peer_alloc(max(256, 128 * count), ctypes.byref(ptr), h), "peer_alloc")
                 self._own["__signal__"] = ptr.value
                 gathered = [None] * self.world
                 dist.all_gather_object(gathered, bytes(h), group=self.group)
@@ -113,13 +114,15 @@ class PeerBuffers:
                     self._opened.append(q.value)
                     row.append(q.value)
                 self.signal_ptrs = row
-                self._signal_view = _wrap(ptr.value, 32, torch.int32, self.device)
+                self._signal_view = _wrap(ptr.value, 32 * count, torch.int32, self.device)
             dist.barrier(group=self.group)
-        return list(self.signal_ptrs)
+        if index >= self._n_pads:
+            raise RuntimeError("signal pad index out of range")
+        return [p + 128 * index for p in self.signal_ptrs]
 
     def check_signals(self):
         """Raise if a bounded in-kernel wait gave up (synchronises)."""
-        if self.signal_ptrs is not None and int(self._signal_view[16].item()) != 0:
+        if self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:, 16].any().item()):
             raise RuntimeError("libapex_b200: a cross-GPU wait timed out (a rank did not reach the step)")
 
     def barrier(self, flag: torch.Tensor | None = None):

@@ -331,6 +331,20 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
                                int32_t* dev_flag, const b200_peer_sync* sync, void* stream);
 int32_t b200_peer_wait_flags(const b200_peer_sync* sync, int32_t* dev_flag, void* stream);
 
+/* The all-gather half as a kernel of its own, for callers that need the averaged gradient
+ * materialised (apex.parallel.DistributedDataParallel keeps apex's contract that param.grad
+ * holds the mean after backward): waits for every rank's shard (if `sync`), ORs the overflow bits
+ * into *dev_flag and copies each element of [0, bounds[world]) from its owner's `reduced` buffer
+ * into `local_out`.  bounds[1..world-1] must be multiples of 8.  b200_peer_reduce_shard +
+ * b200_peer_gather is a complete all-reduce over peer memory in two launches, no NCCL. */
+int32_t b200_peer_gather(const void* const* peer_reduced, int32_t world, void* local_out,
+                         const int64_t* bounds, int32_t dtype, int32_t* dev_flag,
+                         const b200_peer_sync* sync, void* stream);
+
+/* Cap the grid of the peer kernels (0 = fill the GPU).  Under DDP they overlap with backward and
+ * spin while they wait for slower ranks, so they are run as a small "communication" grid. */
+int32_t b200_set_peer_grid(int32_t max_ctas);
+
 int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles,
                              int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                              const b200_adam_group* groups, int32_t n_groups,

@@ -68,6 +68,7 @@ def _worker_train(rank, world, port, kwargs, out):
         assert torch.equal(lo, hi), "parameters diverged across ranks"
     if rank == 0:
         out.put((scales, len(ddp.buckets)))
+    ddp.close()
     dist.destroy_process_group()
 
 
@@ -78,7 +79,9 @@ def _need(n):
 
 @pytest.mark.parametrize("kwargs", [dict(), dict(message_size=20000), dict(delay_allreduce=True),
                                     dict(message_size=20000, num_allreduce_streams=2),
-                                    dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0)])
+                                    dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0),
+                                    dict(allreduce_backend="peer"), dict(allreduce_backend="peer", message_size=20000),
+                                    dict(allreduce_backend="peer", delay_allreduce=True, num_allreduce_streams=2)])
 def test_two_rank_training_identical_ranks_and_skips(kwargs):
     _need(2)
     ctx = mp.get_context("spawn")
@@ -88,12 +91,12 @@ def test_two_rank_training_identical_ranks_and_skips(kwargs):
     assert n_buckets == (2 if kwargs.get("message_size") else 1)      # [16,4096,256,65536] | [256,16384]
 
 
-def _worker_mean(rank, world, port):
+def _worker_mean(rank, world, port, backend="nccl"):
     _init(rank, world, port)
     from apex.parallel import DistributedDataParallel
     model = _mlp(0).cuda().half()
     ref = _mlp(0).cuda().half()
-    ddp = DistributedDataParallel(model, message_size=30000)
+    ddp = DistributedDataParallel(model, message_size=30000, allreduce_backend=backend)
     gen = torch.Generator().manual_seed(9 + rank)
     x = torch.randn(16, 64, generator=gen).cuda().half()
     ddp(x).float().pow(2).mean().backward()
@@ -102,13 +105,17 @@ def _worker_mean(rank, world, port):
         want = q.grad.clone()
         dist.all_reduce(want)                       # fp16 SUM, then x 1/world in fp16: apex's order
         want.mul_(1.0 / world)
+        # two addends: the fp16 sum is the correctly rounded exact sum whichever way it is accumulated, so the
+        # NCCL path and the peer path (fp32 accumulation, one rounding) must both reproduce it exactly
         assert torch.equal(p.grad, want)
+    ddp.close()
     dist.destroy_process_group()
 
 
-def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype():
+@pytest.mark.parametrize("backend", ["nccl", "peer"])
+def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype(backend):
     _need(2)
-    mp.spawn(_worker_mean, args=(2, _free_port()), nprocs=2, join=True)
+    mp.spawn(_worker_mean, args=(2, _free_port(), backend), nprocs=2, join=True)
 
 
 def _worker_single(rank, world, port):
