@@ -197,6 +197,8 @@ def main():
     ap.add_argument("--no-train", dest="train", action="store_false",
                     help="skip the GPT-2 medium training measurement (amp O2 + FusedAdam + apex DDP) reported under 'train'")
     ap.add_argument("--train-batch", type=int, default=4, help="per-GPU micro-batch of 1024-token sequences")
+    ap.add_argument("--ddp-backend", default="nccl", help="apex DDP bucket all-reduce for the training measurement: "
+                    "nccl | peer | nccl,peer (measure both; the first is reported under 'train')")
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
@@ -412,7 +414,11 @@ def main():
     train = None
     if args.train:
         try:
-            train = run_train(dev, world, rank, barrier, args.train_batch)
+            backends = [b for b in args.ddp_backend.split(",") if b] if world > 1 else ["nccl"]
+            runs = [run_train(dev, world, rank, barrier, args.train_batch, ddp_backend=b) for b in backends]
+            train = runs[0]
+            if len(runs) > 1:
+                train["other_ddp_backends"] = runs[1:]
         except Exception as exc:                    # reported, never fatal for the headline line
             train = {"error": f"{type(exc).__name__}: {exc}"[:300]}
 
@@ -448,7 +454,7 @@ def main():
         dist.destroy_process_group()
 
 
-def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmup=3):
+def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmup=3, ddp_backend="nccl"):
     """GPT-2 medium (24 x 1024, 354.8M parameters, random init) on synthetic tokens through the
     drop-in API exactly as the reference drives it: amp.initialize(O2) -> apex DDP -> scale_loss /
     backward / FusedAdam.step.  The transformer's forward/backward is torch/transformers library
@@ -471,8 +477,9 @@ def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmu
     n_params = sum(p.numel() for p in model.parameters())
     opt = FusedAdam(model.parameters(), lr=1e-4, weight_decay=0.01)
     model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    ddp = None
     if world > 1:
-        model = DistributedDataParallel(model)
+        model = ddp = DistributedDataParallel(model, allreduce_backend=ddp_backend)
     host_tokens = torch.randint(0, 50257, (micro_batch, seq), generator=torch.Generator().manual_seed(rank)).pin_memory()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
 
@@ -511,14 +518,16 @@ def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmu
     step_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / steps       # FusedAdam.step: one launch per dtype set
     scaler = amp._amp_state.loss_scalers[0]
     res = {"model": "GPT-2 medium (GPT2Config(n_embd=1024, n_layer=24, n_head=16)), amp O2, FusedAdam, "
-                    + ("apex DistributedDataParallel" if world > 1 else "single GPU"),
+                    + (f"apex DistributedDataParallel (bucket all-reduce: {ddp_backend})" if world > 1 else "single GPU"),
            "params": n_params, "micro_batch_per_gpu": micro_batch, "seq_len": seq, "n_gpus": world,
            "samples_per_s": micro_batch * world / (ms * 1e-3), "tokens_per_s": micro_batch * seq * world / (ms * 1e-3),
            "ms_per_step": ms, "ms_scale_loss_exit": post_bwd, "ms_optimizer_step": step_ms,
            "optimizer_step_gbs": BYTES_PER_PARAM * n_params / (step_ms * 1e-3) / 1e9,
            "b200_kernel_launches_per_step": (ops.launch_count() - l0) / steps,
            "final_loss": float(loss.item()), "loss_scale": scaler.loss_scale(), "steps": steps}
-    del model, opt
+    if ddp is not None:
+        ddp.close()
+    del model, opt, ddp
     torch.cuda.empty_cache()
     return res
 
