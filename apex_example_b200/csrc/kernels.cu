@@ -87,6 +87,9 @@ static int after_launch(const char* name) {
 // per-thread accumulator carried through the walk: a bool ("saw inf/NaN") unless the Op declares its own
 template <class Op, class = void> struct AccOf { using type = bool; };
 template <class Op> struct AccOf<Op, std::void_t<typename Op::Acc>> { using type = typename Op::Acc; };
+// optional per-Op cap on resident CTAs per SM (0 = whatever the occupancy calculator allows)
+template <class Op, class = void> struct MaxCtasOf { static constexpr int value = 0; };
+template <class Op> struct MaxCtasOf<Op, std::void_t<decltype(Op::kMaxCtasPerSm)>> { static constexpr int value = Op::kMaxCtasPerSm; };
 
 template <class Op, int kThreads, int kUnroll>
 __global__ void __launch_bounds__(kThreads)
@@ -106,7 +109,11 @@ static int launch_one(const char* name, const void* dev_table, int64_t n_tiles, 
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) dev = 0;
-    if (occ[dev] == 0) occ[dev] = resident_ctas_per_sm(kernel, kThreads);
+    if (occ[dev] == 0) {
+        occ[dev] = resident_ctas_per_sm(kernel, kThreads);
+        if constexpr (MaxCtasOf<Op>::value > 0)
+            if (occ[dev] > MaxCtasOf<Op>::value) occ[dev] = MaxCtasOf<Op>::value;
+    }
     unsigned grid = grid_for(n_tiles, occ[dev]);
     if (max_grid && grid > max_grid) grid = max_grid;
     kernel<<<grid, kThreads, 0, st>>>(dev_table, prm);
@@ -498,6 +505,9 @@ template <int G, int S, int C>
 struct SgdOp {
     using Params = SgdParams;
     static constexpr int kUnrollMul = 1;
+    // measured (profiles/r01_tune_sweep_*.txt): 2 resident CTAs/SM stream at 6.5-6.7 TB/s, the 3 the
+    // register budget would allow only at 6.0 TB/s (more concurrent streams per DRAM page)
+    static constexpr int kMaxCtasPerSm = 2;
     struct Ctx { SgdConsts k; float s; const void* g; };
     static constexpr int kCopyCol = 3;
     static __device__ __forceinline__ uint32_t rotation(const Params& p) { return p.pull.first_tile; }
