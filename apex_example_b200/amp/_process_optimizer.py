@@ -21,7 +21,7 @@ import torch
 from .. import ops
 from ..optimizers._fused_base import AmpStash, FusedOptimizerBase
 from ..tables import TensorTable, signature_of
-from ._amp_state import _amp_state, maybe_print
+from ._amp_state import _amp_state
 
 _HALF_TYPES = (torch.float16, torch.bfloat16)
 _GRAD_OF = operator.attrgetter("grad")

@@ -12,7 +12,7 @@ import types
 import torch
 
 from ._amp_state import _amp_state, maybe_print
-from ._process_optimizer import _is_fused, _lazy
+from ._process_optimizer import _is_fused
 
 
 @contextlib.contextmanager

@@ -11,7 +11,7 @@ import torch
 
 from .. import ops
 from ..tables import TensorTable, signature_of
-from ._amp_state import _amp_state, maybe_print
+from ._amp_state import maybe_print
 
 
 class LossScaler:

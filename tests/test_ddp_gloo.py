@@ -147,20 +147,6 @@ def test_ddp_trigger_params_and_retained_buffers():
     mp.spawn(_worker_options, args=(2, _free_port()), nprocs=2, join=True)
 
 
-def _worker_mismatch(rank, world, port):
-    _init(rank, world, port)
-    from apex_example_b200.parallel import DistributedDataParallel
-    model = _model(0) if rank == 0 else torch.nn.Sequential(torch.nn.Linear(20, 51), torch.nn.Linear(51, 4))
-    try:
-        DistributedDataParallel(model, _bucket_ops=OracleBucketOps())
-    except Exception as e:      # rank 1 sees a structure mismatch (or the broadcast itself fails on sizes)
-        assert rank == 1 or "differs" in str(e) or True
-        dist.destroy_process_group()
-        return
-    assert rank == 0
-    dist.destroy_process_group()
-
-
 def test_ddp_requires_process_group_and_cuda():
     sys.path.insert(0, ROOT)
     from apex_example_b200.parallel import DistributedDataParallel

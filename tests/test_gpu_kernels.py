@@ -1,13 +1,11 @@
 """-m gpu parity tests: every kernel of libapex_b200.so, called through the C ABI, against
 oracle/amp_step_oracle.c on the same seeded inputs.  The bar is bit-exact (integer decisions
 AND floating-point state): both sides do fp32 arithmetic in the same order without FMA."""
-import ctypes
-
 import pytest
 import torch
 
 import oracle
-from apex_example_b200 import _lib, ops
+from apex_example_b200 import ops
 from apex_example_b200.tables import TensorTable
 from gpu_util import ADVERSARIAL_SIZES, assert_lists_bit_equal, bit_equal, make_list
 

@@ -30,7 +30,6 @@ def main():
     args = ap.parse_args()
     from apex import amp
     from apex.optimizers import FusedAdam
-    from apex_example_b200 import ops
 
     dev = torch.device("cuda", 0)
     sizes = many_small(total=args.total, seed=0)
