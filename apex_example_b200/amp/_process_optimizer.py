@@ -237,7 +237,10 @@ def _process_optimizer(optimizer, properties):
             grads = []
             for p in params:
                 if p.grad is not None:
-                    p.grad.detach_()
+                    if p.grad.grad_fn is not None:
+                        p.grad.detach_()
+                    else:
+                        p.grad.requires_grad_(False)      # views of the DDP buckets cannot be detached in place
                     grads.append(p.grad)
             if grads:
                 torch._foreach_zero_(grads)

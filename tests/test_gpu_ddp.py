@@ -33,10 +33,17 @@ def _mlp(seed):
 def _worker_train(rank, world, port, kwargs, out):
     _init(rank, world, port)
     from apex import amp
-    from apex.optimizers import FusedAdam
+    from apex.optimizers import FusedAdam, FusedSGD
     from apex.parallel import DistributedDataParallel
+    kwargs = dict(kwargs)
+    which = kwargs.pop("optimizer", "fused_adam")
     model = _mlp(rank).cuda()                       # different per rank; DDP must broadcast rank 0's
-    opt = FusedAdam(model.parameters(), lr=1e-3, weight_decay=0.01)
+    if which == "fused_adam":
+        opt = FusedAdam(model.parameters(), lr=1e-3, weight_decay=0.01)
+    elif which == "fused_sgd":                      # set_grad_none=False: gradients stay views of the buckets
+        opt = FusedSGD(model.parameters(), lr=1e-2, momentum=0.9)
+    else:                                           # the reference script's own choice (test_apex_distributed_spawn.py:119)
+        opt = torch.optim.SGD(model.parameters(), 1e-4)
     model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
     ddp = DistributedDataParallel(model, **kwargs)
     gen = torch.Generator().manual_seed(50 + rank)
@@ -80,6 +87,7 @@ def _need(n):
 @pytest.mark.parametrize("kwargs", [dict(), dict(message_size=20000), dict(delay_allreduce=True),
                                     dict(message_size=20000, num_allreduce_streams=2),
                                     dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0),
+                                    dict(optimizer="torch_sgd"), dict(optimizer="fused_sgd", message_size=20000),
                                     dict(allreduce_backend="peer"), dict(allreduce_backend="peer", message_size=20000),
                                     dict(allreduce_backend="peer", delay_allreduce=True, num_allreduce_streams=2)])
 def test_two_rank_training_identical_ranks_and_skips(kwargs):
