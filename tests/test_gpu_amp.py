@@ -595,3 +595,109 @@ def test_bf16_o2_training_runs_with_bf16_model_and_fp32_masters():
     assert float(loss) < first
     for master, model_p in opt._amp_stash.model_of.items():
         assert master.dtype == torch.float32 and torch.equal(model_p, master.bfloat16())
+
+
+# ------------------------------------------------------------------------------------------------
+# less-travelled paths
+# ------------------------------------------------------------------------------------------------
+def test_step_window_stress_200_unsynchronised_steps_with_random_skips():
+    """The host runs far ahead of the device (tiny tensors, no sync): the step counter must fall back to a
+    sync when more than B200_STEP_WINDOW-1 launches are unobserved, and the result must still equal the
+    oracle's sequential semantics bit for bit."""
+    import random
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    rng = random.Random(3)
+    gen = torch.Generator().manual_seed(6)
+    p = torch.nn.Parameter((torch.randn(257, generator=gen) * 0.1).cuda())
+
+    class Holder(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.p = p
+    model = Holder()
+    opt = FusedAdam(model.parameters(), lr=1e-2, set_grad_none=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    hp = model.p.detach().float().cpu().clone()
+    hm, hv, hc = torch.zeros(257), torch.zeros(257), hp.half()
+    sc = oracle.LossScaler()
+    dummy = torch.zeros((), device="cuda")
+    gbuf = torch.zeros(257, dtype=torch.float16, device="cuda")
+    model.p.grad = gbuf
+    good = 0
+    for it in range(200):
+        bad = rng.random() < 0.15
+        g = (torch.randn(257, generator=gen) * 1e-3 * sc.loss_scale).half()
+        if bad:
+            g[rng.randrange(257)] = float("inf")
+        gbuf.copy_(g, non_blocking=True)
+        with amp.scale_loss(dummy, opt):
+            pass
+        opt.step()
+        if not sc.update_scale(bad):
+            good += 1
+            oracle.adam(g, hp, hm, hv, hc, lr=1e-2, step=good, inv_scale=sc.inv_scale)
+    torch.cuda.synchronize()
+    master = next(amp.master_params(opt))
+    assert torch.equal(master.detach().cpu(), hp) and torch.equal(model.p.detach().cpu(), hc)
+    assert opt.state_dict()["param_groups"][0]["step"] == good
+    assert amp._amp_state.loss_scalers[0].loss_scale() == sc.loss_scale
+
+
+def test_two_losses_two_optimizers_and_frozen_parameters():
+    from apex import amp
+    from apex.optimizers import FusedAdam, FusedSGD
+    net_a, net_b = _mlp(61), _mlp(62)
+    for q in list(net_b.parameters())[:2]:
+        q.requires_grad_(False)                                  # frozen: never gets a gradient
+    opt_a = FusedAdam(net_a.parameters(), lr=1e-2)
+    opt_b = FusedSGD([q for q in net_b.parameters() if q.requires_grad], lr=1e-2, momentum=0.9,
+                     materialize_master_grads=False)
+    (net_a, net_b), (opt_a, opt_b) = amp.initialize([net_a, net_b], [opt_a, opt_b], opt_level="O2", num_losses=2,
+                                                    verbosity=0)
+    assert len(amp._amp_state.loss_scalers) == 2
+    x = torch.randn(16, 32, device="cuda")
+    frozen = [q.detach().clone() for q in list(net_b.parameters())[:2]]
+    before_a = [q.detach().clone() for q in net_a.parameters()]
+    before_b = [q.detach().clone() for q in list(net_b.parameters())[2:]]
+    for it in range(4):
+        la = net_a(x).float().pow(2).mean()
+        lb = net_b(x * (float("inf") if it == 0 else 1.0)).float().pow(2).mean()      # only loss 1 overflows
+        opt_a.zero_grad()
+        opt_b.zero_grad()
+        with amp.scale_loss(la, opt_a, loss_id=0) as s:
+            s.backward()
+        with amp.scale_loss(lb, opt_b, loss_id=1) as s:
+            s.backward()
+        opt_a.step()
+        opt_b.step()
+    torch.cuda.synchronize()
+    assert [s.loss_scale() for s in amp._amp_state.loss_scalers] == [65536.0, 32768.0]
+    assert all(torch.equal(a, b.detach()) for a, b in zip(frozen, list(net_b.parameters())[:2]))
+    assert all(not torch.equal(a, b.detach()) for a, b in zip(before_a, net_a.parameters()))
+    assert all(not torch.equal(a, b.detach()) for a, b in zip(before_b, list(net_b.parameters())[2:]))
+    assert opt_a.state_dict()["param_groups"][0]["step"] == 4 and opt_b.state_dict()["param_groups"][0]["step"] == 3
+
+
+def test_add_param_group_after_steps_starts_its_own_step_count():
+    from apex.optimizers import FusedAdam
+    gen = torch.Generator().manual_seed(9)
+    a = torch.nn.Parameter((torch.randn(100, generator=gen)).cuda())
+    b = torch.nn.Parameter((torch.randn(50, generator=gen)).cuda())
+    opt = FusedAdam([a], lr=1e-2, weight_decay=0.0)
+    ha, hb = a.detach().cpu().clone(), b.detach().cpu().clone()
+    st = {k: torch.zeros(n) for k, n in (("ma", 100), ("va", 100), ("mb", 50), ("vb", 50))}
+    for step in range(1, 6):
+        ga = torch.randn(100, generator=gen)
+        a.grad = ga.cuda()
+        if step == 3:
+            opt.add_param_group({"params": [b], "lr": 1e-3})
+        if step >= 3:
+            gb = torch.randn(50, generator=gen)
+            b.grad = gb.cuda()
+            oracle.adam(gb, hb, st["mb"], st["vb"], None, lr=1e-3, step=step - 2, adam_w_mode=True)
+        opt.step()
+        oracle.adam(ga, ha, st["ma"], st["va"], None, lr=1e-2, step=step, adam_w_mode=True)
+    torch.cuda.synchronize()
+    assert torch.equal(a.detach().cpu(), ha) and torch.equal(b.detach().cpu(), hb)
+    assert [g["step"] for g in opt.param_groups] == [5, 3]
