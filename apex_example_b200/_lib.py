@@ -10,7 +10,7 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libapex_b200.so")
+SO_PATH = os.environ.get("APEX_B200_SO") or os.path.join(_HERE, "libapex_b200.so")   # override: A/B experiments
 CSRC = os.path.join(_HERE, "csrc")
 
 F32, F16, BF16, NONE = 0, 1, 2, -1
