@@ -12,6 +12,16 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 
 
+def pytest_sessionstart(session):
+    """A fresh checkout has no built artefacts (*.so is git-ignored): build the CUDA library (nvcc
+    cross-compiles without a GPU) and the CPU oracle before anything imports them."""
+    from apex_example_b200 import _lib
+    if not os.path.exists(_lib.SO_PATH):
+        _lib.build()
+    import oracle
+    oracle.build()
+
+
 def pytest_collection_modifyitems(config, items):
     import torch
     if torch.cuda.is_available():
