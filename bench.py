@@ -216,6 +216,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback (use --impl reference for the CPU restatement)")
     import torch.distributed as dist
+    from apex_example_b200 import _lib
+    if not os.path.exists(_lib.SO_PATH) and int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        _lib.build()                                 # normally built by __graft_entry__.build() and shipped in-tree
     from apex_example_b200 import ops
     from apex_example_b200.tables import TensorTable
 
