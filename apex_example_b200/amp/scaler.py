@@ -37,7 +37,6 @@ class LossScaler:
         self._mirror = None         # pinned host copy written by the update kernel
         self._seen_seq = 0
         self._seen_skips = 0
-        self._quiet = False
         self._loss_id = 0
         self._tables = {}
 

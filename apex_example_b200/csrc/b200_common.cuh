@@ -12,7 +12,6 @@
 namespace b200 {
 
 constexpr int kVec = 8;            // elements one thread moves per memory instruction group
-constexpr uint32_t kTableMagic = 0x42325442u;
 
 // ------------------------------------------------------------------------------------------
 // Element conversions.  All arithmetic is done in fp32; storage types are widened on load and

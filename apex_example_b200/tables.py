@@ -90,7 +90,7 @@ def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequen
 class TensorTable:
     """A table image resident in device memory plus what the launchers need on the host."""
 
-    __slots__ = ("image", "dev", "n_tiles", "n_tensors", "total_elems", "signature", "keepalive")
+    __slots__ = ("image", "dev", "n_tiles", "n_tensors", "total_elems", "signature")
 
     def __init__(self, columns, groups=None, tile_elems: int | None = None, device=None, signature=None):
         ref = next(c for c in columns if all(t is not None for t in c)) if columns and columns[0] else []
@@ -101,7 +101,6 @@ class TensorTable:
         self.n_tensors = len(ref)
         self.total_elems = sum(t.numel() for t in ref)
         self.signature = signature
-        self.keepalive = None
 
     @property
     def ptr(self) -> int:
