@@ -236,6 +236,16 @@ def main():
     gen = torch.Generator(device=dev).manual_seed(0)
     # gradients live in flat buckets (what apex DDP's flatten produces; at N=1 just contiguous storage)
     use_peer = world > 1 and args.collective == "peer"
+    peer_note = None
+    if use_peer:
+        # the peer-memory path needs every pair of GPUs to be peer-accessible (NVLink / NVSwitch); all ranks
+        # must take the same decision, so the capability is agreed on with a MIN all-reduce
+        ok = all(torch.cuda.can_device_access_peer(local, d) for d in range(torch.cuda.device_count()) if d != local)
+        t = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        if int(t.item()) == 0:
+            use_peer = False
+            peer_note = "peer access not available between all GPUs: fell back to NCCL"
     reducer = None
     if use_peer:
         from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
@@ -444,7 +454,7 @@ def main():
                        "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
                        "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS,
                        "collective": ("peer-memory reduce-scatter + pull-in-optimizer" if use_peer else "nccl all-reduce")
-                       if world > 1 else "none"},
+                       if world > 1 else "none", "collective_note": peer_note},
             "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "train": train,
         }
