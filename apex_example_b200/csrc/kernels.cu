@@ -666,13 +666,14 @@ __device__ __forceinline__ int32_t ld_acquire_sys(const int32_t* p) {
     return v;
 }
 
-// Spin until *p >= want (as seen with acquire/system scope).  Bounded: after ~4e9 cycles (seconds) the
+// Spin until *p >= want (as seen with acquire/system scope).  Bounded: after 6e10 cycles (~30 s; ranks can be
+// seconds apart in a first iteration) the
 // pad's error word is set and the wait gives up, so a missing peer shows up as an error, not a hung GPU.
 __device__ __forceinline__ void wait_at_least(const int32_t* p, int32_t want, int32_t* error) {
     const long long t0 = clock64();
     while (ld_acquire_sys(p) < want) {
         __nanosleep(64);
-        if (clock64() - t0 > 4000000000ll) {
+        if (clock64() - t0 > 60000000000ll) {
             *error = 1;
             break;
         }

@@ -140,6 +140,7 @@ class PeerBuffers:
         lib = _lib.load()
         with torch.cuda.device(self.device):
             torch.cuda.synchronize()
+            timed_out = self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:, 16].any().item())
             for p in self._opened:
                 lib.b200_peer_close(p)
             self._opened = []
@@ -152,6 +153,9 @@ class PeerBuffers:
             for p in self._own.values():
                 lib.b200_peer_free(p)
             self._own = {}
+        if timed_out:
+            raise RuntimeError("libapex_b200: a cross-GPU wait timed out during this run (a rank did not reach a step "
+                               "within ~30 s); results after that point are not valid")
 
 
 class PeerGradientReducer:

@@ -312,7 +312,8 @@ int32_t b200_peer_free(void* dev_ptr);
  * last block publish "my shard of `epoch` is written" plus this rank's overflow bit to every pad;
  * b200_peer_wait_flags (one tiny kernel, next on the stream) waits for all ranks' (b) and ORs the
  * overflow bits into *dev_flag.  `epoch` starts at 1 and grows by one per step on every rank.
- * Waits are bounded (seconds): a rank that never arrives sets pad->error instead of hanging the GPU. */
+ * Waits are bounded (~30 s): a rank that never arrives sets pad->error instead of hanging the GPU;
+ * check pad->error after synchronising (apex_example_b200.parallel.peer.PeerBuffers.check_signals). */
 typedef struct b200_peer_signal_pad {
     int32_t ready[B200_MAX_PEERS];          /* ready[r]: highest epoch rank r has announced */
     int32_t done[B200_MAX_PEERS];           /* done[r]:  (epoch << 1) | overflow bit of rank r */
