@@ -147,3 +147,26 @@ def test_kernel_entry_points_validate_arguments_without_a_gpu():
     with pytest.raises(RuntimeError):
         _lib.check(lib.b200_set_launch_config(0, 256, 3), "set_launch_config")
     assert lib.b200_set_launch_config(0, 256, 2) == 0
+
+
+def test_header_is_plain_c_and_the_library_links_from_c(tmp_path):
+    """The boundary is a C ABI: the header must compile as C99 and a C program must link against the .so."""
+    import shutil
+    import subprocess
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    src = tmp_path / "abi.c"
+    src.write_text(
+        '#include <stdio.h>\n#include "apex_b200.h"\n'
+        "int main(void) {\n"
+        "    int64_t numel[2] = {5000, 17};\n"
+        "    int64_t bytes = b200_table_bytes(2, numel, B200_TILE_ELEMS_DEFAULT);\n"
+        "    if (sizeof(b200_scaler_state) != 48 || sizeof(b200_peer_signal_pad) != 128 || sizeof(b200_table_row) != 64) return 2;\n"
+        "    return (b200_abi_version() == B200_ABI_VERSION && bytes == 64 + 2 * 64 + 3 * 8) ? 0 : 1;\n"
+        "}\n")
+    exe = tmp_path / "abi"
+    libdir = os.path.dirname(_lib.SO_PATH)
+    subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
+                    "-L", libdir, "-l:" + os.path.basename(_lib.SO_PATH), "-Wl,-rpath," + libdir], check=True)
+    assert subprocess.run([str(exe)]).returncode == 0
