@@ -3,8 +3,14 @@ and the patched optimizers)."""
 from __future__ import annotations
 
 
+import weakref
+
+
 class AmpState:
     def __init__(self):
+        # live apex.parallel.DistributedDataParallel wrappers (the patched zero_grad asks them to clear
+        # gradients that are views of their buckets with one memset per bucket); survives reset()
+        self.ddp_wrappers = weakref.WeakSet()
         self.reset()
 
     def reset(self):

@@ -39,6 +39,7 @@ class LossScaler:
         self._seen_skips = 0
         self._loss_id = 0
         self._tables = {}
+        self._updates_since_step = 0    # update_scale() calls no optimizer step has consumed yet
 
     # ---- device record -----------------------------------------------------------------------
     def _ensure_state(self, device=None):
@@ -119,7 +120,11 @@ class LossScaler:
         ``should_skip`` when the caller needs it on the host (generic optimizers — one sync, as in
         apex), else None (fused optimizers skip on the device)."""
         self._ensure_state()
-        ops.scaler_update(self._state, self.dynamic, self._scale_seq_len, self._scale_factor,
+        # A second update before any step() (gradient accumulation without delay_unscale) must not
+        # forget an overflow the first one saw: apex's patched skip_step stays until step() runs.
+        mode = (ops.SCALER_DYNAMIC if self.dynamic else 0) | (ops.SCALER_KEEP_SKIP if self._updates_since_step else 0)
+        self._updates_since_step += 1
+        ops.scaler_update(self._state, mode, self._scale_seq_len, self._scale_factor,
                           float(self._min_loss_scale or 0.0), float(self._max_loss_scale), self._mirror)
         if need_host_decision and self.dynamic:
             self._refresh(sync=True, quiet=True)        # the patched skip_step prints the message (as apex)
@@ -127,6 +132,10 @@ class LossScaler:
         if not self.dynamic:
             return False
         return None
+
+    def note_step(self):
+        """An optimizer step has been issued: the next update_scale starts a fresh decision."""
+        self._updates_since_step = 0
 
     def _refresh(self, sync: bool, quiet: bool = False):
         """Fold what the device has mirrored so far into the host copy; prints apex's overflow line

@@ -53,6 +53,13 @@ static int sm_count() {
     return cached[dev];
 }
 
+// index of the current device into the per-device caches below (occupancy depends on the device)
+static int current_device_slot() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    return dev;
+}
+
 // Persistent grids must not exceed what is resident at once (a second wave would run at a
 // fraction of the occupancy): CTAs/SM comes from the occupancy calculator, per kernel and device.
 template <class Kernel>
@@ -106,9 +113,7 @@ static int launch_one(const char* name, const void* dev_table, int64_t n_tiles, 
                       cudaStream_t st, unsigned max_grid) {
     auto kernel = tile_kernel<Op, kThreads, kUnroll>;
     static int occ[64];                       // per device; one static per instantiation
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64) dev = 0;
+    const int dev = current_device_slot();
     if (occ[dev] == 0) {
         occ[dev] = resident_ctas_per_sm(kernel, kThreads);
         if constexpr (MaxCtasOf<Op>::value > 0)
@@ -674,10 +679,17 @@ __device__ __forceinline__ void wait_at_least(const int32_t* p, int32_t want, in
     while (ld_acquire_sys(p) < want) {
         __nanosleep(64);
         if (clock64() - t0 > 60000000000ll) {
-            *error = 1;
+            *reinterpret_cast<volatile int32_t*>(error) = 1;
+            __threadfence();
             break;
         }
     }
+}
+
+// A wait that gave up poisons the step: the caller raises the overflow flag, so the optimizer kernel writes
+// nothing (the same all-or-nothing path as a gradient overflow) instead of updating from incomplete sums.
+__device__ __forceinline__ bool wait_failed(const int32_t* error) {
+    return *reinterpret_cast<const volatile int32_t*>(error) != 0;
 }
 
 template <int DT, int kThreads, int kWorld>
@@ -696,6 +708,10 @@ peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __res
         if (blockIdx.x == 0 && threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->ready[sync.rank], sync.epoch);
         if (threadIdx.x < sync.world) wait_at_least(&mine->ready[threadIdx.x], sync.epoch, &mine->error);
         __syncthreads();
+        if (wait_failed(&mine->error)) {      // a rank never arrived: read nobody's buffer, poison the step
+            bad = true;
+            end = begin;
+        }
     }
     const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
@@ -789,7 +805,7 @@ __global__ void peer_wait_flags_kernel(const __grid_constant__ PeerSync sync, in
     __syncthreads();
     if (threadIdx.x < sync.world) {
         wait_at_least(&mine->done[threadIdx.x], sync.epoch << 1, &mine->error);
-        if (ld_acquire_sys(&mine->done[threadIdx.x]) & 1) atomicOr(&s_any, 1);
+        if ((ld_acquire_sys(&mine->done[threadIdx.x]) & 1) || wait_failed(&mine->error)) atomicOr(&s_any, 1);
     }
     __syncthreads();
     if (threadIdx.x == 0 && s_any && flag) *flag = 1;
@@ -815,7 +831,7 @@ peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __
         __syncthreads();
         if (threadIdx.x < sync.world) {
             wait_at_least(&mine->done[threadIdx.x], sync.epoch << 1, &mine->error);
-            if (ld_acquire_sys(&mine->done[threadIdx.x]) & 1) atomicOr(&s_any, 1);
+            if ((ld_acquire_sys(&mine->done[threadIdx.x]) & 1) || wait_failed(&mine->error)) atomicOr(&s_any, 1);
         }
         __syncthreads();
         if (blockIdx.x == 0 && threadIdx.x == 0 && s_any && flag) *flag = 1;
@@ -871,13 +887,18 @@ __global__ void scaler_init_kernel(b200_scaler_state* s, float init_scale) {
     s->reserved[0] = s->reserved[1] = s->reserved[2] = 0;
 }
 
-__global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scale_window, float scale_factor,
+__global__ void scaler_update_kernel(b200_scaler_state* s, int mode, int scale_window, float scale_factor,
                                      float min_scale, float max_scale, b200_scaler_state* mirror) {
     b200_scaler_state st = *s;
+    const int dynamic = mode & B200_SCALER_DYNAMIC;
     const int flag = st.overflow_acc != 0;
     st.inv_scale = __fdiv_rn(1.0f, st.loss_scale);
     st.had_overflow = flag;
-    st.found_inf = (dynamic && flag) ? 1 : 0;
+    // B200_SCALER_KEEP_SKIP: no optimizer step has consumed the previous decision yet (a second backward of a
+    // gradient-accumulation cycle), so an earlier overflow must keep the pending step skipped — apex's patched
+    // skip_step stays in place until step() is called
+    const int carried = (mode & B200_SCALER_KEEP_SKIP) ? st.found_inf : 0;
+    st.found_inf = ((dynamic && flag) || carried) ? 1 : 0;
     if (dynamic) {
         if (flag) {
             float ns = __fdiv_rn(st.loss_scale, 2.0f);
@@ -896,7 +917,7 @@ __global__ void scaler_update_kernel(b200_scaler_state* s, int dynamic, int scal
     }
     st.overflow_acc = 0;
     st.seq += 1;
-    st.skipped_total += st.found_inf;
+    st.skipped_total += (st.found_inf && !carried) ? 1 : 0;
     st.inv_loss_scale = __fdiv_rn(1.0f, st.loss_scale);
     *s = st;
     if (mirror) {
@@ -991,7 +1012,8 @@ int32_t b200_scaler_init(b200_scaler_state* dev_state, float init_scale, void* s
 int32_t b200_scaler_update(b200_scaler_state* dev_state, int32_t dynamic, int32_t scale_window, float scale_factor,
                            float min_scale, float max_scale, b200_scaler_state* mirror, void* stream) {
     if (!dev_state) return set_error(B200_EINVAL, "scaler_update: dev_state is NULL");
-    if (dynamic && scale_window <= 0) return set_error(B200_EINVAL, "scaler_update: scale_window must be > 0");
+    if (dynamic & ~(B200_SCALER_DYNAMIC | B200_SCALER_KEEP_SKIP)) return set_error(B200_EINVAL, "scaler_update: unknown mode bits");
+    if ((dynamic & B200_SCALER_DYNAMIC) && scale_window <= 0) return set_error(B200_EINVAL, "scaler_update: scale_window must be > 0");
     scaler_update_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(dev_state, dynamic, scale_window, scale_factor,
                                                                           min_scale, max_scale, mirror);
     return after_launch("scaler_update");
@@ -1251,7 +1273,8 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
 #define B200_LAUNCH_REDUCE(W_)                                                                                    \
     {                                                                                                             \
         auto kernel = peer_reduce_kernel<DT, kThreads, W_>;                                                       \
-        static int occ = 0;                                                                                       \
+        static int occ_dev[64];                                                                                   \
+        int& occ = occ_dev[current_device_slot()];                                                                \
         if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);                                               \
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                                  \
         if (blocks > want) blocks = want;                                                                         \
@@ -1289,7 +1312,12 @@ int32_t b200_peer_gather(const void* const* peer_reduced, int32_t world, void* l
     if (sb.b[0] != 0) return set_error(B200_EINVAL, "peer_gather: bounds[0] must be 0");
     for (int r = 0; r < world; r++) {
         if (!pb.p[r]) return set_error(B200_EINVAL, "peer_gather: peer buffer %d is NULL", r);
-        if (sb.b[r] > sb.b[r + 1] || (r > 0 && sb.b[r] % kVec)) return set_error(B200_EINVAL, "peer_gather: bounds must be non-decreasing multiples of 8");
+        if (sb.b[r] > sb.b[r + 1]) return set_error(B200_EINVAL, "peer_gather: bounds must be non-decreasing");
+        // a shard boundary inside the buffer must not cut an 8-element group; boundaries equal to the total
+        // (empty trailing shards of a small bucket) are fine
+        if (r > 0 && sb.b[r] % kVec && sb.b[r] != sb.b[world])
+            return set_error(B200_EINVAL, "peer_gather: bounds[%d] = %lld is inside the buffer and not a multiple of 8", r,
+                             static_cast<long long>(sb.b[r]));
     }
     constexpr int kThreads = 256;
     const int64_t groups = sb.b[world] / kVec + 1;
@@ -1297,7 +1325,8 @@ int32_t b200_peer_gather(const void* const* peer_reduced, int32_t world, void* l
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     B200_DISPATCH_DT(dtype, DT, {
         auto kernel = peer_gather_kernel<DT, kThreads>;
-        static int occ = 0;
+        static int occ_dev[64];
+        int& occ = occ_dev[current_device_slot()];
         if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;
         if (blocks > want) blocks = want;
@@ -1353,6 +1382,14 @@ int32_t b200_fused_adam_noalloc(int32_t n_tensors, const void* const* ptrs, cons
                          "fused_adam_noalloc: this tensor list needs a %lld-byte table but the built-in static table "
                          "holds %d bytes; use b200_fused_adam with a caller-allocated table instead",
                          static_cast<long long>(need), B200_NOALLOC_TABLE_BYTES);
+    // every column the kernel dereferences must be there (b200_table_build itself accepts NULL as
+    // "column absent", which the Adam kernel has no use for)
+    const int n_cols = copy_dtype == B200_NONE ? 4 : 5;
+    for (int d = 0; d < n_cols; d++)
+        for (int t = 0; t < n_tensors; t++)
+            if (numel[t] > 0 && ptrs[static_cast<size_t>(d) * n_tensors + t] == nullptr)
+                return set_error(B200_EINVAL, "fused_adam_noalloc: ptrs[%d * n_tensors + %d] (column %d of tensor %d) is NULL",
+                                 d, t, d, t);
     const int depth = copy_dtype == B200_NONE ? 4 : 5;
     const int g_sz = grad_dtype == B200_F32 ? 4 : 2, s_sz = state_dtype == B200_F32 ? 4 : 2;
     const int32_t elem_size[5] = {g_sz, s_sz, s_sz, s_sz, copy_dtype == B200_F32 ? 4 : 2};
@@ -1364,9 +1401,9 @@ int32_t b200_fused_adam_noalloc(int32_t n_tensors, const void* const* ptrs, cons
     const int64_t n_tiles = b200_table_build(g_noalloc_host_image, B200_NOALLOC_TABLE_BYTES, n_tensors, depth, ptrs, elem_size,
                                              numel, nullptr, B200_TILE_ELEMS_DEFAULT);
     if (n_tiles < 0) return static_cast<int32_t>(n_tiles);
-    // Pageable source: the runtime has consumed the host image by the time this returns, so the
-    // static host buffer can be reused by the next call; the device copy is ordered on `stream`
-    // ahead of the kernel below.
+    // The source is ordinary (pageable) host memory: in a normal, non-captured stream the runtime
+    // stages it before cudaMemcpyAsync returns, so the next call (serialised by the mutex above) may
+    // overwrite the static host buffer; the device-side copy is ordered on `stream` ahead of the kernel.
     cudaError_t e = cudaMemcpyAsync(dev_table, g_noalloc_host_image, static_cast<size_t>(need), cudaMemcpyHostToDevice,
                                     static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "fused_adam_noalloc: table upload");
@@ -1386,7 +1423,8 @@ int32_t b200_bucket_epilogue(void* dev_bucket, int64_t numel, int32_t dtype, flo
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     B200_DISPATCH_DT(dtype, DT, {
         auto kernel = bucket_epilogue_kernel<DT, kThreads>;
-        static int occ = 0;
+        static int occ_dev[64];
+        int& occ = occ_dev[current_device_slot()];
         if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;      // one resident wave, grid-stride inside
         if (blocks > want) blocks = want;

@@ -165,7 +165,10 @@ def scaler_init(state: torch.Tensor, init_scale: float):
     _lib.check(_lib.load().b200_scaler_init(state.data_ptr(), init_scale, _stream()), "scaler_init")
 
 
-def scaler_update(state: torch.Tensor, dynamic: bool, scale_window: int, scale_factor: float, min_scale: float,
+SCALER_DYNAMIC, SCALER_KEEP_SKIP = 1, 2      # b200_scaler_update mode bits
+
+
+def scaler_update(state: torch.Tensor, dynamic, scale_window: int, scale_factor: float, min_scale: float,
                   max_scale: float, mirror: torch.Tensor | None = None):
     _lib.check(_lib.load().b200_scaler_update(state.data_ptr(), int(dynamic), scale_window, scale_factor, min_scale,
                                               max_scale, _addr(mirror), _stream()), "scaler_update")

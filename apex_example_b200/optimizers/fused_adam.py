@@ -44,7 +44,7 @@ class FusedAdam(FusedOptimizerBase):
             g = self.param_groups[gi]
             beta1, beta2 = g["betas"]
             hyper.append(ops.AdamGroup(float(g["lr"]), float(beta1), float(beta2), float(g["eps"]),
-                                       float(g["weight_decay"]), int(steps[gi]), 1 if g["bias_correction"] else 0,
+                                       float(g["weight_decay"]), int(steps[gi]), 1 if g.get("bias_correction", True) else 0,
                                        self.adam_w_mode))
         inv_scale, dev_inv, dev_found = scale_args
         ops.fused_adam(table, gdt, sdt, cdt, hyper, inv_scale=inv_scale, dev_inv_scale=dev_inv,

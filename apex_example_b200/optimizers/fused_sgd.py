@@ -41,6 +41,17 @@ class FusedSGD(FusedOptimizerBase):
         for group in self.param_groups:
             group.setdefault("nesterov", False)
 
+    def load_state_dict(self, state_dict):
+        """Checkpoints written by torch.optim.SGD or apex's FusedSGD carry ``momentum_buffer`` in the
+        state but no step count in the param groups.  apex keys ``first_run`` on whether the buffers
+        exist; here it is keyed on the group's step, so a group that arrives with buffers and without
+        a step is marked as having stepped (otherwise the first step would overwrite the loaded
+        momentum with the gradient)."""
+        super().load_state_dict(state_dict)
+        for group in self.param_groups:
+            if "step" not in group and any("momentum_buffer" in self.state.get(p, {}) for p in group["params"]):
+                group["step"] = 1
+
     def _state_columns(self, p, group):
         if group["momentum"] == 0:
             return (None,)

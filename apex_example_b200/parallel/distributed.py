@@ -20,6 +20,8 @@ apex does.
 """
 from __future__ import annotations
 
+import operator
+
 import torch
 import torch.distributed as dist
 from torch.autograd import Variable
@@ -29,6 +31,7 @@ from .. import ops
 from ..tables import TensorTable
 
 _SUPPORTED = (torch.float16, torch.bfloat16, torch.float32)
+_GRAD_OF = operator.attrgetter("grad")
 
 
 def split_by_dtype(tensors):
@@ -177,9 +180,31 @@ class DistributedDataParallel(Module):
 
         self._build_buckets(params)
         self._sync_bucket_structure()
+        self._next = 0
         if self.world_size > 1 or not self._on_cuda:
             for p in params:
                 p.register_post_accumulate_grad_hook(self._hook)
+        try:
+            from ..amp._amp_state import _amp_state
+            _amp_state.ddp_wrappers.add(self)
+        except Exception:
+            pass
+
+    def zero_bucket_grads(self, params):
+        """amp's patched ``zero_grad`` (a9): every bucket whose parameters' gradients currently ARE its
+        views is cleared with one memset of the flat buffer; returns the parameters not covered."""
+        if not self._on_cuda:
+            return params
+        handled = set()
+        for b in self.buckets:
+            if b.flat is None or not b.views:
+                continue
+            if all(map(operator.is_, map(_GRAD_OF, b.params), b.views)):
+                b.flat.zero_()
+                handled.update(map(id, b.params))
+        if not handled:
+            return params
+        return [p for p in params if id(p) not in handled]
 
     def _resync_amp_masters(self):
         """amp.initialize runs BEFORE this wrapper (reference :121 then :122), so at O2 the fp32
@@ -320,6 +345,7 @@ class DistributedDataParallel(Module):
     def forward(self, *inputs, **kwargs):
         self._armed = self._enabled
         self._callback_queued = False
+        self._next = 0
         for b in self.buckets:
             b.ready = 0
             b.launched = False
@@ -334,8 +360,17 @@ class DistributedDataParallel(Module):
             self._callback_queued = True
         b = self._bucket_of[id(param)]
         b.ready += 1
-        if b.ready == len(b.params) and not self.delay_allreduce and not b.launched:
-            self._reduce_bucket(b)
+        if b.ready == len(b.params) and not self.delay_allreduce:
+            # Collectives must be issued in the same order on every rank, whatever order the gradients
+            # arrive in (a data-dependent graph can differ between ranks): buckets go out in index order,
+            # a bucket that is ready early waits for its predecessors (apex: next_bucket).
+            while self._next < len(self.buckets):
+                nb = self.buckets[self._next]
+                if not nb.launched:
+                    if nb.ready != len(nb.params):
+                        break
+                    self._reduce_bucket(nb)
+                self._next += 1
 
     def _overflow_flag(self):
         """Device flag of amp's loss scaler (if amp is active): the epilogue doubles as the overflow check."""

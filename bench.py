@@ -1,30 +1,37 @@
 #!/usr/bin/env python
 """bench.py — the mixed-precision step hot path on B200 (BASELINE.json metric
-"fused optimizer step HBM GB/s").
+"fused optimizer step HBM GB/s; train samples/sec at 1/2/4/8 B200 (amp O2)").
 
     python bench.py --gpus 1 --steps 50 --warmup 5
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
     python bench.py --impl reference            # the CPU restatement on the host cores
 
-Workload (BASELINE.json configs[1]): the 148-tensor / 124,439,808-element
-GPT-2-small parameter list at amp O2 — fp16 gradients carrying the loss scale, fp32 master / m / v,
-fp16 model copy.  One *step* = everything between backward and the next forward:
+Headline workload (BASELINE.json configs[1]): the 148-tensor /
+124,439,808-element GPT-2-small parameter list at amp O2 — fp16 gradients carrying the loss scale,
+fp32 master / m / v, fp16 model copy.  One *step* = everything between backward and the next forward:
   N = 1 : overflow check over the gradients -> loss-scaler update -> fused unscale+AdamW+copy
   N > 1 : gradient mean across ranks -> loss-scaler update -> fused unscale+AdamW+copy
           (weak scaling: every rank owns a full replica).  The mean runs over NVLink peer memory by
           default (--collective peer: one reduce-scatter+mean+check kernel, then the optimizer
           kernel pulls each tile's reduced gradient from its owner); --collective nccl selects
           ncclAllReduce per 10M-element bucket + the epilogue kernel.
-`value` = 28 B/param x params x ranks / step time, inputs resident in HBM.  `e2e` = the same step
-through the public API (apex.amp + apex.optimizers.FusedAdam) with the step's gradients copied in
-from pinned host memory and the scaler state read back, every step.  `train` = GPT-2 medium
-samples/s through amp O2 + FusedAdam + apex DistributedDataParallel (the metric's second half).
+`value` = 28 B/param x params x ranks / step time, inputs resident in HBM.  Before anything is timed
+the same buffers run a PARITY block: one step and one injected-overflow step are compared bit for bit
+with oracle/ on every rank (key `parity`; a mismatch ends the run with a non-zero exit code).
+`e2e` = the same step through the public API (apex.amp + apex.optimizers.FusedAdam, at N > 1 with
+apex.parallel.Reducer for the gradient mean) with the step's gradients copied in from pinned host
+memory and the scaler state read back, every step.  Further keys, one per BASELINE.json config:
+`train` (GPT-2 medium O2 + FusedAdam + apex DDP samples/s, with torch's DDP as the incumbent),
+`train_resnet50` (ResNet-50 O2 + FusedSGD + apex DDP images/s), `config5` (1.3 B-parameter
+many-small-tensor list at O3 with injected inf/NaN on one random rank), `allreduce` (NCCL bus GB/s on
+GPT-2 medium's 709.6 MB for several message sizes).
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
+import random
 import statistics
 import subprocess
 import sys
@@ -41,6 +48,7 @@ BYTES_PER_PARAM = 28            # 2 (fp16 g) + 12 (p,m,v in) + 12 (p,m,v out) + 
 LOSS_SCALE = 65536.0
 HYPER = dict(lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01)
 BUCKET_ELEMS = 10_000_000       # apex DistributedDataParallel message_size default
+METRIC = "fused optimizer step HBM GB/s"
 
 
 def workload_sizes(name):
@@ -50,6 +58,19 @@ def workload_sizes(name):
     if name == "gpt2_medium":
         return GPT2_MEDIUM, "GPT-2-medium-shaped list: 292 tensors, 354,823,168 params, amp O2"
     raise SystemExit(f"unknown workload {name}")
+
+
+def config_dict(desc, world, collective="peer", note=None):
+    """The `config` object both arms print (the driver compares them)."""
+    if world == 1:
+        coll = "none"
+    elif collective == "peer":
+        coll = "peer-memory reduce-scatter + pull-in-optimizer"
+    else:
+        coll = "nccl all-reduce"
+    return {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
+            "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
+            "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS, "collective": coll, "collective_note": note}
 
 
 def peaks():
@@ -158,28 +179,147 @@ def cpu_model():
 
 
 def reference_arm(args, sizes, desc):
+    """The reference's hot path lives in NVIDIA/apex (CUDA only, not vendored, not installable offline),
+    so this arm times its CPU restatement, oracle/amp_step_oracle.c, with OpenMP on every host core, on the
+    same workload, step count and warm-up as the B200 arm (each step is the whole 124 M-parameter list:
+    ~40 ms, so even the default 1000 steps end within a minute)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     n = sum(sizes)
-    steps = max(1, min(args.steps, 20))
-    warm = max(1, min(args.warmup, 2))
-    times = run_cpu(sizes, steps, warm)
+    steps = max(1, min(args.steps, 2000))
+    times = run_cpu(sizes, steps, args.warmup)
     t = sum(times) / len(times)
     gbs = BYTES_PER_PARAM * n / t / 1e9
     cores = omp_threads()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     line = {
-        "impl": "reference", "metric": "fused optimizer step HBM GB/s", "value": gbs, "unit": "GB/s",
-        "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "note": "reference's hot path lives in NVIDIA/apex (CUDA only, not installed); "
-                   "this arm times its CPU restatement oracle/amp_step_oracle.c on the host cores"},
+        "config": config_dict(desc, world, args.collective),
+        "reference_note": "reference's hot path lives in NVIDIA/apex (CUDA only, not installed); this arm times its CPU "
+                          "restatement oracle/amp_step_oracle.c on the host cores (one replica, whatever N is)",
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
                          "sample": f"full list, {steps} steps of check + unscale+AdamW+copy (OpenMP, {cores} threads)"},
         "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------
+# parity block: the timed buffers, one clean step and one overflow step, against oracle/
+# ---------------------------------------------------------------------------------------------------
+def _ulp_fp16(a, b):
+    """max distance in fp16 ulps between two finite fp16 tensors (sign-magnitude to ordered ints)."""
+    def key(t):
+        i = t.view(torch.int16).to(torch.int32)
+        return torch.where(i < 0, -(i & 0x7fff), i)
+    return int((key(a) - key(b)).abs().max()) if a.numel() else 0
+
+
+def parity_block(ctx, sabotage=False):
+    """Runs on every rank, untimed, before the warm-up.  Clean step: the gradient mean this rank owns (peer
+    path: its `reduced` shard; NCCL path: the whole all-reduced buffer) and p / m / v / fp16 copy after the
+    fused step are compared with oracle.peer_reduce + oracle.adam_list computed from EVERY rank's inputs.
+    Overflow step: one inf on the LAST rank only -> every rank must skip (found_inf = 1, state untouched,
+    loss scale halved; SURVEY.md §3.4, reference skip path test_apex_distributed_spawn.py:160-164)."""
+    import torch.distributed as dist
+    import oracle
+    from apex_example_b200 import ops
+    world, rank, dev, n, sizes = ctx["world"], ctx["rank"], ctx["dev"], ctx["n"], ctx["sizes"]
+    gflat, state, reducer = ctx["gflat"], ctx["state"], ctx["reducer"]
+    cols = ctx["cols"]                                  # p, m, v, copy (device lists)
+    res = {"world": world, "path": ctx["path"], "params": n}
+
+    gen = torch.Generator(device=dev).manual_seed(4242 + rank)
+    gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
+    if world > 1:
+        parts = [torch.empty_like(gflat) for _ in range(world)]
+        dist.all_gather(parts, gflat)
+        host_all = [t.cpu() for t in parts]
+        del parts
+    else:
+        host_all = [gflat.cpu()]
+    before = [[t.cpu() for t in col] for col in cols]
+    torch.cuda.synchronize()
+
+    factor = 1.0 / world
+    ctx["step"](factor_override=(2.0 * factor if sabotage else None))
+    torch.cuda.synchronize()
+    found = int(state.cpu()[ops.IDX_FOUND_INF])
+
+    # oracle: mean in rank order (fp32 accumulate, round to fp16, x 1/world, round), then the fused step
+    want_mean = torch.zeros(n, dtype=torch.float16)
+    wflag = oracle.peer_reduce(host_all, want_mean, 0, n, factor) if world > 1 else oracle.check(host_all[0])
+    if world == 1:
+        want_mean = host_all[0]
+    if ctx["path"] == "peer":
+        b0, b1 = ctx["bounds"][rank], ctx["bounds"][rank + 1]
+        got = reducer.buf.local["reduced"][b0:b1].cpu()
+        res["mean_bit_exact"] = bool(torch.equal(got.view(torch.int16), want_mean[b0:b1].view(torch.int16)))
+        step_grad = want_mean
+    elif world > 1:
+        got = gflat.cpu()
+        exact = bool(torch.equal(got.view(torch.int16), want_mean.view(torch.int16)))
+        res["mean_bit_exact"] = exact
+        res["mean_max_ulp_vs_oracle"] = 0 if exact else _ulp_fp16(got, want_mean)
+        # NCCL does not specify its summation order: the mean must agree with the rank-ordered fp32 sum within
+        # a few fp16 ulps and be IDENTICAL on every rank; the optimizer is then checked on the mean NCCL produced
+        digest = torch.tensor([int(got.view(torch.int16).to(torch.int64).sum())], device=dev)
+        lo, hi = digest.clone(), digest.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        res["mean_identical_on_all_ranks"] = bool(int(lo) == int(hi))
+        res["mean_ok"] = res["mean_identical_on_all_ranks"] and res["mean_max_ulp_vs_oracle"] <= world
+        step_grad = got
+    else:
+        res["mean_bit_exact"] = True
+        step_grad = want_mean
+    assert wflag == 0 and found == 0, "parity block: finite gradients flagged as overflow"
+    hg = list(torch.split(step_grad, sizes))
+    hp, hm, hv, hc = before
+    oracle.adam_list(hg, hp, hm, hv, hc, inv_scale=1.0 / LOSS_SCALE, step=ctx["step_no"][0], adam_w_mode=True,
+                     check_overflow=False, **HYPER)
+    ok = True
+    for col, want in zip(cols, (hp, hm, hv, hc)):
+        for d, h in zip(col, want):
+            it = torch.int32 if h.element_size() == 4 else torch.int16
+            if not torch.equal(d.cpu().view(it), h.view(it)):
+                ok = False
+                break
+    res["state_bit_exact"] = ok
+    del host_all, before, hg
+
+    # overflow on the last rank only
+    snap = [[t.clone() for t in col] for col in cols]
+    if rank == world - 1:
+        gflat[n - 7] = float("inf")
+    ctx["step"]()
+    torch.cuda.synchronize()
+    st = state.cpu()
+    skipped = int(st[ops.IDX_FOUND_INF]) == 1
+    untouched = all(torch.equal(a, b) for ca, cb in zip(cols, snap) for a, b in zip(ca, cb))
+    halved = float(st.view(torch.float32)[ops.IDX_LOSS_SCALE]) == LOSS_SCALE / 2
+    res["skip_agreed"] = bool(skipped and untouched and halved)
+    del snap
+    mean_good = res["mean_ok"] if ctx["path"] == "nccl" else res["mean_bit_exact"]
+    good = res["state_bit_exact"] and res["skip_agreed"] and mean_good
+    if world > 1:
+        t = torch.tensor([1 if good else 0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        res["all_ranks_ok"] = bool(int(t.item()))
+        for k in ("mean_bit_exact", "state_bit_exact", "skip_agreed"):      # AND over ranks
+            t = torch.tensor([1 if res.get(k, True) else 0], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            res[k] = bool(int(t.item()))
+    else:
+        res["all_ranks_ok"] = bool(good)
+    # back to a clean slate for the timed run
+    ops.scaler_init(state, LOSS_SCALE)
+    torch.cuda.synchronize()
+    return res
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -194,11 +334,23 @@ def main():
     ap.add_argument("--workload", default="gpt2_small", choices=["gpt2_small", "gpt2_medium"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", dest="parity", action="store_false", help="skip the untimed parity block")
+    ap.add_argument("--parity-sabotage", action="store_true",
+                    help="self-test of the parity block: run its clean step with a wrong averaging factor (must fail)")
     ap.add_argument("--no-train", dest="train", action="store_false",
-                    help="skip the GPT-2 medium training measurement (amp O2 + FusedAdam + apex DDP) reported under 'train'")
+                    help="skip the training measurements (GPT-2 medium under 'train', ResNet-50 under 'train_resnet50')")
+    ap.add_argument("--no-resnet", dest="resnet", action="store_false")
+    ap.add_argument("--no-config5", dest="config5", action="store_false",
+                    help="skip BASELINE configs[4] (1.3 B-parameter many-small-tensor list at O3 with injected overflows)")
+    ap.add_argument("--config5-total", type=int, default=1_300_000_000)
+    ap.add_argument("--config5-steps", type=int, default=30)
+    ap.add_argument("--no-incumbent", dest="incumbent", action="store_false",
+                    help="N>1: skip the torch.nn.parallel.DistributedDataParallel comparison run")
     ap.add_argument("--train-batch", type=int, default=4, help="per-GPU micro-batch of 1024-token sequences")
+    ap.add_argument("--resnet-batch", type=int, default=256, help="per-GPU batch of 224x224 images")
     ap.add_argument("--ddp-backend", default="nccl", help="apex DDP bucket all-reduce for the training measurement: "
                     "nccl | peer | nccl,peer (measure both; the first is reported under 'train')")
+    ap.add_argument("--message-size", type=int, default=0, help="apex DDP message_size for the training runs (0 = apex default)")
     ap.add_argument("--threads", type=int, default=0, help="tuning: threads per CTA (256|512)")
     ap.add_argument("--unroll", type=int, default=0, help="tuning: 8-element groups in flight per thread (1|2)")
     ap.add_argument("--ctas-per-sm", type=int, default=0)
@@ -246,7 +398,7 @@ def main():
         if int(t.item()) == 0:
             use_peer = False
             peer_note = "peer access not available between all GPUs: fell back to NCCL"
-    reducer = None
+    reducer, bounds = None, None
     if use_peer:
         from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
         from apex_example_b200.tables import tile_aligned_shards
@@ -258,9 +410,12 @@ def main():
         bounds, first_tiles = tile_aligned_shards(offs, sizes, n, world, return_first_tiles=True)
         reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles, barrier=args.peer_barrier)
         gflat = pbufs.local["grads"]
-        gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
     else:
-        gflat = (torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half()
+        gflat = torch.empty(n, dtype=torch.float16, device=dev)
+
+    def bench_gradients():
+        gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
+
     grads = list(torch.split(gflat, sizes))
     copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
     p = [c.float() for c in copy]
@@ -280,13 +435,17 @@ def main():
     inv_ref, found_ref, acc_ref = fstate[ops.IDX_INV_SCALE:], state[ops.IDX_FOUND_INF:], state[ops.IDX_OVERFLOW_ACC:]
     step_no = [0]
 
-    def step(ev=None):
+    def step(ev=None, factor_override=None):
         step_no[0] += 1
         if use_peer:
-            # barrier -> ONE kernel: reduce-scatter + mean + overflow check over NVLink -> barrier + flag OR
+            # ONE kernel: (hand-shake) reduce-scatter + mean + overflow check over NVLink -> flag OR
             if ev is not None:
                 ev[2].record()
+            if factor_override is not None:
+                keep, reducer.factor = reducer.factor, factor_override
             reducer.reduce(acc_ref)
+            if factor_override is not None:
+                reducer.factor = keep
             if ev is not None:
                 ev[3].record()
         elif world > 1:
@@ -296,7 +455,7 @@ def main():
                 ev[2].record()
             for b in buckets:
                 dist.all_reduce(b)
-                ops.bucket_epilogue(b, 1.0 / world, acc_ref)
+                ops.bucket_epilogue(b, (1.0 / world) if factor_override is None else factor_override, acc_ref)
             if ev is not None:
                 ev[3].record()
         else:
@@ -319,6 +478,25 @@ def main():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    # ---- parity (untimed) ----
+    parity = None
+    if args.parity:
+        ctx = dict(world=world, rank=rank, dev=dev, n=n, sizes=sizes, gflat=gflat, state=state, reducer=reducer,
+                   cols=[p, m, v, copy], path="peer" if use_peer else ("nccl" if world > 1 else "single"),
+                   bounds=bounds, step=step, step_no=step_no)
+        parity = parity_block(ctx, sabotage=args.parity_sabotage)
+        step_no[0] -= 1                               # the skipped step did not count
+        if not parity["all_ranks_ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "error": "parity block failed", "parity": parity}), flush=True)
+            if use_peer:
+                del reducer
+                pbufs.close()
+            if world > 1:
+                dist.destroy_process_group()
+            raise SystemExit(3)
+    bench_gradients()
 
     for _ in range(args.warmup):
         step()
@@ -364,6 +542,8 @@ def main():
     value = BYTES_PER_PARAM * n * world / (ms_per_step * 1e-3) / 1e9
     skipped = int(state.cpu()[ops.IDX_FOUND_INF])
     assert skipped == 0, "synthetic gradients are finite: the step must not have been skipped"
+    if use_peer:
+        pbufs.check_signals()
 
     # ---- roofline of the dominant kernel (fused step) ----
     peak, peak_src = peaks()
@@ -381,7 +561,7 @@ def main():
         # gradient mean: every rank receives (N-1)/N of the buffer over NVLink in the reduce phase and
         # again while the optimizer pulls the reduced shards; bus bandwidth as NCCL defines it
         nbytes = n * 2
-        roof["gradient_mean"] = {"path": "peer reduce-scatter kernel + 2 flag/barrier all-reduces" if use_peer
+        roof["gradient_mean"] = {"path": "peer reduce-scatter kernel (in-kernel hand-shake) + flag wait" if use_peer
                                  else "ncclAllReduce per 10M-element bucket + epilogue kernel",
                                  "ms_avg": cm, "bytes": nbytes,
                                  "busbw_gbs": nbytes / (cm * 1e-3) * 2 * (world - 1) / world / 1e9 if not use_peer
@@ -396,44 +576,52 @@ def main():
         except Exception:
             pass
 
-    # ---- allreduce bus bandwidth (N > 1) ----
     extra = {}
+    del table, check_table, grads, p, m, v, copy, buckets
+    if use_peer:
+        del reducer, gflat
+        pbufs.close()
+    else:
+        del gflat
+    torch.cuda.empty_cache()
+
+    # ---- NCCL all-reduce bus bandwidth on config 4's gradient bytes (N > 1) ----
     if world > 1:
-        barrier()
-        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record()
-        reps = 10
-        for _ in range(reps):
-            for b in buckets:
-                dist.all_reduce(b)
-        a1.record()
-        barrier()
-        ar_ms = a0.elapsed_time(a1) / reps
-        t = torch.tensor([ar_ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ar_ms = float(t.item())
-        nbytes = gflat.numel() * 2
-        extra["allreduce"] = {"bytes_per_step": nbytes, "buckets": len(buckets), "ms": ar_ms,
-                              "busbw_gbs": nbytes / (ar_ms * 1e-3) * 2 * (world - 1) / world / 1e9,
-                              "nvlink_peak_gbs_per_dir": 900.0}
+        extra["allreduce"] = run_allreduce_sweep(dev, world, barrier)
 
     # ---- e2e through the public API with host buffers ----
     e2e = None
     if not args.no_e2e:
-        del table, check_table
         e2e = run_e2e(sizes, dev, world, max(3, min(args.steps, 20)), args.warmup, barrier)
 
-    # ---- the second half of BASELINE.json's metric: train samples/s (GPT-2 medium, amp O2, FusedAdam, apex DDP) ----
+    # ---- the second half of BASELINE.json's metric: train samples/s ----
     train = None
+    msg = args.message_size or None
     if args.train:
         try:
             backends = [b for b in args.ddp_backend.split(",") if b] if world > 1 else ["nccl"]
-            runs = [run_train(dev, world, rank, barrier, args.train_batch, ddp_backend=b) for b in backends]
+            runs = [run_train(dev, world, rank, barrier, args.train_batch, ddp_backend=b, message_size=msg) for b in backends]
             train = runs[0]
             if len(runs) > 1:
                 train["other_ddp_backends"] = runs[1:]
+            if world > 1 and args.incumbent:
+                train["incumbent_torch_ddp"] = run_train(dev, world, rank, barrier, args.train_batch, ddp_backend="torch")
         except Exception as exc:                    # reported, never fatal for the headline line
             train = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        if args.resnet:
+            try:
+                extra["train_resnet50"] = run_train_resnet50(dev, world, rank, barrier, args.resnet_batch, message_size=msg)
+            except Exception as exc:
+                extra["train_resnet50"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        torch.cuda.empty_cache()
+
+    # ---- BASELINE configs[4]: many small tensors, O3 dynamic, inf/NaN on one random rank ----
+    if args.config5:
+        try:
+            extra["config5"] = run_config5(dev, world, rank, barrier, args.config5_total, args.config5_steps)
+        except Exception as exc:
+            extra["config5"] = {"error": f"{type(exc).__name__}: {exc}"[:300]}
+        torch.cuda.empty_cache()
 
     # ---- CPU baseline (rank 0, N = 1 only) ----
     cpu = None
@@ -445,38 +633,82 @@ def main():
                "cpu": cpu_model(), "ms_per_step": tc * 1e3,
                "sample": f"full list, 3 steps of check + unscale+AdamW+copy via oracle/amp_step_oracle.c (OpenMP, {cores} threads)"}
 
+    bad_trace = isinstance(extra.get("config5"), dict) and extra["config5"].get("scale_trace_equals_oracle") is False
     if rank == 0:
         line = {
-            "metric": "fused optimizer step HBM GB/s", "value": value, "unit": "GB/s", "n_gpus": world,
+            "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
-                       "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
-                       "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS,
-                       "collective": ("peer-memory reduce-scatter + pull-in-optimizer" if use_peer else "nccl all-reduce")
-                       if world > 1 else "none", "collective_note": peer_note},
-            "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "train": train,
+            "config": config_dict(desc, world, "peer" if use_peer else "nccl", peer_note),
+            "parity": parity, "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+            "clocks": clocks, "train": train,
         }
         line.update(extra)
         print(json.dumps(line), flush=True)
-    if use_peer:
-        del reducer
-        pbufs.close()
     if world > 1:
         dist.destroy_process_group()
+    if bad_trace:
+        raise SystemExit(4)
 
 
-def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmup=3, ddp_backend="nccl"):
+def run_allreduce_sweep(dev, world, barrier):
+    """ncclAllReduce(SUM, fp16) in place on GPT-2 medium's gradient bytes (354,823,168 elements = 709.6 MB,
+    BASELINE configs[3]) cut into messages of several sizes, back to back on one stream; bus GB/s as NCCL
+    defines it (bytes/t x 2(n-1)/n) against NVLink 5's 900 GB/s per direction."""
+    import torch.distributed as dist
+    n = 354_823_168
+    flat = torch.zeros(n, dtype=torch.float16, device=dev)
+    out = {"bytes_per_step": n * 2, "nvlink_peak_gbs_per_dir": 900.0, "by_message_elems": {}}
+    for msg in (10_000_000, 32_000_000, 64_000_000, n):
+        chunks = [flat[o:min(n, o + msg)] for o in range(0, n, msg)]
+        for c in chunks:                                # warm-up: NCCL sets its channels up per size class
+            dist.all_reduce(c)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 5
+        a0.record()
+        for _ in range(reps):
+            for c in chunks:
+                dist.all_reduce(c)
+        a1.record()
+        barrier()
+        ms = a0.elapsed_time(a1) / reps
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        out["by_message_elems"][str(msg)] = {"messages": len(chunks), "ms": ms,
+                                             "busbw_gbs": n * 2 / (ms * 1e-3) * 2 * (world - 1) / world / 1e9}
+    best = max(out["by_message_elems"].items(), key=lambda kv: kv[1]["busbw_gbs"])
+    apex_default = out["by_message_elems"][str(10_000_000)]
+    out.update(ms=apex_default["ms"], busbw_gbs=apex_default["busbw_gbs"], buckets=apex_default["messages"],
+               best_message_elems=int(best[0]), best_busbw_gbs=best[1]["busbw_gbs"])
+    del flat
+    return out
+
+
+def _ddp_wrap(model, world, ddp_backend, message_size, local):
+    if world <= 1:
+        return model, None
+    if ddp_backend == "torch":
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local])
+        return ddp, None
+    from apex.parallel import DistributedDataParallel
+    kw = {"message_size": message_size} if message_size else {}
+    ddp = DistributedDataParallel(model, allreduce_backend=ddp_backend, **kw)
+    return ddp, ddp
+
+
+def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmup=3, ddp_backend="nccl", message_size=None):
     """GPT-2 medium (24 x 1024, 354.8M parameters, random init) on synthetic tokens through the
     drop-in API exactly as the reference drives it: amp.initialize(O2) -> apex DDP -> scale_loss /
     backward / FusedAdam.step.  The transformer's forward/backward is torch/transformers library
-    code; what is under test is everything between backward and the next forward."""
+    code; what is under test is everything between backward and the next forward.
+    ddp_backend="torch" swaps apex DDP for torch.nn.parallel.DistributedDataParallel (the incumbent; the
+    reference's other branch, test_apex_distributed_spawn.py:124) with everything else unchanged."""
     import torch.distributed as dist
     from transformers import GPT2Config, GPT2LMHeadModel
     from apex import amp
     from apex.optimizers import FusedAdam
-    from apex.parallel import DistributedDataParallel
     from apex_example_b200 import ops
 
     amp._amp_state.reset()
@@ -490,9 +722,7 @@ def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmu
     n_params = sum(p.numel() for p in model.parameters())
     opt = FusedAdam(model.parameters(), lr=1e-4, weight_decay=0.01)
     model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
-    ddp = None
-    if world > 1:
-        model = ddp = DistributedDataParallel(model, allreduce_backend=ddp_backend)
+    model, ddp = _ddp_wrap(model, world, ddp_backend, message_size, dev.index)
     host_tokens = torch.randint(0, 50257, (micro_batch, seq), generator=torch.Generator().manual_seed(rank)).pin_memory()
     ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
 
@@ -530,13 +760,15 @@ def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmu
     post_bwd = sum(e[0].elapsed_time(e[1]) for e in ev) / steps      # scale_loss exit: (DDP join) + check + scaler update
     step_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / steps       # FusedAdam.step: one launch per dtype set
     scaler = amp._amp_state.loss_scalers[0]
-    res = {"model": "GPT-2 medium (GPT2Config(n_embd=1024, n_layer=24, n_head=16)), amp O2, FusedAdam, "
-                    + (f"apex DistributedDataParallel (bucket all-reduce: {ddp_backend})" if world > 1 else "single GPU"),
+    wrap = {"nccl": "apex DistributedDataParallel (bucket all-reduce: nccl)", "peer": "apex DistributedDataParallel (bucket all-reduce: peer)",
+            "torch": "torch.nn.parallel.DistributedDataParallel (incumbent)"}[ddp_backend] if world > 1 else "single GPU"
+    res = {"model": "GPT-2 medium (GPT2Config(n_embd=1024, n_layer=24, n_head=16)), amp O2, FusedAdam, " + wrap,
            "params": n_params, "micro_batch_per_gpu": micro_batch, "seq_len": seq, "n_gpus": world,
            "samples_per_s": micro_batch * world / (ms * 1e-3), "tokens_per_s": micro_batch * seq * world / (ms * 1e-3),
            "ms_per_step": ms, "ms_scale_loss_exit": post_bwd, "ms_optimizer_step": step_ms,
            "optimizer_step_gbs": BYTES_PER_PARAM * n_params / (step_ms * 1e-3) / 1e9,
            "b200_kernel_launches_per_step": (ops.launch_count() - l0) / steps,
+           "message_size": (message_size or 10_000_000) if ddp_backend != "torch" else "25 MiB buckets",
            "final_loss": float(loss.item()), "loss_scale": scaler.loss_scale(), "steps": steps}
     if ddp is not None:
         ddp.close()
@@ -545,13 +777,201 @@ def run_train(dev, world, rank, barrier, micro_batch=4, seq=1024, steps=8, warmu
     return res
 
 
+def run_train_resnet50(dev, world, rank, barrier, batch=256, steps=8, warmup=4, message_size=None):
+    """BASELINE configs[2]: torchvision resnet50() (161 tensors, 25,557,032 parameters; the 106 BatchNorm
+    tensors stay fp32 at O2 -> two dtype launch sets), amp O2, FusedSGD(lr 0.1, momentum 0.9, wd 1e-4),
+    apex DistributedDataParallel, synthetic 224x224 images (channels_last), dynamic loss scale."""
+    import torch.distributed as dist
+    import torchvision
+    from apex import amp
+    from apex.optimizers import FusedSGD
+    from apex_example_b200 import ops
+
+    amp._amp_state.reset()
+    torch.manual_seed(0)
+    model = torchvision.models.resnet50().to(dev).to(memory_format=torch.channels_last)
+    n_params = sum(p.numel() for p in model.parameters())
+    n_tensors = sum(1 for _ in model.parameters())
+    opt = FusedSGD(model.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4, materialize_master_grads=False)
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    model, ddp = _ddp_wrap(model, world, "nccl", message_size, dev.index)
+    g = torch.Generator().manual_seed(100 + rank)
+    images = torch.randn(batch, 3, 224, 224, generator=g).pin_memory()
+    labels = torch.randint(0, 1000, (batch,), generator=g).pin_memory()
+    crit = torch.nn.CrossEntropyLoss().to(dev)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
+    torch.backends.cudnn.benchmark = True
+
+    def one(e=None):
+        x = images.to(dev, non_blocking=True).contiguous(memory_format=torch.channels_last)
+        y = labels.to(dev, non_blocking=True)
+        loss = crit(model(x), y)
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+            if e is not None:
+                e[0].record()
+        if e is not None:
+            e[1].record()
+        opt.step()
+        if e is not None:
+            e[2].record()
+        return loss
+
+    for _ in range(warmup):
+        one()
+    barrier()
+    l0 = ops.launch_count()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for k in range(steps):
+        loss = one(ev[k])
+    t1.record()
+    barrier()
+    ms = t0.elapsed_time(t1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    step_us = sum(e[1].elapsed_time(e[2]) for e in ev) / steps * 1e3
+    exit_us = sum(e[0].elapsed_time(e[1]) for e in ev) / steps * 1e3
+    n_bn = sum(p.numel() for p in opt._amp_stash.all_fp32_params)
+    algo = 20 * n_params       # momentum SGD at O2: fp16 params 2+4+4 in, 4+4+2 out; fp32 BatchNorm params 4+4+4 in, 4+4 out
+    res = {"model": "torchvision resnet50(), amp O2, FusedSGD(lr=0.1, momentum=0.9, weight_decay=1e-4), "
+                    + ("apex DistributedDataParallel (nccl)" if world > 1 else "single GPU") + ", channels_last",
+           "params": n_params, "tensors": n_tensors, "fp32_batchnorm_params": n_bn, "batch_per_gpu": batch, "n_gpus": world,
+           "images_per_s": batch * world / (ms * 1e-3), "ms_per_step": ms,
+           "us_scale_loss_exit": exit_us, "us_optimizer_step": step_us,
+           "optimizer_step_gbs": algo / (step_us * 1e-6) / 1e9, "optimizer_dtype_launch_sets": 2,
+           "b200_kernel_launches_per_step": (ops.launch_count() - l0) / steps,
+           "final_loss": float(loss.item()), "loss_scale": amp._amp_state.loss_scalers[0].loss_scale(), "steps": steps}
+    if ddp is not None:
+        ddp.close()
+    del model, opt, ddp
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_config5(dev, world, rank, barrier, total=1_300_000_000, steps=30):
+    """BASELINE configs[4] / SURVEY.md §8d config 5: a 1.3 B-parameter list of many small tensors (sizes
+    log-uniform in [256, 262144], most not divisible by 8) at O3 with dynamic loss scaling — all-fp16 p, m,
+    v, g — stepped by amp + FusedAdam.  The gradient mean across the N ranks goes through
+    apex.parallel.Reducer (in place on the flat gradient arena: ncclAllReduce per message + the epilogue
+    kernel, which also raises amp's overflow flag).  At steps drawn Bernoulli(0.1) (seed 1; plus the first
+    two steps) ONE random rank gets an inf or NaN in one element (first / last / random) of one random
+    tensor.  Pass = the skip / loss-scale trace equals the oracle's state machine on EVERY rank and sampled
+    p / m / v are untouched on skipped steps."""
+    import torch.distributed as dist
+    import oracle
+    from workloads import many_small
+    from apex import amp
+    from apex.optimizers import FusedAdam
+    from apex.parallel import Reducer
+    from apex_example_b200 import ops
+
+    amp._amp_state.reset()
+    sizes = many_small(total=total, seed=0)
+    n = sum(sizes)
+    offs, acc = [], 0
+    for s_ in sizes:                                   # every tensor starts 32-byte aligned inside the gradient arena
+        acc += (-acc) % 16
+        offs.append(acc)
+        acc += s_
+    t0 = time.time()
+    torch.manual_seed(0)
+    flat_p = torch.randn(n, device=dev) * 0.02
+    flat_g = torch.zeros(acc, dtype=torch.float16, device=dev)
+
+    class Holder(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.ps = torch.nn.ParameterList([torch.nn.Parameter(t) for t in torch.split(flat_p, sizes)])
+
+    model = Holder()
+    opt = FusedAdam(model.parameters(), lr=1e-4, set_grad_none=False)
+    model, opt = amp.initialize(model, opt, opt_level="O3", loss_scale="dynamic", verbosity=0)
+    del flat_p
+    params = list(model.parameters())
+    assert all(p.dtype == torch.float16 for p in params)
+    for p, o, s_ in zip(params, offs, sizes):
+        p.grad = flat_g[o:o + s_]
+    reducer = Reducer([p.grad for p in params], message_size=64_000_000).covers(params) if world > 1 else None
+    setup_s = time.time() - t0
+    rng = random.Random(1)                             # the same draws on every rank
+    sc = oracle.LossScaler()
+    scaler = amp._amp_state.loss_scalers[0]
+    dummy = torch.zeros((), device=dev)
+    sample = sorted(set([0, len(sizes) - 1] + [rng.randrange(len(sizes)) for _ in range(62)]))
+    trace_ok, untouched_ok = True, True
+    normal_ms, skip_ms, host_ms, reduce_ms = [], [], [], []
+    gen = torch.Generator(device=dev).manual_seed(rank)
+    for it in range(steps):
+        flat_g.copy_((torch.randn(flat_g.numel(), device=dev, generator=gen) * 1e-3 * sc.loss_scale).half())
+        inject = rng.random() < 0.1 or it in (0, 1)
+        t_idx = rng.randrange(len(sizes))
+        e_idx = rng.choice([0, sizes[t_idx] - 1, rng.randrange(sizes[t_idx])])
+        who = rng.randrange(world)
+        bad = float("nan") if rng.random() < 0.3 else float("inf")
+        if inject and rank == who:
+            params[t_idx].grad[e_idx] = bad
+        before = None
+        if inject:
+            before = [(params[i].detach().clone(), opt.state[params[i]]["exp_avg"].clone() if params[i] in opt.state else None)
+                      for i in sample]
+        torch.cuda.synchronize()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        h0 = time.perf_counter()
+        e[0].record()
+        if reducer is not None:
+            reducer.reduce()                           # gradient mean + overflow check (epilogue kernel)
+        e[1].record()
+        with amp.scale_loss(dummy, opt):
+            pass
+        opt.step()
+        e[2].record()
+        host_ms.append((time.perf_counter() - h0) * 1e3)
+        torch.cuda.synchronize()
+        reduce_ms.append(e[0].elapsed_time(e[1]))
+        (skip_ms if inject else normal_ms).append(e[1].elapsed_time(e[2]))
+        skipped = sc.update_scale(inject)
+        trace_ok &= scaler.loss_scale() == sc.loss_scale and skipped == inject
+        if inject:
+            for i, (pb, mb) in zip(sample, before):
+                untouched_ok &= torch.equal(params[i].detach(), pb)
+                if mb is not None:
+                    untouched_ok &= torch.equal(opt.state[params[i]]["exp_avg"], mb)
+    if world > 1:
+        t = torch.tensor([1 if trace_ok else 0, 1 if untouched_ok else 0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        trace_ok, untouched_ok = bool(int(t[0])), bool(int(t[1]))
+    med = lambda xs: sorted(xs)[len(xs) // 2] if xs else None  # noqa: E731
+    res = {"config": "BASELINE configs[4]: many-small-tensor list, amp O3 + dynamic loss scale + FusedAdam, inf/NaN injected on "
+                     "one random rank" + (", gradient mean through apex.parallel.Reducer (in place, NCCL + epilogue kernel)" if world > 1 else ""),
+           "n_gpus": world, "tensors": len(sizes), "params": n, "not_divisible_by_8": sum(1 for s in sizes if s % 8),
+           "steps": steps, "injected": len(skip_ms), "scale_trace_equals_oracle": bool(trace_ok),
+           "scale_trace_checked_on": "every rank (AND over ranks)", "state_untouched_on_skips": bool(untouched_ok),
+           "normal_step_ms_gpu": med(normal_ms),
+           "normal_step_gbs_at_14B": 14 * n / (med(normal_ms) * 1e-3) / 1e9 if normal_ms else None,
+           "skip_step_ms_gpu": med(skip_ms), "gradient_mean_ms": med(reduce_ms) if world > 1 else None,
+           "host_ms_per_step_python": med(host_ms), "setup_s": setup_s,
+           "step_definition": "scale_loss exit (check unless the Reducer's epilogue did it, scaler update) + FusedAdam.step",
+           "final_loss_scale": sc.loss_scale}
+    del model, opt, params, flat_g, reducer
+    torch.cuda.empty_cache()
+    return res
+
+
 def run_e2e(sizes, dev, world, steps, warmup, barrier):
     """Same step through apex.amp + apex.optimizers.FusedAdam; per step the gradients come from
-    pinned host memory (H2D) and the scaler state is read back (D2H)."""
+    pinned host memory (H2D) and the scaler state is read back (D2H).  At N > 1 the gradient mean is
+    taken by apex.parallel.Reducer (in place on the flat gradient buffer: NCCL all-reduce per message +
+    this library's epilogue kernel, which also does the overflow check)."""
     import torch.distributed as dist
     from apex import amp
     from apex.optimizers import FusedAdam
+    from apex.parallel import Reducer
 
+    amp._amp_state.reset()
     n = sum(sizes)
     gen = torch.Generator(device=dev).manual_seed(0)
 
@@ -567,8 +987,10 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
     model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
     host_g = (torch.randn(n) * 1e-3 * LOSS_SCALE).half().pin_memory()
     dev_g = torch.empty(n, dtype=torch.float16, device=dev)
-    for prm, g in zip(model.parameters(), torch.split(dev_g, sizes)):
+    params = list(model.parameters())
+    for prm, g in zip(params, torch.split(dev_g, sizes)):
         prm.grad = g
+    reducer = Reducer([p_.grad for p_ in params]).covers(params) if world > 1 else None
     dummy = torch.zeros((), device=dev)
     scaler = amp._amp_state.loss_scalers[0]
 
@@ -592,9 +1014,8 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
         dev_g.copy_(staging, non_blocking=True)
         consumed.record(main)
         upload()                                               # overlaps with everything below
-        if world > 1:
-            dist.all_reduce(dev_g)
-            dev_g.mul_(1.0 / world)
+        if reducer is not None:
+            reducer.reduce()
         with amp.scale_loss(dummy, opt):
             pass                                               # backward already "happened": grads are in place
         opt.step()
@@ -616,11 +1037,14 @@ def run_e2e(sizes, dev, world, steps, warmup, barrier):
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    return {"value": BYTES_PER_PARAM * n * world / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms,
-            "h2d_bytes_per_step": n * 2, "d2h_bytes_per_step": 32, "steps": steps,
-            "api": "apex.amp.scale_loss + apex.optimizers.FusedAdam.step (O2)",
-            "note": "bound by the host link: 248.9 MB of fp16 gradients per step over PCIe, uploaded on a side stream "
-                    "while the previous step runs"}
+    res = {"value": BYTES_PER_PARAM * n * world / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms,
+           "h2d_bytes_per_step": n * 2, "d2h_bytes_per_step": 32, "steps": steps,
+           "api": "apex.amp.scale_loss + apex.optimizers.FusedAdam.step (O2)" + (" + apex.parallel.Reducer.reduce" if world > 1 else ""),
+           "note": "bound by the host link: 248.9 MB of fp16 gradients per step over PCIe, uploaded on a side stream "
+                   "while the previous step runs"}
+    del model, opt, params, dev_g, staging, reducer
+    torch.cuda.empty_cache()
+    return res
 
 
 if __name__ == "__main__":

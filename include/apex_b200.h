@@ -133,8 +133,15 @@ typedef struct b200_scaler_state {
 /* Initialise *dev_state (loss_scale = init_scale, inv_scale = inv_loss_scale = 1/init_scale, rest 0). */
 int32_t b200_scaler_init(b200_scaler_state* dev_state, float init_scale, void* stream);
 
+/* `dynamic` argument of b200_scaler_update: 0 = static scale, 1 = dynamic (the two values ABI version 1
+ * has always taken).  OR-ing in B200_SCALER_KEEP_SKIP says "no optimizer step has run since the previous
+ * update" (a further backward of a gradient-accumulation cycle): a pending found_inf then stays set, the
+ * way apex's one-shot skip_step stays patched in until step() is called. */
+#define B200_SCALER_DYNAMIC   1
+#define B200_SCALER_KEEP_SKIP 2
+
 /* One LossScaler.update_scale() on the device:
- *   flag = overflow_acc != 0;  inv_scale = 1/loss_scale;  found_inf = dynamic && flag
+ *   flag = overflow_acc != 0;  inv_scale = 1/loss_scale;  found_inf = dynamic && flag  (| pending one, see above)
  *   dynamic: flag ? (loss_scale = max(min_scale, loss_scale/2), unskipped = 0) : ++unskipped;
  *            unskipped == scale_window ? (loss_scale = min(max_scale, loss_scale*scale_factor), unskipped = 0)
  *   overflow_acc = 0; ++seq; inv_loss_scale = 1/loss_scale
@@ -312,8 +319,10 @@ int32_t b200_peer_free(void* dev_ptr);
  * last block publish "my shard of `epoch` is written" plus this rank's overflow bit to every pad;
  * b200_peer_wait_flags (one tiny kernel, next on the stream) waits for all ranks' (b) and ORs the
  * overflow bits into *dev_flag.  `epoch` starts at 1 and grows by one per step on every rank.
- * Waits are bounded (~30 s): a rank that never arrives sets pad->error instead of hanging the GPU;
- * check pad->error after synchronising (apex_example_b200.parallel.peer.PeerBuffers.check_signals). */
+ * Waits are bounded (~30 s): a rank that never arrives sets pad->error instead of hanging the GPU, and the
+ * kernel that gave up raises the overflow flag without reading any peer buffer, so the step that follows is
+ * SKIPPED (nothing is written from incomplete sums); pad->error stays set, every later step is skipped too,
+ * and the host reports it (apex_example_b200.parallel.peer.PeerBuffers.check_signals / close). */
 typedef struct b200_peer_signal_pad {
     int32_t ready[B200_MAX_PEERS];          /* ready[r]: highest epoch rank r has announced */
     int32_t done[B200_MAX_PEERS];           /* done[r]:  (epoch << 1) | overflow bit of rank r */
@@ -336,7 +345,8 @@ int32_t b200_peer_wait_flags(const b200_peer_sync* sync, int32_t* dev_flag, void
  * materialised (apex.parallel.DistributedDataParallel keeps apex's contract that param.grad
  * holds the mean after backward): waits for every rank's shard (if `sync`), ORs the overflow bits
  * into *dev_flag and copies each element of [0, bounds[world]) from its owner's `reduced` buffer
- * into `local_out`.  bounds[1..world-1] must be multiples of 8.  b200_peer_reduce_shard +
+ * into `local_out`.  bounds[1..world-1] must be multiples of 8 or equal to bounds[world] (empty trailing
+ * shards of a small bucket).  b200_peer_reduce_shard +
  * b200_peer_gather is a complete all-reduce over peer memory in two launches, no NCCL. */
 int32_t b200_peer_gather(const void* const* peer_reduced, int32_t world, void* local_out,
                          const int64_t* bounds, int32_t dtype, int32_t* dev_flag,
@@ -364,18 +374,21 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
  * b200_fused_adam_noalloc — the fused Adam step for callers that must not allocate.
  * (No counterpart in the reference: apex always goes through the torch allocator.)
  *
- * Who this is for: code that runs where cudaMalloc / the torch caching allocator are off
- * limits — a hook that fires while someone else's CUDA graph is being captured or replayed, a
- * plugin that was handed a fixed memory budget by its host application, a C caller that brings
- * its own p/m/v/grad buffers and has nowhere to put a tensor-list table.  b200_fused_adam needs
- * such a table in device memory and leaves allocating it to the caller; this entry point keeps
- * the table in a B200_NOALLOC_TABLE_BYTES static device array that is part of the library image
- * instead (every GPU that loads the library carries those bytes until the process exits).
+ * Who this is for: code that has no way to allocate device memory at the point where it needs an
+ * optimizer step — a plugin that its host application handed a fixed set of buffers and a rule
+ * "no further allocation", a callback that runs in a context where cudaMalloc and the torch
+ * caching allocator must not be entered (they may take locks or synchronise the device), a C
+ * caller that brings its own p/m/v/grad buffers and has nowhere to put a tensor-list table.
+ * b200_fused_adam needs such a table in device memory and leaves allocating it to the caller;
+ * this entry point keeps the table in a B200_NOALLOC_TABLE_BYTES static device array that is
+ * part of the library image instead (every GPU that loads the library carries those bytes until
+ * the process exits).
  *
  * Arguments are b200_table_build's description of the list (`ptrs` column-major over the Adam
  * columns g, p, m, v [, copy]; depth 4 when copy_dtype is B200_NONE, else 5), one
  * hyper-parameter group, and b200_fused_adam's scale / skip arguments.  The caller still owns
- * every input and output buffer.  Same arithmetic, same results as b200_fused_adam.
+ * every input and output buffer; a NULL entry in a column the kernel uses is refused with
+ * B200_EINVAL.  Same arithmetic, same results as b200_fused_adam.
  *
  * Limits and rules:
  *   - the list must fit: b200_table_bytes(n_tensors, numel, 4096) <= B200_NOALLOC_TABLE_BYTES
@@ -383,7 +396,7 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
  *     124M-parameter GPT-2-small list fits).  Larger lists are refused with B200_ESIZE and a
  *     message that says so.
  *   - it calls no cudaMalloc / cudaFree and nothing that allocates; the table image is assembled
- *     in a static host buffer and sent with one cudaMemcpyAsync on `stream`.
+ *     in a static (pageable) host buffer and sent with one cudaMemcpyAsync on `stream` at call time.
  *   - the first call on each device looks up the array's device address (a one-time set-up with
  *     that device current).  Make that first call before starting any stream capture.
  *   - all calls share the one array, and each call overwrites the previous table in full

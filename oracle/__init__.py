@@ -153,10 +153,10 @@ class LossScaler:
             self.loss_scale = min(self.max_loss_scale, self.loss_scale)
         self._s = _ScalerState(self.loss_scale, 1.0 / self.loss_scale, 0, self.unskipped, 0, 0, 0, 1.0 / self.loss_scale, 0)
 
-    def update_scale(self, overflow: bool) -> bool:
-        """Returns should_skip."""
+    def update_scale(self, overflow: bool, keep_skip: bool = False) -> bool:
+        """Returns should_skip.  ``keep_skip``: no optimizer step ran since the previous update."""
         self._s.overflow_acc = int(bool(overflow))
-        lib().oracle_scaler_update(ctypes.byref(self._s), ctypes.c_int(int(self.dynamic)),
+        lib().oracle_scaler_update(ctypes.byref(self._s), ctypes.c_int(int(self.dynamic) | (2 if keep_skip else 0)),
                                    ctypes.c_int(self.scale_window), ctypes.c_float(self.scale_factor),
                                    ctypes.c_float(self.min_loss_scale or 0.0),
                                    ctypes.c_float(self.max_loss_scale))

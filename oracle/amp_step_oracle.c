@@ -326,12 +326,17 @@ typedef struct {
 /* apex LossScaler.update_scale; equal to torch._amp_update_scale_
  * (TORCH/amp/grad_scaler.py:549-556) with backoff 0.5 / growth `scale_factor`, plus apex's
  * max_loss_scale (2**24) and optional min_loss_scale which torch lacks. */
-void oracle_scaler_update(oracle_scaler_state* s, int dynamic, int scale_window,
+void oracle_scaler_update(oracle_scaler_state* s, int mode, int scale_window,
                           float scale_factor, float min_scale, float max_scale) {
+    /* mode bit 0: dynamic scaling; bit 1: "no optimizer step has run since the previous update" — apex's
+     * one-shot skip_step stays patched in until step() is called, so a skip decided by
+     * an earlier backward of a gradient-accumulation cycle survives later clean backwards. */
+    int dynamic = mode & 1;
+    int carried = (mode & 2) ? s->found_inf : 0;
     int flag = s->overflow_acc != 0;
     s->inv_scale = 1.0f / s->loss_scale;
     s->had_overflow = flag;
-    s->found_inf = (dynamic && flag) ? 1 : 0;
+    s->found_inf = ((dynamic && flag) || carried) ? 1 : 0;
     if (dynamic) {
         if (flag) {
             float ns = s->loss_scale / 2.0f;
@@ -350,7 +355,7 @@ void oracle_scaler_update(oracle_scaler_state* s, int dynamic, int scale_window,
     }
     s->overflow_acc = 0;
     s->seq += 1;
-    s->skipped_total += s->found_inf;
+    s->skipped_total += (s->found_inf && !carried) ? 1 : 0;
     s->inv_loss_scale = 1.0f / s->loss_scale;
 }
 

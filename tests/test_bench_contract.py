@@ -25,6 +25,8 @@ def test_reference_arm_prints_the_contract_line():
     assert BASE_KEYS <= set(d) and d["impl"] == "reference"
     assert d["metric"] == "fused optimizer step HBM GB/s" and d["unit"] == "GB/s" and d["higher_is_better"] is True
     assert d["vs_baseline"] is None and "workload" in d["config"] and "model" not in d["config"]
+    assert d["warmup"] == 3 and d["steps"] == 1          # W >= 3 like the B200 arm, K as asked
+    assert set(d["config"]) == {"workload", "l2", "step", "parallelism", "bucket_elems", "collective", "collective_note"}
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
@@ -32,8 +34,10 @@ def test_reference_arm_prints_the_contract_line():
 
 @pytest.mark.gpu
 def test_b200_arm_prints_the_contract_line():
-    d = _run(["--steps", "20", "--warmup", "3", "--no-train"], timeout=900)
-    assert BASE_KEYS | {"roofline", "clocks"} <= set(d) and "impl" not in d
+    d = _run(["--steps", "20", "--warmup", "3", "--no-train", "--no-config5"], timeout=900)
+    assert BASE_KEYS | {"roofline", "clocks", "parity"} <= set(d) and "impl" not in d
+    par = d["parity"]
+    assert par["world"] == 1 and par["state_bit_exact"] is True and par["skip_agreed"] is True and par["all_ranks_ok"] is True
     assert d["n_gpus"] == 1 and d["steps"] == 20 and d["warmup"] == 3 and d["scaling"] == "weak" and d["data"] == "synthetic"
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9

@@ -204,3 +204,43 @@ def test_config1_reference_convnet_torch_ddp_gloo_adam():
     mp.spawn(_worker_config1, args=(2, _free_port(), out), nprocs=2, join=True)
     sums = dict(out.get() for _ in range(2))
     assert sums[0] == sums[1]
+
+
+# ---- apex.parallel.Reducer (manual-trigger gradient mean) ---------------------------------------------
+def _worker_reducer(rank, world, port, flat):
+    _init(rank, world, port)
+    from apex_example_b200.parallel import Reducer
+    model = _model(200 + rank)
+    red = Reducer(model, message_size=700)           # several chunks
+    ref = _model(200)
+    for p, q in zip(model.parameters(), ref.parameters()):
+        assert torch.equal(p, q), "Reducer(module) must broadcast rank 0's parameters"
+    g = torch.Generator().manual_seed(17 + rank)
+    x = torch.randn(16, 20, generator=g)
+    if flat:                                         # gradients as views of one flat arena: reduced in place
+        n = sum(p.numel() for p in model.parameters())
+        arena = torch.zeros(n)
+        off = 0
+        for p in model.parameters():
+            p.grad = arena[off:off + p.numel()].view_as(p)
+            off += p.numel()
+    model(x).pow(2).sum().backward()
+    ref(x).pow(2).sum().backward()
+    ptrs = [p.grad.data_ptr() for p in model.parameters()]
+    red.reduce()
+    for p, q, ptr in zip(model.parameters(), ref.parameters(), ptrs):
+        want = q.grad.clone()
+        dist.all_reduce(want)
+        torch.testing.assert_close(p.grad, want / world, rtol=1e-6, atol=1e-7)
+        assert p.grad.data_ptr() == ptr              # gradients stay where they were
+    # a list of gradient tensors instead of a module
+    grads = [torch.full((5,), float(rank + 1)), torch.full((3, 2), float(10 * (rank + 1)))]
+    Reducer(grads).reduce()
+    assert torch.equal(grads[0], torch.full((5,), (1 + world) / 2.0))
+    assert torch.equal(grads[1], torch.full((3, 2), 10 * (1 + world) / 2.0))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("flat", [False, True])
+def test_reducer_averages_gradients_on_demand_gloo(flat):
+    mp.spawn(_worker_reducer, args=(2, _free_port(), flat), nprocs=2, join=True)

@@ -430,7 +430,7 @@ def _run_steps(model, opt, xs, start, stop, overflow=()):
         opt.step()
 
 
-@pytest.mark.parametrize("which", ["adam", "sgd"])
+@pytest.mark.parametrize("which", ["adam", "sgd", "torch_adamw", "torch_sgd"])
 def test_checkpoint_round_trip_continues_bit_exactly(which):
     """optimizer.state_dict() + amp.state_dict() + model.state_dict() (fp32 at O2) restore a run so that
     it continues exactly like the uninterrupted one — including the skipped steps' effect on the step
@@ -442,8 +442,14 @@ def test_checkpoint_round_trip_continues_bit_exactly(which):
     def build():
         _amp_state.reset()
         model = _mlp(21)
-        opt = (FusedAdam(model.parameters(), lr=1e-2, weight_decay=0.01) if which == "adam"
-               else FusedSGD(model.parameters(), lr=1e-2, momentum=0.9, materialize_master_grads=False))
+        if which == "adam":
+            opt = FusedAdam(model.parameters(), lr=1e-2, weight_decay=0.01)
+        elif which == "sgd":
+            opt = FusedSGD(model.parameters(), lr=1e-2, momentum=0.9, materialize_master_grads=False)
+        elif which == "torch_adamw":            # stock torch optimizers adopted by the fused kernels
+            opt = torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.01)
+        else:
+            opt = torch.optim.SGD(model.parameters(), lr=1e-2, momentum=0.9)
         return amp.initialize(model, opt, opt_level="O2", verbosity=0)
 
     torch.manual_seed(5)
@@ -701,3 +707,203 @@ def test_add_param_group_after_steps_starts_its_own_step_count():
     torch.cuda.synchronize()
     assert torch.equal(a.detach().cpu(), ha) and torch.equal(b.detach().cpu(), hb)
     assert [g["step"] for g in opt.param_groups] == [5, 3]
+
+
+# ------------------------------------------------------------------------------------------------
+# round 2: gradient accumulation without delay_unscale, sticky skips, adopted torch optimizers
+# ------------------------------------------------------------------------------------------------
+class _PlainSGD(torch.optim.SGD):
+    """A subclass is never adopted by the fused kernels: it exercises amp's generic path."""
+
+
+def _make_opt(which, params, lr=1e-2):
+    from apex.optimizers import FusedAdam, FusedSGD
+    if which == "fused_adam":
+        return FusedAdam(params, lr=lr, set_grad_none=False)
+    if which == "fused_sgd":
+        return FusedSGD(params, lr=lr, momentum=0.9, materialize_master_grads=False)
+    if which == "torch_sgd":
+        return torch.optim.SGD(params, lr=lr, momentum=0.9)
+    if which == "torch_adamw":
+        return torch.optim.AdamW(params, lr=lr, weight_decay=0.01)
+    if which == "generic_sgd":
+        return _PlainSGD(params, lr=lr, momentum=0.9, foreach=False)
+    raise ValueError(which)
+
+
+def _bn_mlp(seed):
+    torch.manual_seed(seed)           # BatchNorm stays fp32 at O2: covers the fp32-parameter half of the path
+    return torch.nn.Sequential(torch.nn.Linear(32, 64), torch.nn.BatchNorm1d(64), torch.nn.ReLU(),
+                               torch.nn.Linear(64, 8)).cuda()
+
+
+@pytest.mark.parametrize("level", ["O2", "O1"])
+@pytest.mark.parametrize("which", ["fused_adam", "fused_sgd", "torch_sgd", "torch_adamw", "generic_sgd"])
+def test_gradient_accumulation_without_delay_unscale(which, level):
+    """Two scale_loss blocks, no zero_grad between them, no delay_unscale: each block is
+    unscaled on its own and merged, so the result must equal ONE backward of the summed loss."""
+    from apex import amp
+    from apex_example_b200.amp._amp_state import _amp_state
+    torch.manual_seed(8)
+    x1, x2 = torch.randn(16, 32, device="cuda"), torch.randn(16, 32, device="cuda")
+
+    def build():
+        _amp_state.reset()
+        model = _bn_mlp(33)
+        model.eval()                  # fixed BatchNorm statistics: both arrangements see the same function
+        for p in model.parameters():
+            p.requires_grad_(True)
+        return amp.initialize(model, _make_opt(which, model.parameters()), opt_level=level, loss_scale=1024.0, verbosity=0)
+
+    def fwd(model, x):
+        return model(x).float().pow(2).mean()
+
+    model_a, opt_a = build()
+    opt_a.zero_grad()
+    with amp.scale_loss(fwd(model_a, x1), opt_a) as s1:
+        s1.backward()
+    with amp.scale_loss(fwd(model_a, x2), opt_a) as s2:
+        s2.backward()
+    opt_a.step()
+
+    model_b, opt_b = build()
+    opt_b.zero_grad()
+    with amp.scale_loss(fwd(model_b, x1) + fwd(model_b, x2), opt_b) as s:
+        s.backward()
+    opt_b.step()
+    torch.cuda.synchronize()
+    moved = False
+    for a, b, p0 in zip(amp.master_params(opt_a), amp.master_params(opt_b), _bn_mlp(33).parameters()):
+        # the wrong merge (2*g1 + g2, or a gradient left scaled) is off by ~lr*|g| = 1e-3..1e-2; rounding of the
+        # fp16 gradient sum is 2^-11 relative -> <= 2e-5 after one lr=1e-2 step
+        torch.testing.assert_close(a.detach().float(), b.detach().float(), rtol=0, atol=3e-5)
+        moved |= not torch.equal(a.detach().float(), p0.detach().float())
+    assert moved
+
+
+@pytest.mark.parametrize("which", ["fused_adam", "torch_sgd", "generic_sgd"])
+def test_overflow_in_first_micro_batch_skips_the_accumulated_step(which):
+    """apex patches step() into a one-shot skip at the scale_loss exit that saw the overflow and leaves it
+    there until step() is called; a clean second backward must not un-skip the step."""
+    from apex import amp
+    model = _bn_mlp(5)
+    model, opt = amp.initialize(model, _make_opt(which, model.parameters()), opt_level="O2", verbosity=0)
+    x = torch.randn(16, 32, device="cuda")
+    before = [p.detach().clone() for p in model.parameters()]
+    opt.zero_grad()
+    with amp.scale_loss(model(x * float("inf")).float().pow(2).mean(), opt) as s:
+        s.backward()
+    with amp.scale_loss(model(x).float().pow(2).mean(), opt) as s:
+        s.backward()
+    opt.step()
+    torch.cuda.synchronize()
+    assert all(torch.equal(a, p.detach()) for a, p in zip(before, model.parameters())), "the poisoned step ran"
+    assert amp._amp_state.loss_scalers[0].loss_scale() == 2.0 ** 15
+    # and the next ordinary step runs again
+    opt.zero_grad()
+    with amp.scale_loss(model(x).float().pow(2).mean(), opt) as s:
+        s.backward()
+    opt.step()
+    torch.cuda.synchronize()
+    assert any(not torch.equal(a, p.detach()) for a, p in zip(before, model.parameters()))
+
+
+@pytest.mark.parametrize("which", ["torch_sgd", "torch_adamw"])
+def test_stock_torch_optimizer_takes_the_fused_sync_free_path(which):
+    """The reference's own configuration (torch.optim.SGD at test_apex_distributed_spawn.py:119): same launch
+    count as FusedSGD/FusedAdam, no host synchronisation anywhere in the step, torch-compatible state_dict."""
+    from apex import amp
+    from apex_example_b200 import ops
+    model = _mlp(3)
+    opt = _make_opt(which, model.parameters())
+    model, opt = amp.initialize(model, opt, opt_level="O2", verbosity=0)
+    assert getattr(opt, "_b200_engine", None) is not None
+    xs = [torch.randn(8, 32, device="cuda") for _ in range(6)]
+
+    def one(x):
+        loss = model(x).float().pow(2).mean()
+        opt.zero_grad()
+        with amp.scale_loss(loss, opt) as s:
+            s.backward()
+        opt.step()
+
+    one(xs[0])
+    one(xs[1])                         # tables and plans are built by now
+    torch.cuda.synchronize()
+    l0 = ops.launch_count()
+    torch.cuda.set_sync_debug_mode("error")
+    try:
+        for x in xs[2:]:
+            one(x)
+    finally:
+        torch.cuda.set_sync_debug_mode("default")
+    torch.cuda.synchronize()
+    assert (ops.launch_count() - l0) / 4 == 3          # check + scaler update + ONE fused step launch
+    sd = opt.state_dict()
+    fresh = type(opt)([torch.nn.Parameter(p.detach().clone()) for p in amp.master_params(opt)], lr=1e-2,
+                      **({"momentum": 0.9} if which == "torch_sgd" else {"weight_decay": 0.01}))
+    fresh.load_state_dict(sd)                          # an unpatched torch optimizer accepts it
+    if which == "torch_adamw":
+        steps = {float(st["step"]) for st in fresh.state.values()}
+        assert steps == {6.0}
+        assert all("exp_avg" in st and "exp_avg_sq" in st for st in fresh.state.values())
+    else:
+        assert all("momentum_buffer" in st for st in fresh.state.values())
+
+
+def test_adopted_torch_sgd_equals_torch_sgd_bit_for_bit_on_fp32_params():
+    """O0-like use (no amp): FusedSGD engine vs torch.optim.SGD(foreach=False) on identical fp32 inputs."""
+    from apex.optimizers import FusedSGD
+    gen = torch.Generator().manual_seed(4)
+    ps = [torch.randn(n, generator=gen).cuda() for n in (1000, 17, 4096)]
+    a = [torch.nn.Parameter(p.clone()) for p in ps]
+    b = [torch.nn.Parameter(p.clone()) for p in ps]
+    oa = FusedSGD(a, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    ob = torch.optim.SGD(b, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=True, foreach=False)
+    for _ in range(4):
+        gs = [torch.randn(p.shape, generator=gen).cuda() for p in ps]
+        for x, y, g in zip(a, b, gs):
+            x.grad, y.grad = g.clone(), g.clone()
+        oa.step()
+        ob.step()
+    for x, y in zip(a, b):
+        torch.testing.assert_close(x.detach(), y.detach(), rtol=1e-6, atol=1e-9)
+
+
+def test_fused_sgd_loads_a_torch_sgd_checkpoint_without_resetting_momentum():
+    from apex.optimizers import FusedSGD
+    gen = torch.Generator().manual_seed(9)
+    p0 = torch.randn(5000, generator=gen).cuda()
+    a, b = torch.nn.Parameter(p0.clone()), torch.nn.Parameter(p0.clone())
+    ta = torch.optim.SGD([a], lr=0.1, momentum=0.9, foreach=False)
+    for _ in range(3):
+        a.grad = torch.randn(5000, generator=gen).cuda()
+        ta.step()
+    sd = ta.state_dict()
+    assert "step" not in sd["param_groups"][0]
+    b.data.copy_(a.data)
+    fb = FusedSGD([b], lr=0.1, momentum=0.9)
+    fb.load_state_dict(sd)
+    g = torch.randn(5000, generator=gen).cuda()
+    a.grad, b.grad = g.clone(), g.clone()
+    ta.step()
+    fb.step()
+    torch.testing.assert_close(b.detach(), a.detach(), rtol=1e-6, atol=1e-9)
+    torch.testing.assert_close(fb.state[b]["momentum_buffer"], ta.state[a]["momentum_buffer"], rtol=1e-6, atol=1e-9)
+
+
+def test_plan_notices_moved_parameter_storage_on_the_very_next_step():
+    """model.half()/.to()/EMA swaps re-point p.data while the gradient object stays the same."""
+    from apex.optimizers import FusedAdam
+    p = torch.nn.Parameter(torch.randn(5000, device="cuda"))
+    opt = FusedAdam([p], lr=1e-2, set_grad_none=False)
+    p.grad = torch.randn(5000, device="cuda")
+    opt.step()
+    opt.step()
+    old = p.data
+    keep = old.clone()
+    p.data = old.clone()               # new storage, same values; the grad object is untouched
+    opt.step()
+    torch.cuda.synchronize()
+    assert torch.equal(old, keep), "the step wrote through a stale address"
+    assert not torch.equal(p.data, keep)

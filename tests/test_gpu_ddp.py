@@ -54,6 +54,12 @@ def _worker_train(rank, world, port, kwargs, out):
             x = x * float("inf")                    # overflow on ONE rank only: every rank must skip
         loss = ddp(x).float().pow(2).mean()
         opt.zero_grad()
+        if it >= 1 and which in ("fused_sgd", "torch_sgd"):
+            # zero_grad without set-to-none: the gradients are still the bucket views and every bucket was
+            # cleared as a whole (one memset per bucket)
+            for b in ddp.buckets:
+                assert all(p.grad is v for p, v in zip(b.params, b.views))
+                assert float(b.flat.float().abs().max()) == 0.0
         with amp.scale_loss(loss, opt) as scaled:
             scaled.backward()
         # post-allreduce gradients are bit-identical on every rank
@@ -84,19 +90,29 @@ def _need(n):
         pytest.skip(f"needs {n} GPUs (run under gpurun --gpus {n})")
 
 
-@pytest.mark.parametrize("kwargs", [dict(), dict(message_size=20000), dict(delay_allreduce=True),
-                                    dict(message_size=20000, num_allreduce_streams=2),
-                                    dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0),
-                                    dict(optimizer="torch_sgd"), dict(optimizer="fused_sgd", message_size=20000),
-                                    dict(allreduce_backend="peer"), dict(allreduce_backend="peer", message_size=20000),
-                                    dict(allreduce_backend="peer", delay_allreduce=True, num_allreduce_streams=2)])
-def test_two_rank_training_identical_ranks_and_skips(kwargs):
-    _need(2)
+_TRAIN_CASES = [dict(), dict(message_size=20000), dict(delay_allreduce=True),
+                dict(message_size=20000, num_allreduce_streams=2),
+                dict(allreduce_always_fp32=True), dict(gradient_predivide_factor=2.0),
+                dict(optimizer="torch_sgd"), dict(optimizer="fused_sgd", message_size=20000),
+                dict(allreduce_backend="peer"), dict(allreduce_backend="peer", message_size=20000),
+                dict(allreduce_backend="peer", delay_allreduce=True, num_allreduce_streams=2),
+                dict(allreduce_backend="peer", message_size=10)]      # every bucket closes at once: tiny 16-element buckets
+
+
+@pytest.mark.parametrize("world,kwargs", [(2, k) for k in _TRAIN_CASES] +
+                         [(w, k) for w in (4, 8) for k in (dict(), dict(optimizer="torch_sgd"),
+                                                            dict(allreduce_backend="peer", message_size=20000),
+                                                            dict(allreduce_backend="peer", message_size=10))])
+def test_multi_rank_training_identical_ranks_and_skips(world, kwargs):
+    """One rank's inf must make EVERY rank skip; gradients after the all-reduce and parameters after the steps
+    are bit-identical on all ranks (SURVEY.md §3.4, §4 "distributed GPU" tier) — at world 2, 4 and 8."""
+    _need(world)
     ctx = mp.get_context("spawn")
     out = ctx.SimpleQueue()
-    mp.spawn(_worker_train, args=(2, _free_port(), kwargs, out), nprocs=2, join=True)
+    mp.spawn(_worker_train, args=(world, _free_port(), kwargs, out), nprocs=world, join=True)
     scales, n_buckets = out.get()
-    assert n_buckets == (2 if kwargs.get("message_size") else 1)      # [16,4096,256,65536] | [256,16384]
+    ms = kwargs.get("message_size")
+    assert n_buckets == (6 if ms == 10 else 2 if ms else 1)           # [16,4096,256,65536] | [256,16384]
 
 
 def _worker_mean(rank, world, port, backend="nccl"):
@@ -124,6 +140,37 @@ def _worker_mean(rank, world, port, backend="nccl"):
 def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype(backend):
     _need(2)
     mp.spawn(_worker_mean, args=(2, _free_port(), backend), nprocs=2, join=True)
+
+
+def _worker_mean_oracle(rank, world, port):
+    """Peer backend at any world size: the bucket mean must equal the oracle's rank-ordered fp32 sum, rounded
+    to fp16, times 1/world — bit for bit, on every rank."""
+    _init(rank, world, port)
+    import oracle
+    from apex.parallel import DistributedDataParallel
+    model = _mlp(0).cuda().half()
+    ddp = DistributedDataParallel(model, message_size=30000, allreduce_backend="peer")
+    refs = []
+    for r in range(world):                          # every rank replays every rank's local backward
+        ref = _mlp(0).cuda().half()
+        x = torch.randn(16, 64, generator=torch.Generator().manual_seed(9 + r)).cuda().half()
+        ref(x).float().pow(2).mean().backward()
+        refs.append([q.grad.detach().cpu().reshape(-1) for q in ref.parameters()])
+    x = torch.randn(16, 64, generator=torch.Generator().manual_seed(9 + rank)).cuda().half()
+    ddp(x).float().pow(2).mean().backward()
+    torch.cuda.synchronize()
+    for i, p in enumerate(model.parameters()):
+        want = torch.zeros(p.numel(), dtype=torch.float16)
+        oracle.peer_reduce([refs[r][i] for r in range(world)], want, 0, p.numel(), 1.0 / world)
+        assert torch.equal(p.grad.detach().cpu().reshape(-1).view(torch.int16), want.view(torch.int16)), f"param {i}"
+    ddp.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_peer_bucket_mean_equals_oracle_at_every_world_size(world):
+    _need(world)
+    mp.spawn(_worker_mean_oracle, args=(world, _free_port()), nprocs=world, join=True)
 
 
 def _worker_single(rank, world, port):

@@ -103,6 +103,32 @@ def test_fused_adam_pulls_each_tile_from_its_owner_emulated(world):
         assert_lists_bit_equal(dc, oc, f"copy(rank {rank})")
 
 
+@pytest.mark.parametrize("n,world", [(10, 4), (10, 2), (3, 8), (64, 4), (70, 8)])
+def test_small_bucket_with_empty_trailing_shards_reduces_and_gathers(n, world):
+    """DDP's peer backend shards a bucket in multiples of 8 elements, so a small bucket whose size
+    is not a multiple of 8 (a lone 10-element bias at world 4: bounds [0, 8, 10, 10, 10]) has interior bounds
+    equal to its size.  Both halves of the all-reduce must accept and handle them."""
+    gen = torch.Generator().manual_seed(n * 10 + world)
+    host = [(torch.randn(n, generator=gen) * 8).half() for _ in range(world)]
+    dev = [h.cuda() for h in host]
+    shard = -(-n // world)
+    shard += (-shard) % 8
+    bounds = [min(r * shard, n) for r in range(world)] + [n]
+    reduced = [torch.full((n,), float("nan"), dtype=torch.float16, device="cuda") for _ in range(world)]
+    want = torch.zeros(n, dtype=torch.float16)
+    for r in range(world):
+        ops.peer_reduce_shard([d.data_ptr() for d in dev], reduced[r], bounds[r], bounds[r + 1], 1.0 / world)
+        oracle.peer_reduce(host, want, bounds[r], bounds[r + 1], 1.0 / world)
+    out = torch.zeros(n, dtype=torch.float16, device="cuda")
+    ops.peer_gather([t.data_ptr() for t in reduced], out, bounds)
+    torch.cuda.synchronize()
+    assert bit_equal(out, want)
+    # a boundary INSIDE the buffer that cuts an 8-element group is still refused
+    if n > 9:
+        with pytest.raises(RuntimeError, match="multiple of 8"):
+            ops.peer_gather([t.data_ptr() for t in reduced[:2]], out, [0, 5, n])
+
+
 def test_tile_aligned_shards_never_cut_a_tile():
     sizes = [5000, 17, 4096, 70001, 8, 12345, 9000]
     offs, total = _layout(sizes)
@@ -182,8 +208,9 @@ def _worker_ipc(rank, world, port, barrier="nccl", repeats=1):
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("barrier,repeats", [("nccl", 1), ("signal", 200)])
-def test_two_rank_ipc_reduce_and_fused_pull(barrier, repeats):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs (run under gpurun --gpus 2)")
-    mp.spawn(_worker_ipc, args=(2, _free_port(), barrier, repeats), nprocs=2, join=True)
+def test_real_rank_ipc_reduce_and_fused_pull(barrier, repeats, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run under gpurun --gpus {world})")
+    mp.spawn(_worker_ipc, args=(world, _free_port(), barrier, repeats), nprocs=world, join=True)

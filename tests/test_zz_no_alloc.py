@@ -1,13 +1,14 @@
 """b200_fused_adam_noalloc — the Adam step for callers that are not allowed to allocate.
 
 Some users of this library cannot call cudaMalloc or go through torch's allocator at the moment
-they need an optimizer step: a hook running while another component captures or replays a CUDA
-graph, a plugin living inside a host application with a fixed memory budget, a plain C program
-that owns its parameter buffers and nothing else.  The regular entry point needs a tensor-list
-table in device memory that the caller allocates; this one keeps the table in a 256 KiB static
-device array inside the library.  The test drives it through the C ABI twice in a row (the second
-time with a different, smaller list, so a stale table would show) and requires bit-identical
-results to the regular entry point — the same bar as the other kernel tests.
+they need an optimizer step: a plugin living inside a host application that gave it a fixed
+memory budget, a callback that must not enter an allocator (allocators may lock or synchronise
+the device), a plain C program that owns its parameter buffers and nothing else.  The regular
+entry point needs a tensor-list table in device memory that the caller allocates; this one keeps
+the table in a 256 KiB static device array inside the library.  The test drives it through the C
+ABI twice in a row (the second time with a different, smaller list, so a stale table would show)
+and requires bit-identical results to the regular entry point and to the CPU oracle — the same
+bar as the other kernel tests.
 
 This file is named so that pytest collects it last."""
 import ctypes
@@ -48,8 +49,28 @@ def test_lists_beyond_the_static_table_are_refused_with_a_clear_error():
     assert rc == -2
 
 
+def test_a_missing_column_pointer_is_refused_instead_of_dereferenced():
+    """Runs without a GPU: argument checks come before any CUDA call.  b200_table_build treats a
+    NULL pointer as "column absent"; the Adam kernel reads every column, so the entry point must
+    not let one through."""
+    lib = _lib.load()
+    n = 3
+    numel = (ctypes.c_int64 * n)(16, 0, 8)
+    grp = _lib.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.0, 1, 1, 1)
+    for depth, cdt in ((4, _lib.NONE), (5, _lib.F16)):
+        for hole in range(depth * n):
+            if numel[hole % n] == 0:
+                continue                       # an empty tensor has nothing to point at
+            ptrs = (ctypes.c_void_p * (depth * n))(*([0x1000] * (depth * n)))
+            ptrs[hole] = None
+            rc = lib.b200_fused_adam_noalloc(n, ptrs, numel, _lib.F16, _lib.F32, cdt, ctypes.byref(grp), 1.0, None, None, None)
+            assert rc == -1, (depth, hole)     # B200_EINVAL
+            assert "NULL" in lib.b200_last_error().decode()
+
+
 @pytest.mark.gpu
 def test_noalloc_entry_point_matches_the_regular_one_twice_in_a_row():
+    import oracle
     from apex_example_b200 import ops
     from apex_example_b200.tables import TensorTable
 
@@ -77,4 +98,12 @@ def test_noalloc_entry_point_matches_the_regular_one_twice_in_a_row():
         for name, ca, cb in zip("gpmvc", a, b):
             for i, (x, y) in enumerate(zip(ca, cb)):
                 assert torch.equal(x, y), f"call {call + 1}: column {name}[{i}] differs between the two entry points"
+        # and against the CPU oracle, on the same inputs (bit for bit, like every other kernel test)
+        h = [[t.cpu() for t in col] for col in make(sizes, 100 + call)]
+        for t in range(len(sizes)):
+            oracle.adam(h[0][t], h[1][t], h[2][t], h[3][t], h[4][t], lr=1e-3, weight_decay=0.01, step=step,
+                        inv_scale=1.0 / 128)
+        for name, ca, ch in zip("gpmvc", a, h):
+            for i, (x, y) in enumerate(zip(ca, ch)):
+                assert torch.equal(x.cpu(), y), f"call {call + 1}: column {name}[{i}] differs from the oracle"
         assert not torch.equal(a[1][0], make(sizes, 100 + call)[1][0]), "the step did not run"
