@@ -354,6 +354,7 @@ def _process_optimizer(optimizer, properties):
             # apex clears the master grads once they are consumed
             for p in stash.all_fp32_from_fp16_params:
                 p.grad = None
+        stash.grads_scaled = False                       # consumed: a later backward starts a new cycle
         if stash.accumulating:
             stash.accumulating = False
             stash.version += 1

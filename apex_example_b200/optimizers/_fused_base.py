@@ -13,7 +13,7 @@ import operator
 import torch
 
 from .. import _lib, ops
-from ..tables import TensorTable
+from ..tables import TensorTable, is_dense, layout_key
 
 _SUPPORTED = (torch.float16, torch.bfloat16, torch.float32)
 _GRAD_OF = operator.attrgetter("grad")
@@ -244,8 +244,10 @@ class FusedOptimizerBase(torch.optim.Optimizer):
                 cols = self._state_columns(p, group)
                 if s["state"] is None:
                     s["state"] = [[] for _ in cols]
-                if not g.is_contiguous():
-                    g = g.contiguous()
+                if layout_key(g) != layout_key(p) or not is_dense(g):
+                    # the gradient was produced in another memory layout than the parameter (e.g. a strided
+                    # view, or NCHW for a channels_last weight): bring it into the parameter's element order
+                    g = torch.empty_like(p.data, dtype=g.dtype).copy_(g)
                     grad_objs[-1] = None                     # a temporary copy: never replay this plan
                     holders[-1] = _NEVER
                 s["g"].append(g)

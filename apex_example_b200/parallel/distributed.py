@@ -28,7 +28,7 @@ from torch.autograd import Variable
 from torch.nn.modules import Module
 
 from .. import ops
-from ..tables import TensorTable
+from ..tables import TensorTable, flat_view_like, layout_key
 
 _SUPPORTED = (torch.float16, torch.bfloat16, torch.float32)
 _GRAD_OF = operator.attrgetter("grad")
@@ -258,7 +258,7 @@ class DistributedDataParallel(Module):
             b.numel = off
             b.flat = None if self._use_peer() else torch.zeros(off, dtype=b.dtype, device=device)
             if b.flat is not None:
-                b.views = [b.flat[o:o + p.numel()].view_as(p) for o, p in zip(b.offsets, b.params)]
+                b.views = [flat_view_like(b.flat, o, p) for o, p in zip(b.offsets, b.params)]
             if self.allreduce_always_fp32 and b.dtype != torch.float32 and not self._use_peer():
                 b.flat32 = torch.zeros(off, dtype=torch.float32, device=device)
             slot = b.index % self.num_allreduce_streams
@@ -300,7 +300,7 @@ class DistributedDataParallel(Module):
             for i, (b, st) in enumerate(zip(group, starts)):
                 b.flat = bufs.local["grads"][st:st + b.numel]
                 b.reduced = bufs.local["reduced"][st:st + b.numel]
-                b.views = [b.flat[o:o + p.numel()].view_as(p) for o, p in zip(b.offsets, b.params)]
+                b.views = [flat_view_like(b.flat, o, p) for o, p in zip(b.offsets, b.params)]
                 b.grad_ptrs = [ptr + st * esize for ptr in bufs.ptrs("grads")]
                 b.red_ptrs = [ptr + st * esize for ptr in bufs.ptrs("reduced")]
                 b.pads = bufs.signal_pads(index=i)
@@ -401,18 +401,26 @@ class DistributedDataParallel(Module):
         pre = 1.0 / self.gradient_predivide_factor
         with ctx:
             srcs, dsts = [], []
+            in_place = 0
             for p, view in zip(b.params, b.views):
                 g = p.grad
                 if g is None:
                     view.zero_()                      # parameter unused in this backward
-                elif g.data_ptr() != view.data_ptr():
+                elif g.data_ptr() == view.data_ptr():
+                    in_place += 1
+                else:
                     if self._on_cuda:
                         g.record_stream(side)         # the gather reads it on the side stream
-                    srcs.append(g if g.is_contiguous() else g.contiguous())
-                    dsts.append(view)
+                    if layout_key(g) == layout_key(view):
+                        srcs.append(g)
+                        dsts.append(view)
+                    else:                             # produced in another memory layout than the parameter's
+                        view.copy_(g)
+                        if pre != 1.0:
+                            view.mul_(pre)
             if srcs:
                 self._ops.gather(srcs, dsts, pre, self._table_cache, b.index)
-            if len(srcs) < len(b.params) and pre != 1.0:
+            if in_place and pre != 1.0:
                 # gradients that already live in the bucket (accumulated in place) still need the predivide
                 raise RuntimeError("gradient_predivide_factor != 1 cannot be combined with accumulating into "
                                    "bucket views across iterations; call zero_grad() between reductions.")

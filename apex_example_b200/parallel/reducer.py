@@ -16,7 +16,7 @@ import torch.distributed as dist
 from torch.nn.modules import Module
 
 from .. import ops
-from ..tables import TensorTable
+from ..tables import TensorTable, flat_view_like
 from .distributed import flat_dist_call
 
 
@@ -95,7 +95,7 @@ class Reducer:
                 flat = torch.zeros(total, dtype=dt, device=gs[0].device)
                 views, off = [], 0
                 for g in gs:
-                    views.append(flat[off:off + g.numel()].view_as(g))
+                    views.append(flat_view_like(flat, off, g))
                     off += g.numel()
                 entry["views"] = views
                 if gs[0].is_cuda:

@@ -25,6 +25,35 @@ def dtype_code(dt) -> int:
         raise RuntimeError(f"libapex_b200 only supports fp16, bf16 and fp32 tensors, got {dt}") from None
 
 
+def layout_key(x: torch.Tensor):
+    """None for the default (row-major contiguous) layout, else (shape, strides).  The kernels treat every
+    tensor as ``numel`` consecutive elements in MEMORY order, so the columns of one table row may use any
+    dense layout (e.g. channels_last convolution weights) as long as they all use the same one."""
+    if x.is_contiguous():
+        return None
+    return (tuple(x.shape), tuple(x.stride()))
+
+
+def is_dense(x: torch.Tensor) -> bool:
+    """True when the tensor's elements occupy ``numel`` consecutive slots of memory, in any dimension order."""
+    if x.is_contiguous():
+        return True
+    expect = 1
+    for stride, size in sorted((st, sz) for sz, st in zip(x.shape, x.stride()) if sz != 1):
+        if stride != expect:
+            return False
+        expect *= size
+    return True
+
+
+def flat_view_like(flat: torch.Tensor, offset: int, like: torch.Tensor) -> torch.Tensor:
+    """View of ``flat[offset : offset + like.numel()]`` with ``like``'s shape AND memory layout."""
+    v = flat[offset:offset + like.numel()]
+    if like.is_contiguous() or not is_dense(like):
+        return v.view(like.shape)
+    return v.as_strided(like.size(), like.stride())
+
+
 def auto_tile_elems(columns) -> int:
     """Tile size by measurement (profiles/r1_tuning.md): a tile should be exactly one trip of a
     CTA — 256 threads x 8 elements x the kernel's groups in flight.  The 4-5 column optimizer
@@ -64,6 +93,7 @@ def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequen
     esize = (ctypes.c_int32 * depth)()
     for t in range(n):
         numel[t] = ref[t].numel()
+    layouts = [layout_key(x) for x in ref]
     for d, col in enumerate(columns):
         es = 4
         for t, x in enumerate(col):
@@ -72,7 +102,10 @@ def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequen
                 continue
             if x.numel() != numel[t]:
                 raise RuntimeError(f"size mismatch in tensor_lists[{d}][{t}]: {x.numel()} vs {numel[t]}")
-            if not x.is_contiguous():
+            if layout_key(x) != layouts[t]:
+                raise RuntimeError(f"tensor_lists[{d}][{t}] has another memory layout than the other columns of "
+                                   f"tensor {t} (shape {tuple(x.shape)}, strides {tuple(x.stride())})")
+            if layouts[t] is not None and not is_dense(x):
                 raise RuntimeError(f"tensor_lists[{d}][{t}] is not contiguous")
             es = x.element_size()
             ptrs[d * n + t] = x.data_ptr()

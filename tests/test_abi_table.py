@@ -112,7 +112,11 @@ def test_builder_rejects_bad_input():
     with pytest.raises(RuntimeError):
         tables.build_image([[a], [torch.empty(11)]])
     with pytest.raises(RuntimeError):
-        tables.build_image([[torch.empty(4, 4).t()]])
+        tables.build_image([[torch.empty(4, 8)[:, ::2]]])          # holes in memory: not a dense tensor
+    with pytest.raises(RuntimeError):
+        tables.build_image([[torch.empty(4, 4).t()], [torch.empty(4, 4)]])   # dense, but the columns disagree on the layout
+    img, tiles = tables.build_image([[torch.empty(4, 4).t()], [torch.empty(4, 4).t()]])  # same dense layout: memory order
+    assert tiles == 1
     with pytest.raises(RuntimeError):
         tables.build_image([[a]], tile_elems=100)
     with pytest.raises(RuntimeError):

@@ -907,3 +907,25 @@ def test_plan_notices_moved_parameter_storage_on_the_very_next_step():
     torch.cuda.synchronize()
     assert torch.equal(old, keep), "the step wrote through a stale address"
     assert not torch.equal(p.data, keep)
+
+
+@pytest.mark.parametrize("grad_layout", ["channels_last", "nchw"])
+def test_channels_last_parameters_are_stepped_in_their_own_memory_order(grad_layout):
+    """The kernels walk memory order; a channels_last convolution weight (and its state) is dense but not
+    row-major.  Whatever layout the gradient arrives in, the result must equal torch.optim.SGD's."""
+    from apex.optimizers import FusedSGD
+    gen = torch.Generator().manual_seed(12)
+    w = torch.randn(32, 16, 3, 3, generator=gen).cuda().contiguous(memory_format=torch.channels_last)
+    a, b = torch.nn.Parameter(w.clone()), torch.nn.Parameter(w.clone())
+    assert not a.is_contiguous() and a.stride() == w.stride()
+    oa = FusedSGD([a], lr=0.1, momentum=0.9, weight_decay=1e-4)
+    ob = torch.optim.SGD([b], lr=0.1, momentum=0.9, weight_decay=1e-4, foreach=False)
+    for _ in range(3):
+        g = torch.randn(32, 16, 3, 3, generator=gen).cuda()
+        if grad_layout == "channels_last":
+            g = g.contiguous(memory_format=torch.channels_last)
+        a.grad, b.grad = g.clone(), g.clone()
+        oa.step()
+        ob.step()
+    torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-6, atol=1e-9)
+    torch.testing.assert_close(oa.state[a]["momentum_buffer"], ob.state[b]["momentum_buffer"], rtol=1e-6, atol=1e-9)

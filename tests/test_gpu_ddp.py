@@ -115,14 +115,22 @@ def test_multi_rank_training_identical_ranks_and_skips(world, kwargs):
     assert n_buckets == (6 if ms == 10 else 2 if ms else 1)           # [16,4096,256,65536] | [256,16384]
 
 
-def _worker_mean(rank, world, port, backend="nccl"):
+def _convnet(seed):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Conv2d(8, 16, 3, padding=1), torch.nn.ReLU(), torch.nn.Conv2d(16, 8, 3, padding=1),
+                               torch.nn.Flatten(), torch.nn.Linear(8 * 6 * 6, 4)).to(memory_format=torch.channels_last)
+
+
+def _worker_mean(rank, world, port, backend="nccl", conv=False):
     _init(rank, world, port)
     from apex.parallel import DistributedDataParallel
-    model = _mlp(0).cuda().half()
-    ref = _mlp(0).cuda().half()
+    make = _convnet if conv else _mlp                # conv: channels_last weights -> bucket views in that layout
+    model = make(0).cuda().half()
+    ref = make(0).cuda().half()
     ddp = DistributedDataParallel(model, message_size=30000, allreduce_backend=backend)
     gen = torch.Generator().manual_seed(9 + rank)
-    x = torch.randn(16, 64, generator=gen).cuda().half()
+    x = (torch.randn(16, 8, 6, 6, generator=gen).cuda().half().contiguous(memory_format=torch.channels_last) if conv
+         else torch.randn(16, 64, generator=gen).cuda().half())
     ddp(x).float().pow(2).mean().backward()
     ref(x).float().pow(2).mean().backward()
     for p, q in zip(model.parameters(), ref.parameters()):
@@ -132,14 +140,16 @@ def _worker_mean(rank, world, port, backend="nccl"):
         # two addends: the fp16 sum is the correctly rounded exact sum whichever way it is accumulated, so the
         # NCCL path and the peer path (fp32 accumulation, one rounding) must both reproduce it exactly
         assert torch.equal(p.grad, want)
+        assert p.grad.stride() == p.stride() or p.grad.is_contiguous() and p.is_contiguous()
     ddp.close()
     dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("conv", [False, True])
 @pytest.mark.parametrize("backend", ["nccl", "peer"])
-def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype(backend):
+def test_two_rank_bucket_mean_is_sum_then_scale_in_grad_dtype(backend, conv):
     _need(2)
-    mp.spawn(_worker_mean, args=(2, _free_port(), backend), nprocs=2, join=True)
+    mp.spawn(_worker_mean, args=(2, _free_port(), backend, conv), nprocs=2, join=True)
 
 
 def _worker_mean_oracle(rank, world, port):
