@@ -78,6 +78,11 @@ def _patch_skip_step(optimizer, loss_scaler, loss_id):
             loss_id, loss_scaler.loss_scale()))
         for p in stash.all_fp32_from_fp16_params:
             p.grad = None
+        loss_scaler.note_step()                  # the skip consumed the decision: the next update starts afresh
+        stash.grads_scaled = False
+        if stash.accumulating:
+            stash.accumulating = False
+            stash.version += 1
         self.step = old_step
         stash.already_patched = False
 

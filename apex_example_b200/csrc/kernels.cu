@@ -409,10 +409,16 @@ __device__ __forceinline__ void adam_elem(float g_in, float& p, float& m, float&
     p = __fadd_rn(p, __fmul_rn(k.neg_step, __fdiv_rn(m, denom)));
 }
 
+// 16-bit state (amp O3: p, m, v and g all fp16/bf16) moves half the bytes per element, so a thread keeps
+// twice as many 8-element groups in flight and the table uses 8192-element tiles (tables.auto_tile_elems)
+#ifndef B200_U16_MUL
+#define B200_U16_MUL 2
+#endif
+
 template <int G, int S, int C>      // grad, state (p/m/v) and copy element types; C may be B200_NONE
 struct AdamOp {
     using Params = AdamParams;
-    static constexpr int kUnrollMul = 1;
+    static constexpr int kUnrollMul = (S != B200_F32 && G != B200_F32) ? B200_U16_MUL : 1;
     struct Ctx { AdamConsts k; float s; const void* g; };     // g: the tile's gradient column (local or a peer's)
     static constexpr int kCopyCol = 4;
     static __device__ __forceinline__ uint32_t rotation(const Params& p) { return p.pull.first_tile; }
@@ -509,7 +515,7 @@ __device__ __forceinline__ void sgd_elem(float g_in, float& p, float& mom, const
 template <int G, int S, int C>
 struct SgdOp {
     using Params = SgdParams;
-    static constexpr int kUnrollMul = 1;
+    static constexpr int kUnrollMul = (S != B200_F32 && G != B200_F32) ? B200_U16_MUL : 1;
     // measured (profiles/r01_tune_sweep_*.txt): 2 resident CTAs/SM stream at 6.5-6.7 TB/s, the 3 the
     // register budget would allow only at 6.0 TB/s (more concurrent streams per DRAM page)
     static constexpr int kMaxCtasPerSm = 2;

@@ -851,7 +851,7 @@ def test_stock_torch_optimizer_takes_the_fused_sync_free_path(which):
         assert all("momentum_buffer" in st for st in fresh.state.values())
 
 
-def test_adopted_torch_sgd_equals_torch_sgd_bit_for_bit_on_fp32_params():
+def test_fused_sgd_equals_torch_sgd_on_fp32_params_nesterov():
     """O0-like use (no amp): FusedSGD engine vs torch.optim.SGD(foreach=False) on identical fp32 inputs."""
     from apex.optimizers import FusedSGD
     gen = torch.Generator().manual_seed(4)
@@ -866,8 +866,8 @@ def test_adopted_torch_sgd_equals_torch_sgd_bit_for_bit_on_fp32_params():
             x.grad, y.grad = g.clone(), g.clone()
         oa.step()
         ob.step()
-    for x, y in zip(a, b):
-        torch.testing.assert_close(x.detach(), y.detach(), rtol=1e-6, atol=1e-9)
+    for x, y in zip(a, b):            # vs torch's CUDA kernels (which may fuse multiply-adds): a few fp32 ulps at |p| ~ 1
+        torch.testing.assert_close(x.detach(), y.detach(), rtol=1e-6, atol=1e-6)
 
 
 def test_fused_sgd_loads_a_torch_sgd_checkpoint_without_resetting_momentum():
@@ -879,7 +879,7 @@ def test_fused_sgd_loads_a_torch_sgd_checkpoint_without_resetting_momentum():
     for _ in range(3):
         a.grad = torch.randn(5000, generator=gen).cuda()
         ta.step()
-    sd = ta.state_dict()
+    sd = copy.deepcopy(ta.state_dict())       # load_state_dict keeps same-dtype tensors by reference: do not share buffers
     assert "step" not in sd["param_groups"][0]
     b.data.copy_(a.data)
     fb = FusedSGD([b], lr=0.1, momentum=0.9)
@@ -888,8 +888,9 @@ def test_fused_sgd_loads_a_torch_sgd_checkpoint_without_resetting_momentum():
     a.grad, b.grad = g.clone(), g.clone()
     ta.step()
     fb.step()
-    torch.testing.assert_close(b.detach(), a.detach(), rtol=1e-6, atol=1e-9)
-    torch.testing.assert_close(fb.state[b]["momentum_buffer"], ta.state[a]["momentum_buffer"], rtol=1e-6, atol=1e-9)
+    # a reset momentum buffer (mom = grad instead of 0.9*mom + grad) would be off by ~|mom| ~ 1
+    torch.testing.assert_close(b.detach(), a.detach(), rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(fb.state[b]["momentum_buffer"], ta.state[a]["momentum_buffer"], rtol=1e-6, atol=1e-6)
 
 
 def test_plan_notices_moved_parameter_storage_on_the_very_next_step():
@@ -927,5 +928,6 @@ def test_channels_last_parameters_are_stepped_in_their_own_memory_order(grad_lay
         a.grad, b.grad = g.clone(), g.clone()
         oa.step()
         ob.step()
-    torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-6, atol=1e-9)
-    torch.testing.assert_close(oa.state[a]["momentum_buffer"], ob.state[b]["momentum_buffer"], rtol=1e-6, atol=1e-9)
+    # a wrong element pairing between the layouts would be off by ~|g| ~ 1; fp32 rounding is ~1e-7 here
+    torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(oa.state[a]["momentum_buffer"], ob.state[b]["momentum_buffer"], rtol=1e-6, atol=1e-6)
