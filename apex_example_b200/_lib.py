@@ -110,6 +110,13 @@ SIGNATURES = {
     "b200_fused_sgd_peer": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(SgdGroup),
                                       c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                       ctypes.POINTER(PeerPull), c_void_p]),
+    "b200_spec_shadow_delta": (c_int64, [c_int64, c_int32]),
+    "b200_fused_adam_spec": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup), c_int32,
+                                       c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
+                                       ctypes.POINTER(PeerPull), c_void_p]),
+    "b200_spec_commit": (c_int32, [c_void_p, c_int32, c_int32, c_float, c_float, c_float, c_void_p, c_void_p,
+                                   ctypes.POINTER(StepSync), c_void_p]),
+    "b200_spec_repair": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

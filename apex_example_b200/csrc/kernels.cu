@@ -479,6 +479,147 @@ struct AdamOp {
     static __device__ __forceinline__ void finish(const Params& p, bool) { step_epilogue(p.sync, false); }
 };
 
+
+// ============================================================================================
+// speculative single-pass step (no separate overflow-check pass)
+// ============================================================================================
+// The all-or-nothing skip normally costs a pass of its own: every gradient has to be inspected
+// before the first state element may be overwritten.  Here p, m and v are double-buffered — every
+// state tensor is followed by a shadow copy of itself (b200_spec_shadow_delta bytes further on) —
+// and ONE pass reads the gradient and the CURRENT copies, inspects the gradient, and writes the
+// new state into the OTHER copies and the new fp16 weights into the model.  A one-thread commit
+// kernel then runs the loss-scaler update and flips the device-side parity word only if nothing
+// overflowed; after an overflow (rare: the scaler backs off) the parity stays, the state is
+// untouched by construction, and a repair pass re-derives the fp16 weights from the current masters.
+struct SpecParams {
+    AdamConsts grp[B200_MAX_GROUPS][B200_STEP_WINDOW];
+    float inv_scale;
+    const float* dev_inv_scale;
+    int32_t* flag;                  // raised on a non-finite gradient (the loss scaler's overflow_acc)
+    const int32_t* parity;          // 0: the primary copies are current, 1: the shadows are
+    StepSync sync;
+    PeerPull pull;
+};
+
+__device__ __forceinline__ int64_t spec_delta(int64_t numel, int elem_size) {
+    return (numel * elem_size + 255) / 256 * 256;
+}
+
+template <int G, int S, int C>
+struct AdamSpecOp {
+    using Params = SpecParams;
+    static constexpr int kUnrollMul = (S != B200_F32 && G != B200_F32) ? B200_U16_MUL : 1;
+    struct Ctx { AdamConsts k; float s; const void* g; int64_t rd, wr; };
+    static constexpr int kCopyCol = 4;
+    static __device__ __forceinline__ uint32_t rotation(const Params& p) { return p.pull.first_tile; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
+        step_prologue(nullptr, p.sync, win);
+        return false;                                   // never skipped up front: this pass IS the check
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win, int64_t start) {
+        using GT = typename Elem<G>::type;
+        using ST = typename Elem<S>::type;
+        const char* g0 = reinterpret_cast<const char*>(r.ptr[0]);
+        const long long d = peer_delta(p.pull, reinterpret_cast<const GT*>(g0) + start);
+        const int cur = *reinterpret_cast<const volatile int32_t*>(p.parity) & 1;
+        const int64_t delta = spec_delta(r.numel, sizeof(ST)) / static_cast<int64_t>(sizeof(ST));   // in elements
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale, g0 + d,
+                   cur ? delta : 0, cur ? 0 : delta};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool& bad) {
+        Raw8<G> rg[U];
+        Raw8<S> rp[U], rm[U], rv[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                load8<G, true>(c.g, idx[u], rg[u]);
+                load8<S, true>(r.ptr[1], idx[u] + c.rd, rp[u]);     // read-only here: the other copy is written
+                load8<S, true>(r.ptr[2], idx[u] + c.rd, rm[u]);
+                load8<S, true>(r.ptr[3], idx[u] + c.rd, rv[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float g[kVec], p[kVec], m[kVec], v[kVec];
+            unpack8<G>(rg[u], g);
+            unpack8<S>(rp[u], p);
+            unpack8<S>(rm[u], m);
+            unpack8<S>(rv[u], v);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                bad |= !is_finite(g[i]);
+                adam_elem(g[i], p[i], m[i], v[i], c.k, c.s);
+            }
+            store8<S>(r.ptr[1], idx[u] + c.wr, p);
+            store8<S>(r.ptr[2], idx[u] + c.wr, m);
+            store8<S>(r.ptr[3], idx[u] + c.wr, v);
+            if constexpr (C != B200_NONE) {
+                if constexpr (S != B200_F32) {
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) p[i] = round_through<S>(p[i]);
+                }
+                store8<C>(r.ptr[kCopyCol], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool& bad) {
+        float p = load1<S>(r.ptr[1], i + c.rd), m = load1<S>(r.ptr[2], i + c.rd), v = load1<S>(r.ptr[3], i + c.rd);
+        const float g = load1<G>(c.g, i);
+        bad |= !is_finite(g);
+        adam_elem(g, p, m, v, c.k, c.s);
+        store1<S>(r.ptr[1], i + c.wr, p);
+        store1<S>(r.ptr[2], i + c.wr, m);
+        store1<S>(r.ptr[3], i + c.wr, v);
+        if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
+    }
+    static __device__ __forceinline__ void finish(const Params& p, bool bad) {
+        if (p.flag) raise_flag(p.flag, bad);
+    }
+};
+
+// repair after a skipped speculative step: model copy = cast(current master); exits at once otherwise
+struct RepairParams {
+    const int32_t* found_inf;
+    const int32_t* parity;
+};
+
+template <int S, int C>
+struct SpecRepairOp {
+    using Params = RepairParams;
+    static constexpr int kUnrollMul = 2;
+    struct Ctx { int64_t rd; };
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int&) {
+        return *reinterpret_cast<const volatile int32_t*>(p.found_inf) == 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int, int64_t) {
+        using ST = typename Elem<S>::type;
+        const int cur = *reinterpret_cast<const volatile int32_t*>(p.parity) & 1;
+        return Ctx{cur ? spec_delta(r.numel, sizeof(ST)) / static_cast<int64_t>(sizeof(ST)) : 0};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+        Raw8<S> in[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) load8<S, true>(r.ptr[1], idx[u] + c.rd, in[u]);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec];
+            unpack8<S>(in[u], x);
+            store8<C>(r.ptr[4], idx[u], x);
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        store1<C>(r.ptr[4], i, load1<S>(r.ptr[1], i + c.rd));
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
 // ============================================================================================
 // fused unscale + SGD + master->model copy
 // ============================================================================================
@@ -893,8 +1034,8 @@ __global__ void scaler_init_kernel(b200_scaler_state* s, float init_scale) {
     s->reserved[0] = s->reserved[1] = s->reserved[2] = 0;
 }
 
-__global__ void scaler_update_kernel(b200_scaler_state* s, int mode, int scale_window, float scale_factor,
-                                     float min_scale, float max_scale, b200_scaler_state* mirror) {
+__device__ __forceinline__ int scaler_update_body(b200_scaler_state* s, int mode, int scale_window, float scale_factor,
+                                                  float min_scale, float max_scale, b200_scaler_state* mirror) {
     b200_scaler_state st = *s;
     const int dynamic = mode & B200_SCALER_DYNAMIC;
     const int flag = st.overflow_acc != 0;
@@ -940,6 +1081,22 @@ __global__ void scaler_update_kernel(b200_scaler_state* s, int mode, int scale_w
         __threadfence_system();
         mv->seq = st.seq;
     }
+    return st.found_inf;
+}
+
+__global__ void scaler_update_kernel(b200_scaler_state* s, int mode, int scale_window, float scale_factor,
+                                     float min_scale, float max_scale, b200_scaler_state* mirror) {
+    scaler_update_body(s, mode, scale_window, scale_factor, min_scale, max_scale, mirror);
+}
+
+// Commit of a speculative step: the loss-scaler update (which turns the accumulated overflow flag into
+// found_inf and the new scale) followed by the parity flip that makes the freshly written copies current —
+// only if nothing overflowed.  Also advances the {calls, skips} step counters.
+__global__ void spec_commit_kernel(b200_scaler_state* s, int mode, int scale_window, float scale_factor, float min_scale,
+                                   float max_scale, b200_scaler_state* mirror, int32_t* parity, StepSync sync) {
+    const int found = scaler_update_body(s, mode, scale_window, scale_factor, min_scale, max_scale, mirror);
+    if (!found) *parity = (*parity & 1) ^ 1;
+    step_epilogue(sync, found != 0);
 }
 
 // ============================================================================================
@@ -1105,6 +1262,35 @@ int32_t b200_clip_scale(float* dev_sumsq, const float* dev_inv_scale, float inv_
     return after_launch("clip_scale");
 }
 
+// Per-group constants of one Adam launch for every step-window candidate.  Hyper-parameters are derived in
+// double and rounded to float once, exactly like the Python scalars torch.optim.Adam hands to its fp32 tensor ops.
+static int fill_adam_consts(const char* name, const b200_adam_group* groups, int32_t n_groups,
+                            AdamConsts (*grp)[B200_STEP_WINDOW]) {
+    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
+        return set_error(B200_EINVAL, "%s: n_groups must be 1..%d", name, B200_MAX_GROUPS);
+    for (int i = 0; i < n_groups; i++) {
+        const b200_adam_group& h = groups[i];
+        if (h.step < 1) return set_error(B200_EINVAL, "%s: step must be >= 1", name);
+        for (int w = 0; w < B200_STEP_WINDOW; w++) {
+            AdamConsts& k = grp[i][w];
+            const int64_t step = h.step - w > 1 ? h.step - w : 1;
+            k.w1 = static_cast<float>(1.0 - h.beta1);
+            k.one_m_w1 = 1.0f - k.w1;
+            k.b2 = static_cast<float>(h.beta2);
+            k.w2 = static_cast<float>(1.0 - h.beta2);
+            const double bc1 = h.bias_correction ? 1.0 - std::pow(h.beta1, static_cast<double>(step)) : 1.0;
+            const double bc2 = h.bias_correction ? 1.0 - std::pow(h.beta2, static_cast<double>(step)) : 1.0;
+            k.neg_step = static_cast<float>(-(h.lr / bc1));
+            k.bc2_sqrt = static_cast<float>(std::pow(bc2, 0.5));
+            k.eps = static_cast<float>(h.eps);
+            k.wd = static_cast<float>(h.weight_decay);
+            k.decay = static_cast<float>(1.0 - h.lr * h.weight_decay);
+            k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.adam_w_mode ? 2u : 0u) | (k.w1 < 0.5f ? 0u : 4u);
+        }
+    }
+    return 0;
+}
+
 int32_t b200_fused_adam(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
                         const b200_adam_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
                         const int32_t* dev_found_inf, const b200_step_sync* sync, void* stream) {
@@ -1123,38 +1309,63 @@ int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles, int32_t gra
                              int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
                              const float* dev_inv_scale, const int32_t* dev_found_inf, const b200_step_sync* sync,
                              const b200_peer_pull* pull, void* stream) {
-    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
-        return set_error(B200_EINVAL, "fused_adam: n_groups must be 1..%d", B200_MAX_GROUPS);
     AdamParams prm;
     memset(&prm, 0, sizeof(prm));
     if (int rc = to_pull(pull, prm.pull, "fused_adam")) return rc;
-    for (int i = 0; i < n_groups; i++) {
-        const b200_adam_group& h = groups[i];
-        if (h.step < 1) return set_error(B200_EINVAL, "fused_adam: step must be >= 1");
-        for (int w = 0; w < B200_STEP_WINDOW; w++) {
-            AdamConsts& k = prm.grp[i][w];
-            const int64_t step = h.step - w > 1 ? h.step - w : 1;
-            // hyper-parameters are derived in double and rounded to float once, exactly like the
-            // Python scalars torch.optim.Adam hands to its fp32 tensor ops
-            k.w1 = static_cast<float>(1.0 - h.beta1);
-            k.one_m_w1 = 1.0f - k.w1;
-            k.b2 = static_cast<float>(h.beta2);
-            k.w2 = static_cast<float>(1.0 - h.beta2);
-            const double bc1 = h.bias_correction ? 1.0 - std::pow(h.beta1, static_cast<double>(step)) : 1.0;
-            const double bc2 = h.bias_correction ? 1.0 - std::pow(h.beta2, static_cast<double>(step)) : 1.0;
-            k.neg_step = static_cast<float>(-(h.lr / bc1));
-            k.bc2_sqrt = static_cast<float>(std::pow(bc2, 0.5));
-            k.eps = static_cast<float>(h.eps);
-            k.wd = static_cast<float>(h.weight_decay);
-            k.decay = static_cast<float>(1.0 - h.lr * h.weight_decay);
-            k.flags = (h.weight_decay != 0.0 ? 1u : 0u) | (h.adam_w_mode ? 2u : 0u) | (k.w1 < 0.5f ? 0u : 4u);
-        }
-    }
+    if (int rc = fill_adam_consts("fused_adam", groups, n_groups, prm.grp)) return rc;
     prm.inv_scale = inv_scale;
     prm.dev_inv_scale = dev_inv_scale;
     prm.dev_found_inf = dev_found_inf;
     prm.sync = to_sync(sync);
     return dispatch_step<AdamOp>("fused_adam", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// speculative single-pass step (see AdamSpecOp)
+// ------------------------------------------------------------------------------------------------
+int64_t b200_spec_shadow_delta(int64_t numel, int32_t elem_size) {
+    if (numel < 0 || (elem_size != 2 && elem_size != 4)) return set_error(B200_EINVAL, "spec_shadow_delta: bad argument");
+    return (numel * elem_size + 255) / 256 * 256;
+}
+
+int32_t b200_fused_adam_spec(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                             int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
+                             const float* dev_inv_scale, int32_t* dev_flag, const int32_t* dev_parity,
+                             const b200_step_sync* sync, const b200_peer_pull* pull, void* stream) {
+    if (!dev_parity) return set_error(B200_EINVAL, "fused_adam_spec: dev_parity is NULL");
+    SpecParams prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = to_pull(pull, prm.pull, "fused_adam_spec")) return rc;
+    if (int rc = fill_adam_consts("fused_adam_spec", groups, n_groups, prm.grp)) return rc;
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.flag = dev_flag;
+    prm.parity = dev_parity;
+    prm.sync = to_sync(sync);
+    prm.sync.read_only = 1;                              // the commit kernel advances the counters
+    return dispatch_step<AdamSpecOp>("fused_adam_spec", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+int32_t b200_spec_commit(b200_scaler_state* dev_state, int32_t mode, int32_t scale_window, float scale_factor,
+                         float min_scale, float max_scale, b200_scaler_state* mirror, int32_t* dev_parity,
+                         const b200_step_sync* sync, void* stream) {
+    if (!dev_state || !dev_parity) return set_error(B200_EINVAL, "spec_commit: NULL argument");
+    if (mode & ~(B200_SCALER_DYNAMIC | B200_SCALER_KEEP_SKIP)) return set_error(B200_EINVAL, "spec_commit: unknown mode bits");
+    if ((mode & B200_SCALER_DYNAMIC) && scale_window <= 0) return set_error(B200_EINVAL, "spec_commit: scale_window must be > 0");
+    spec_commit_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(dev_state, mode, scale_window, scale_factor, min_scale,
+                                                                       max_scale, mirror, dev_parity, to_sync(sync));
+    return after_launch("spec_commit");
+}
+
+int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                         const int32_t* dev_found_inf, const int32_t* dev_parity, void* stream) {
+    if (!dev_found_inf || !dev_parity) return set_error(B200_EINVAL, "spec_repair: NULL argument");
+    RepairParams prm{dev_found_inf, dev_parity};
+    if (state_dtype == B200_F32 && copy_dtype == B200_F16)
+        return launch_tiles<SpecRepairOp<B200_F32, B200_F16>>("spec_repair", dev_table, n_tiles, prm, stream);
+    if (state_dtype == B200_F32 && copy_dtype == B200_BF16)
+        return launch_tiles<SpecRepairOp<B200_F32, B200_BF16>>("spec_repair", dev_table, n_tiles, prm, stream);
+    return set_error(B200_EDTYPE, "spec_repair: (state,copy) dtypes (%d,%d) not instantiated", state_dtype, copy_dtype);
 }
 
 int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,

@@ -211,3 +211,55 @@ def peer_gather(reduced_ptrs, local_out: torch.Tensor, bounds, dev_flag=None, sy
 
 def set_peer_grid(max_ctas: int = 0):
     _lib.check(_lib.load().b200_set_peer_grid(max_ctas), "set_peer_grid")
+
+
+# ---- speculative single-pass step (b200_fused_adam_spec / b200_spec_commit / b200_spec_repair) -------------------
+def spec_shadow_delta(numel: int, elem_size: int) -> int:
+    """Bytes from a state tensor to its shadow copy."""
+    return int(_lib.check(_lib.load().b200_spec_shadow_delta(numel, elem_size), "spec_shadow_delta", count=True))
+
+
+def spec_state_like(t: torch.Tensor, fill=None):
+    """Allocate a double-buffered state tensor shaped like ``t``: returns (primary view, whole buffer).
+    The shadow copy starts spec_shadow_delta bytes after the primary one, in the same allocation."""
+    es = t.element_size()
+    delta = spec_shadow_delta(t.numel(), es) // es
+    buf = torch.zeros(delta + t.numel(), dtype=t.dtype, device=t.device)
+    prim = buf[:t.numel()].view(t.shape)
+    if fill is not None:
+        prim.copy_(fill)
+    return prim, buf
+
+
+def spec_current(prim: torch.Tensor, buf: torch.Tensor, parity: int) -> torch.Tensor:
+    """The copy of a double-buffered state tensor that ``parity`` (0/1) makes current."""
+    if not parity:
+        return prim
+    es = prim.element_size()
+    delta = spec_shadow_delta(prim.numel(), es) // es
+    return buf[delta:delta + prim.numel()].view(prim.shape)
+
+
+def fused_adam_spec(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup], dev_flag,
+                    dev_parity, inv_scale: float = 1.0, dev_inv_scale=None, sync: StepSync | None = None, pull=None):
+    _require_cuda(table)
+    arr = (AdamGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_fused_adam_spec(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                                dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                                _addr(dev_flag), _addr(dev_parity),
+                                                ctypes.byref(sync) if sync is not None else None,
+                                                ctypes.byref(pull) if pull is not None else None, _stream()),
+               "fused_adam_spec")
+
+
+def spec_commit(state: torch.Tensor, dynamic, scale_window: int, scale_factor: float, min_scale: float, max_scale: float,
+                dev_parity, mirror: torch.Tensor | None = None, sync: StepSync | None = None):
+    _lib.check(_lib.load().b200_spec_commit(state.data_ptr(), int(dynamic), scale_window, scale_factor, min_scale, max_scale,
+                                            _addr(mirror), _addr(dev_parity),
+                                            ctypes.byref(sync) if sync is not None else None, _stream()), "spec_commit")
+
+
+def spec_repair(table: TensorTable, state_dtype, copy_dtype, dev_found_inf, dev_parity):
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_spec_repair(table.ptr, table.n_tiles, dtype_code(state_dtype), dtype_code(copy_dtype),
+                                            _addr(dev_found_inf), _addr(dev_parity), _stream()), "spec_repair")

@@ -60,8 +60,9 @@ def workload_sizes(name):
     raise SystemExit(f"unknown workload {name}")
 
 
-def config_dict(desc, world, collective="peer", note=None):
+def config_dict(desc, world, collective="peer", note=None, step_mode="spec"):
     """The `config` object both arms print (the driver compares them)."""
+    spec = step_mode == "spec" and world == 1
     if world == 1:
         coll = "none"
     elif collective == "peer":
@@ -69,7 +70,9 @@ def config_dict(desc, world, collective="peer", note=None):
     else:
         coll = "nccl all-reduce"
     return {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
-            "step": "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
+            "step": ("speculative single pass (check + unscale + AdamW + fp16 copy into double-buffered state) -> "
+                     "scaler update + commit -> repair-if-skipped") if spec else
+                    "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
             "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS, "collective": coll, "collective_note": note}
 
 
@@ -197,7 +200,7 @@ def reference_arm(args, sizes, desc):
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_dict(desc, world, args.collective),
+        "config": config_dict(desc, world, args.collective, None, args.step_mode),
         "reference_note": "reference's hot path lives in NVIDIA/apex (CUDA only, not installed); this arm times its CPU "
                           "restatement oracle/amp_step_oracle.c on the host cores (one replica, whatever N is)",
         "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": cores, "kind": "port", "cpu": cpu_model(),
@@ -230,7 +233,7 @@ def parity_block(ctx, sabotage=False):
     from apex_example_b200 import ops
     world, rank, dev, n, sizes = ctx["world"], ctx["rank"], ctx["dev"], ctx["n"], ctx["sizes"]
     gflat, state, reducer = ctx["gflat"], ctx["state"], ctx["reducer"]
-    cols = ctx["cols"]                                  # p, m, v, copy (device lists)
+    cols = ctx["cols"]()                                # p, m, v, copy as current now (device lists)
     res = {"world": world, "path": ctx["path"], "params": n}
 
     gen = torch.Generator(device=dev).manual_seed(4242 + rank)
@@ -283,6 +286,7 @@ def parity_block(ctx, sabotage=False):
     oracle.adam_list(hg, hp, hm, hv, hc, inv_scale=1.0 / LOSS_SCALE, step=ctx["step_no"][0], adam_w_mode=True,
                      check_overflow=False, **HYPER)
     ok = True
+    cols = ctx["cols"]()
     for col, want in zip(cols, (hp, hm, hv, hc)):
         for d, h in zip(col, want):
             it = torch.int32 if h.element_size() == 4 else torch.int16
@@ -300,6 +304,7 @@ def parity_block(ctx, sabotage=False):
     torch.cuda.synchronize()
     st = state.cpu()
     skipped = int(st[ops.IDX_FOUND_INF]) == 1
+    cols = ctx["cols"]()
     untouched = all(torch.equal(a, b) for ca, cb in zip(cols, snap) for a, b in zip(ca, cb))
     halved = float(st.view(torch.float32)[ops.IDX_LOSS_SCALE]) == LOSS_SCALE / 2
     res["skip_agreed"] = bool(skipped and untouched and halved)
@@ -356,6 +361,10 @@ def main():
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--peer-barrier", default="signal", choices=["signal", "nccl"],
                     help="peer path: in-kernel signal-pad hand-shake (default) or two 4-byte NCCL all-reduces")
+    ap.add_argument("--step-mode", default="spec", choices=["spec", "checked"],
+                    help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
+                         "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
+                         "check pass -> scaler update -> update in place")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
                          "'nccl' = ncclAllReduce per bucket + epilogue kernel")
@@ -418,10 +427,27 @@ def main():
 
     grads = list(torch.split(gflat, sizes))
     copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
-    p = [c.float() for c in copy]
-    m = [torch.zeros(s, device=dev) for s in sizes]
-    v = [torch.zeros(s, device=dev) for s in sizes]
+    spec = args.step_mode == "spec" and world == 1
+    if spec:
+        # double-buffered state: every p / m / v tensor is followed by its shadow copy (b200_spec_shadow_delta)
+        pb = [ops.spec_state_like(c.float(), fill=c.float()) for c in copy]
+        mb = [ops.spec_state_like(c.float()) for c in copy]
+        vb = [ops.spec_state_like(c.float()) for c in copy]
+        p, m, v = [x for x, _ in pb], [x for x, _ in mb], [x for x, _ in vb]
+        parity_word = torch.zeros(1, dtype=torch.int32, device=dev)
+    else:
+        p = [c.float() for c in copy]
+        m = [torch.zeros(s, device=dev) for s in sizes]
+        v = [torch.zeros(s, device=dev) for s in sizes]
     table = TensorTable([grads, p, m, v, copy])
+
+    def current_cols():
+        """p, m, v, copy as they are current right now (synchronises in spec mode to read the parity)."""
+        if not spec:
+            return [p, m, v, copy]
+        par = int(parity_word.item())
+        return [[ops.spec_current(x, b, par) for x, b in pb], [ops.spec_current(x, b, par) for x, b in mb],
+                [ops.spec_current(x, b, par) for x, b in vb], copy]
     check_table = TensorTable([grads])              # one column: the scheduler picks 32768-element tiles
     buckets = []
     off = 0
@@ -433,10 +459,27 @@ def main():
     ops.scaler_init(state, LOSS_SCALE)
     fstate = state.view(torch.float32)
     inv_ref, found_ref, acc_ref = fstate[ops.IDX_INV_SCALE:], state[ops.IDX_FOUND_INF:], state[ops.IDX_OVERFLOW_ACC:]
+    inv_loss_ref = fstate[ops.IDX_INV_LOSS_SCALE:]
     step_no = [0]
 
     def step(ev=None, factor_override=None):
         step_no[0] += 1
+        if spec:
+            # ONE pass: check + unscale + AdamW + copy into the shadow state; commit = scaler update + parity flip;
+            # repair exits at once unless the step was skipped
+            if ev is not None:
+                ev[2].record()
+                ev[3].record()
+                ev[0].record()
+            grp = [ops.AdamGroup(HYPER["lr"], HYPER["beta1"], HYPER["beta2"], HYPER["eps"], HYPER["weight_decay"],
+                                 step_no[0], 1, 1)]
+            ops.fused_adam_spec(table, torch.float16, torch.float32, torch.float16, grp, acc_ref, parity_word,
+                                dev_inv_scale=inv_loss_ref)
+            if ev is not None:
+                ev[1].record()
+            ops.spec_commit(state, True, 2000, 2.0, 0.0, 2.0 ** 24, parity_word)
+            ops.spec_repair(table, torch.float32, torch.float16, found_ref, parity_word)
+            return
         if use_peer:
             # ONE kernel: (hand-shake) reduce-scatter + mean + overflow check over NVLink -> flag OR
             if ev is not None:
@@ -483,7 +526,7 @@ def main():
     parity = None
     if args.parity:
         ctx = dict(world=world, rank=rank, dev=dev, n=n, sizes=sizes, gflat=gflat, state=state, reducer=reducer,
-                   cols=[p, m, v, copy], path="peer" if use_peer else ("nccl" if world > 1 else "single"),
+                   cols=current_cols, path="peer" if use_peer else ("nccl" if world > 1 else ("single-spec" if spec else "single")),
                    bounds=bounds, step=step, step_no=step_no)
         parity = parity_block(ctx, sabotage=args.parity_sabotage)
         step_no[0] -= 1                               # the skipped step did not count
@@ -554,7 +597,10 @@ def main():
             "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
     cm = sum(check_ms) / len(check_ms)
-    if world == 1:
+    if spec:
+        roof["kernel"] = "tile_kernel<AdamSpecOp<f16,f32,f16>> (b200_fused_adam_spec: check + unscale + AdamW + copy in one pass)"
+        roof["other_kernels"] = {"note": "no separate overflow-check pass: spec_commit (1 thread) and spec_repair (exits at once) follow"}
+    elif world == 1:
         roof["other_kernels"] = {"multi_tensor_check": {"ms_avg": cm, "achieved_gbs": 2 * n / (cm * 1e-3) / 1e9,
                                                         "algorithmic_bytes_per_launch": 2 * n}}
     else:
@@ -578,6 +624,8 @@ def main():
 
     extra = {}
     del table, check_table, grads, p, m, v, copy, buckets
+    if spec:
+        del pb, mb, vb
     if use_peer:
         del reducer, gflat
         pbufs.close()
@@ -639,7 +687,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_dict(desc, world, "peer" if use_peer else "nccl", peer_note),
+            "config": config_dict(desc, world, "peer" if use_peer else "nccl", peer_note, args.step_mode),
             "parity": parity, "roofline": roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks, "train": train,
         }

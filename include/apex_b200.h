@@ -371,6 +371,48 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
                             const b200_peer_pull* pull, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * S2' — speculative single-pass step: the overflow check rides on the update pass.
+ * (No counterpart in apex, whose unscale pass inspects every gradient before multi_tensor_adam
+ * starts — SURVEY.md §7.3 "overflow flag vs all-or-nothing skip".)
+ *
+ * The all-or-nothing skip forces "inspect every gradient before the first state element is
+ * overwritten", i.e. a 2 B/param pass in front of the 28 B/param update (b200_multi_tensor_check,
+ * or the peer reduce-scatter, which cannot overlap the update for the same reason).  This variant
+ * double-buffers p, m and v instead: every state tensor of the table (columns 1..3) is followed by
+ * a SHADOW copy of itself that starts b200_spec_shadow_delta(numel, elem_size) bytes after the
+ * primary one (the next 256-byte boundary).  A device word `parity` says which copy is current.
+ *
+ *   b200_fused_adam_spec : one pass — reads grad + the current p/m/v, raises *dev_flag on a
+ *                          non-finite gradient, writes the new p/m/v into the OTHER copy and the
+ *                          new model weights into column 4.  Never skipped, never destructive.
+ *   b200_spec_commit     : one thread — LossScaler.update_scale (exactly b200_scaler_update), then
+ *                          parity ^= 1 unless found_inf; advances the step counters of `sync`.
+ *   b200_spec_repair     : after a skipped step the model copy holds weights derived from the
+ *                          poisoned gradient: rewrite it from the current masters.  Exits at once
+ *                          when *dev_found_inf == 0 (every normal step), so it is always enqueued.
+ * The unscale factor must be the one of the backward that produced the gradients; because the
+ * scaler update now runs AFTER the pass, pass &state->inv_loss_scale as dev_inv_scale (not
+ * &state->inv_scale).  Same arithmetic and results as b200_fused_adam, 28 B/param of traffic, at
+ * the price of 12 B/param more resident memory.
+ * ------------------------------------------------------------------------------------------ */
+int64_t b200_spec_shadow_delta(int64_t numel, int32_t elem_size);
+
+int32_t b200_fused_adam_spec(const void* dev_table, int64_t n_tiles,
+                             int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                             const b200_adam_group* groups, int32_t n_groups,
+                             float inv_scale, const float* dev_inv_scale,
+                             int32_t* dev_flag, const int32_t* dev_parity,
+                             const b200_step_sync* sync, const b200_peer_pull* pull, void* stream);
+
+int32_t b200_spec_commit(b200_scaler_state* dev_state, int32_t mode,
+                         int32_t scale_window, float scale_factor, float min_scale, float max_scale,
+                         b200_scaler_state* mirror, int32_t* dev_parity,
+                         const b200_step_sync* sync, void* stream);
+
+int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                         const int32_t* dev_found_inf, const int32_t* dev_parity, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * b200_fused_adam_noalloc — the fused Adam step for callers that must not allocate.
  * (No counterpart in the reference: apex always goes through the torch allocator.)
  *

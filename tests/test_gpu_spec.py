@@ -1,0 +1,102 @@
+"""-m gpu tests of the speculative single-pass step (b200_fused_adam_spec / b200_spec_commit /
+b200_spec_repair): the overflow check rides on the update pass, p / m / v are double-buffered and a
+device-side parity word says which copy is current.  Same bar as the other kernels: bit-exact
+against oracle/ step by step, including skipped steps (state untouched, model copy repaired)."""
+import pytest
+import torch
+
+import oracle
+from apex_example_b200 import ops
+from apex_example_b200.tables import TensorTable
+from gpu_util import ADVERSARIAL_SIZES, assert_lists_bit_equal
+
+pytestmark = pytest.mark.gpu
+
+
+def _build(sizes, gdt, sdt, cdt, gen):
+    hp = [(torch.randn(n, generator=gen) * 0.05).to(sdt) for n in sizes]
+    hm = [(torch.randn(n, generator=gen) * 1e-3).to(sdt) for n in sizes]
+    hv = [(torch.randn(n, generator=gen) * 1e-3).square().to(sdt) for n in sizes]
+    hc = [h.to(cdt) for h in hp] if cdt is not None else None
+    dev = {}
+    for name, lst in (("p", hp), ("m", hm), ("v", hv)):
+        pairs = [ops.spec_state_like(h.cuda(), fill=h.cuda()) for h in lst]
+        dev[name] = pairs
+    dc = [h.cuda() for h in hc] if hc is not None else None
+    dg = [torch.zeros(n, dtype=gdt, device="cuda") for n in sizes]
+    cols = [dg] + [[pr for pr, _ in dev[k]] for k in "pmv"] + ([dc] if dc is not None else [])
+    return hp, hm, hv, hc, dev, dc, dg, TensorTable(cols)
+
+
+@pytest.mark.parametrize("gdt,sdt,cdt", [(torch.float16, torch.float32, torch.float16),
+                                         (torch.bfloat16, torch.float32, torch.bfloat16),
+                                         (torch.float32, torch.float32, None),
+                                         (torch.float16, torch.float16, None)])
+def test_speculative_step_matches_oracle_through_skips_and_parity_flips(gdt, sdt, cdt):
+    gen = torch.Generator().manual_seed(21)
+    sizes = [s for s in ADVERSARIAL_SIZES if s]
+    hp, hm, hv, hc, dev, dc, dg, table = _build(sizes, gdt, sdt, cdt, gen)
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    S = 1024.0
+    ops.scaler_init(state, S)
+    fstate = state.view(torch.float32)
+    parity = torch.zeros(1, dtype=torch.int32, device="cuda")
+    sc = oracle.LossScaler(loss_scale=S, scale_window=3)
+    good, expect_parity = 0, 0
+    overflow_at = {1, 4, 5}
+    for it in range(9):
+        hg = [(torch.randn(n, generator=gen) * 1e-2 * sc.loss_scale).to(gdt) for n in sizes]
+        if it in overflow_at:
+            hg[it % len(sizes)][-1] = float("inf") if it % 2 else float("nan")
+        for d, h in zip(dg, hg):
+            d.copy_(h)
+        grp = [ops.AdamGroup(1e-2, 0.9, 0.999, 1e-8, 0.01, good + 1, 1, 1)]
+        ops.fused_adam_spec(table, gdt, sdt, cdt, grp, state[ops.IDX_OVERFLOW_ACC:], parity,
+                            dev_inv_scale=fstate[ops.IDX_INV_LOSS_SCALE:])
+        ops.spec_commit(state, True, 3, 2.0, 0.0, 2.0 ** 24, parity)
+        if cdt is not None:
+            ops.spec_repair(table, sdt, cdt, state[ops.IDX_FOUND_INF:], parity)
+        inv = 1.0 / sc.loss_scale
+        skip = sc.update_scale(it in overflow_at)
+        torch.cuda.synchronize()
+        assert int(state[ops.IDX_FOUND_INF]) == int(skip) == int(it in overflow_at)
+        assert float(fstate[ops.IDX_LOSS_SCALE]) == sc.loss_scale
+        if not skip:
+            good += 1
+            expect_parity ^= 1
+            for i, g in enumerate(hg):
+                oracle.adam(g, hp[i], hm[i], hv[i], hc[i] if hc is not None else None, lr=1e-2, weight_decay=0.01,
+                            step=good, inv_scale=inv)
+        assert int(parity) == expect_parity
+        for name, want in (("p", hp), ("m", hm), ("v", hv)):
+            cur = [ops.spec_current(pr, buf, expect_parity) for pr, buf in dev[name]]
+            assert_lists_bit_equal(cur, want, f"{name} (iteration {it}, parity {expect_parity})")
+        if dc is not None:              # after a skip the repaired copy equals cast(current master) again
+            assert_lists_bit_equal(dc, hc, f"model copy (iteration {it})")
+    assert good == 6
+
+
+def test_speculative_step_never_writes_outside_its_two_copies():
+    """Sentinels right after every shadow copy (the buffers are exactly primary + padding + shadow)."""
+    gen = torch.Generator().manual_seed(3)
+    sizes = [1, 7, 4097, 65537]
+    hp, hm, hv, hc, dev, dc, dg, table = _build(sizes, torch.float16, torch.float32, torch.float16, gen)
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    ops.scaler_init(state, 1.0)
+    parity = torch.zeros(1, dtype=torch.int32, device="cuda")
+    pads = []
+    for name in "pmv":
+        for pr, buf in dev[name]:
+            delta = ops.spec_shadow_delta(pr.numel(), 4) // 4
+            if delta > pr.numel():
+                buf[pr.numel():delta] = 777.0           # the gap between the copies
+                pads.append(buf[pr.numel():delta])
+    for step in (1, 2, 3):
+        for d in dg:
+            d.normal_(0, 1e-2)
+        ops.fused_adam_spec(table, torch.float16, torch.float32, torch.float16,
+                            [ops.AdamGroup(1e-2, 0.9, 0.999, 1e-8, 0.0, step, 1, 1)], state[ops.IDX_OVERFLOW_ACC:], parity)
+        ops.spec_commit(state, True, 2000, 2.0, 0.0, 2.0 ** 24, parity)
+    torch.cuda.synchronize()
+    assert int(parity) == 1
+    assert all(bool((x == 777.0).all()) for x in pads)
