@@ -117,6 +117,12 @@ SIGNATURES = {
     "b200_spec_commit": (c_int32, [c_void_p, c_int32, c_int32, c_float, c_float, c_float, c_void_p, c_void_p,
                                    ctypes.POINTER(StepSync), c_void_p]),
     "b200_spec_repair": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p, c_void_p]),
+    "b200_table_order_for_peer_step": (c_int32, [c_void_p, c_void_p, c_int32, ctypes.POINTER(c_int64), c_int32, c_int32,
+                                                 c_int64]),
+    "b200_peer_spec_step": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup), c_int32,
+                                      c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
+                                      ctypes.POINTER(PeerPull), ctypes.POINTER(c_void_p), c_void_p, c_float,
+                                      ctypes.POINTER(PeerSync), c_int32, c_int64, c_void_p, c_int64, c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

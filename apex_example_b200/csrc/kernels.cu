@@ -839,29 +839,14 @@ __device__ __forceinline__ bool wait_failed(const int32_t* error) {
     return *reinterpret_cast<const volatile int32_t*>(error) != 0;
 }
 
+// Mean of the elements [begin, end) over all ranks' buffers, written to `reduced` at the same offsets; the
+// participating threads are numbered gtid = 0 .. stride-1 (a whole grid, or the reducer CTAs of the fused step).
 template <int DT, int kThreads, int kWorld>
-__global__ void __launch_bounds__(kThreads)
-peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __restrict__ reduced, int64_t begin,
-                   int64_t end, float factor, int32_t* flag, const __grid_constant__ PeerSync sync) {
-    using T = typename Elem<DT>::type;
+__device__ __forceinline__ void reduce_span(const PeerBufs& bufs, int world, void* __restrict__ reduced, int64_t begin,
+                                            int64_t end, float factor, int64_t gtid, int64_t stride, bool& bad) {
     constexpr int kU = (DT == B200_F32 ? 4 : 8) / kWorld > 0 ? (DT == B200_F32 ? 4 : 8) / kWorld : 1;
-    bool bad = false;
+    using T = typename Elem<DT>::type;
     T* out = reinterpret_cast<T*>(reduced);
-    const bool synced = sync.pad[0] != nullptr;
-    if (synced) {
-        // head: tell every rank "my gradients of this epoch are in place (and I am done with last epoch's
-        // reduced buffers)", then wait until every rank has said so before reading anybody's gradients
-        b200_peer_signal_pad* mine = sync.pad[sync.rank];
-        if (blockIdx.x == 0 && threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->ready[sync.rank], sync.epoch);
-        if (threadIdx.x < sync.world) wait_at_least(&mine->ready[threadIdx.x], sync.epoch, &mine->error);
-        __syncthreads();
-        if (wait_failed(&mine->error)) {      // a rank never arrived: read nobody's buffer, poison the step
-            bad = true;
-            end = begin;
-        }
-    }
-    const int64_t gtid = static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x;
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
     // every buffer starts 32-byte aligned, so element offsets that are multiples of 8 are vector-safe
     int64_t head = (kVec - (begin % kVec)) % kVec;
     if (head > end - begin) head = end - begin;
@@ -917,6 +902,29 @@ peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __res
         bad |= !is_finite(round_through<DT>(v));
         store1<DT>(out, tail0 + gtid, v);
     }
+}
+
+template <int DT, int kThreads, int kWorld>
+__global__ void __launch_bounds__(kThreads)
+peer_reduce_kernel(const __grid_constant__ PeerBufs bufs, int world, void* __restrict__ reduced, int64_t begin,
+                   int64_t end, float factor, int32_t* flag, const __grid_constant__ PeerSync sync) {
+    bool bad = false;
+    const bool synced = sync.pad[0] != nullptr;
+    if (synced) {
+        // head: tell every rank "my gradients of this epoch are in place (and I am done with last epoch's
+        // reduced buffers)", then wait until every rank has said so before reading anybody's gradients
+        b200_peer_signal_pad* mine = sync.pad[sync.rank];
+        if (blockIdx.x == 0 && threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->ready[sync.rank], sync.epoch);
+        if (threadIdx.x < sync.world) wait_at_least(&mine->ready[threadIdx.x], sync.epoch, &mine->error);
+        __syncthreads();
+        if (wait_failed(&mine->error)) {      // a rank never arrived: read nobody's buffer, poison the step
+            bad = true;
+            end = begin;
+        }
+    }
+    reduce_span<DT, kThreads, kWorld>(bufs, world, reduced, begin, end, factor,
+                                      static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x,
+                                      static_cast<int64_t>(gridDim.x) * kThreads, bad);
     if (!synced) {
         if (flag) raise_flag(flag, bad);
         return;
@@ -1015,6 +1023,191 @@ peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __
     if (gtid < n - tail0) {
         const long long i = tail0 + gtid;
         out[i] = reinterpret_cast<const T*>(reduced.p[owner_of(i)])[i];
+    }
+}
+
+// ============================================================================================
+// fused gradient mean + speculative step over peer memory: ONE kernel per rank, no serial phase
+// ============================================================================================
+// With an in-place update the reduce-scatter has to finish on every rank before the first state element may
+// be written (an overflow anywhere must stop every write everywhere), so NVLink time and HBM time add up.
+// The speculative update writes only shadow state, so nothing has to wait: the first `n_reducers` CTAs to
+// start take the REDUCE role — they walk this rank's shard chunk by chunk (mean + rounding exactly as
+// b200_peer_reduce_shard) and after each chunk publish "rank r: c chunks done" to every rank's signal pad —
+// while all other CTAs (and the reducers, once their shard is done) take the UPDATE role: they draw tiles
+// from a shared counter, wait until the owner of a tile's gradient has published its chunk, pull the reduced
+// gradient over NVLink and run the speculative Adam pass on it.  The table lists the tiles chunk-major
+// (b200_table_order_for_peer_step) so consumers trail producers by construction.  Every rank inspects every
+// reduced gradient it pulls, so each rank's overflow flag is complete on its own: no flag exchange.
+constexpr int kProgShift = 12;      // progress word = (epoch << 12) | chunks done; compared modulo 2^32
+
+__device__ __forceinline__ void wait_progress(const int32_t* p, uint32_t want, int32_t* error) {
+    const long long t0 = clock64();
+    while (static_cast<int32_t>(static_cast<uint32_t>(ld_acquire_sys(p)) - want) < 0) {
+        __nanosleep(32);
+        if (clock64() - t0 > 60000000000ll) {
+            *reinterpret_cast<volatile int32_t*>(error) = 1;
+            __threadfence();
+            break;
+        }
+    }
+}
+
+struct PeerStepParams {
+    SpecParams spec;                // update role; spec.pull says where each shard's reduced gradients live
+    PeerBufs grads;                 // reduce role: every rank's flat gradient buffer
+    void* reduced;                  // this rank's reduced buffer
+    long long begin, end;           // this rank's shard
+    long long chunk_elems;
+    float factor;
+    int world;
+    int n_reducers;
+    PeerSync sync;
+    int32_t* scratch;               // [0] role tickets [1] tile tickets [2] exits [8 + c] arrivals at chunk c
+};
+
+template <int G, int S, int C, int kThreads, int kWorld>
+__global__ void __launch_bounds__(kThreads)
+peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ PeerStepParams prm) {
+    using Op = AdamSpecOp<G, S, C>;
+    using GT = typename Elem<G>::type;
+    constexpr int kU = 2 * Op::kUnrollMul;
+    constexpr uint32_t kNone = 0xffffffffu;
+    __shared__ __align__(16) RowSlot s_slot[2];
+    __shared__ uint32_t s_tile[2];
+    __shared__ uint32_t s_idx[2];           // list index of the tile in each slot (kNone: no more tiles)
+    __shared__ int s_role;
+    b200_peer_signal_pad* mine = prm.sync.pad[prm.sync.rank];
+    unsigned* tile_ctr = reinterpret_cast<unsigned*>(prm.scratch + 1);
+    if (threadIdx.x == 0) s_role = atomicAdd(prm.scratch, 1);
+    __syncthreads();
+    const int ticket = s_role;
+    bool bad = false;
+
+    if (ticket < prm.n_reducers) {
+        // ---- reduce role --------------------------------------------------------------------------------
+        if (ticket == 0 && threadIdx.x < prm.sync.world)
+            st_release_sys(&prm.sync.pad[threadIdx.x]->ready[prm.sync.rank], prm.sync.epoch);
+        if (threadIdx.x < prm.sync.world) wait_at_least(&mine->ready[threadIdx.x], prm.sync.epoch, &mine->error);
+        __syncthreads();
+        const bool dead = wait_failed(&mine->error);        // a rank never arrived: read nobody's buffer, poison the step
+        bad |= dead;
+        const long long n_chunks = (prm.end - prm.begin + prm.chunk_elems - 1) / prm.chunk_elems;
+        const int64_t gtid = static_cast<int64_t>(ticket) * kThreads + threadIdx.x;
+        const int64_t stride = static_cast<int64_t>(prm.n_reducers) * kThreads;
+        bool rbad = false;                                   // non-finite means are seen again by whoever pulls them
+        for (long long c = 0; c < n_chunks; c++) {
+            const int64_t cb = prm.begin + c * prm.chunk_elems;
+            const int64_t ce = cb + prm.chunk_elems < prm.end ? cb + prm.chunk_elems : prm.end;
+            if (!dead) reduce_span<G, kThreads, kWorld>(prm.grads, prm.world, prm.reduced, cb, ce, prm.factor, gtid, stride, rbad);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                __threadfence();
+                if (atomicAdd(prm.scratch + 8 + c, 1) == prm.n_reducers - 1) {
+                    prm.scratch[8 + c] = 0;                  // ready for the next step
+                    __threadfence_system();
+                    const int32_t val = static_cast<int32_t>((static_cast<uint32_t>(prm.sync.epoch) << kProgShift) |
+                                                             static_cast<uint32_t>(c + 1));
+                    for (int r = 0; r < prm.sync.world; r++) st_release_sys(&prm.sync.pad[r]->progress[prm.sync.rank], val);
+                }
+            }
+        }
+    }
+
+    // ---- update role (every CTA; reducers join once their shard is done) ---------------------------------------
+    const TableView tv = open_table(table);
+    int win = 0;
+    Op::prologue(prm.spec, win);
+    const bool loader = threadIdx.x < 4;
+    uint32_t ahead = kNone;                     // thread 0: the ticket drawn one iteration early
+    if (threadIdx.x == 0) {
+        const uint32_t a = atomicAdd(tile_ctr, 1u);
+        ahead = atomicAdd(tile_ctr, 1u);
+        s_idx[0] = a < tv.n_tiles ? a : kNone;
+    }
+    __syncthreads();
+    if (loader && s_idx[0] != kNone) {
+        const uint2 e = __ldg(reinterpret_cast<const uint2*>(tv.tiles + s_idx[0]));
+        cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
+                   reinterpret_cast<const char*>(tv.rows + e.x) + threadIdx.x * 16);
+        if (threadIdx.x == 0) s_tile[0] = e.y;
+        cp_async_wait_all();
+    }
+    __syncthreads();
+    uint32_t known[kWorld];                     // progress already observed per owner (saves the acquire load)
+#pragma unroll
+    for (int r = 0; r < kWorld; r++) known[r] = static_cast<uint32_t>(prm.sync.epoch) << kProgShift;
+    int slot = 0;
+    while (s_idx[slot] != kNone) {
+        // next tile: ticket drawn last iteration -> entry -> row into the other slot; draw the ticket after that
+        if (threadIdx.x == 0) s_idx[slot ^ 1] = ahead < tv.n_tiles ? ahead : kNone;
+        if (threadIdx.x < 32) {
+            const uint32_t nxt = __shfl_sync(0xffffffffu, ahead, 0);
+            if (loader && nxt < tv.n_tiles) {
+                const uint2 e = __ldg(reinterpret_cast<const uint2*>(tv.tiles + nxt));
+                cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
+                           reinterpret_cast<const char*>(tv.rows + e.x) + threadIdx.x * 16);
+                if (threadIdx.x == 0) s_tile[slot ^ 1] = e.y;
+            }
+            if (threadIdx.x == 0 && nxt < tv.n_tiles) ahead = atomicAdd(tile_ctr, 1u);
+        }
+        const b200_table_row row = s_slot[slot].row;
+        const uint32_t tile_idx = s_tile[slot];
+        const int64_t start = static_cast<int64_t>(tile_idx) * tv.tile_elems;
+        const int64_t left = row.numel - start;
+        const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left) : static_cast<int>(tv.tile_elems);
+        // flow control: the owner of this tile's gradient must have published the chunk its last element lies in
+        {
+            const long long flat = (reinterpret_cast<const char*>(reinterpret_cast<const GT*>(row.ptr[0]) + start) -
+                                    prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT));
+            int owner = 0;
+#pragma unroll
+            for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
+            const uint32_t want = (static_cast<uint32_t>(prm.sync.epoch) << kProgShift) |
+                                  static_cast<uint32_t>((flat + n - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems + 1);
+            uint32_t have = known[0];
+#pragma unroll
+            for (int k = 1; k < kWorld; k++) have = owner == k ? known[k] : have;
+            if (static_cast<int32_t>(have - want) < 0) {
+                wait_progress(&mine->progress[owner], want, &mine->error);
+                const uint32_t now = static_cast<uint32_t>(ld_acquire_sys(&mine->progress[owner]));
+#pragma unroll
+                for (int k = 0; k < kWorld; k++) known[k] = owner == k ? now : known[k];
+                bad |= wait_failed(&mine->error);
+            }
+        }
+        const typename Op::Ctx ctx = Op::make_ctx(prm.spec, row, win, start);
+        if (row.flags & 1u) {
+            const int n8 = n & ~(kVec - 1);
+            for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kU) {
+                int64_t idx[kU];
+                bool act[kU];
+#pragma unroll
+                for (int u = 0; u < kU; u++) {
+                    const int off = base + u * kThreads * kVec;
+                    act[u] = off < n8;
+                    idx[u] = start + off;
+                }
+                Op::template vec<kU>(row, ctx, idx, act, bad);
+            }
+            const int tail = n - n8;
+            if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
+        } else {
+            for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
+        }
+        if (loader) cp_async_wait_all();
+        __syncthreads();
+        slot ^= 1;
+    }
+    Op::finish(prm.spec, bad);
+    // the last CTA to leave resets the tickets (the next launch is ordered after this one on the stream)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(prm.scratch + 2, 1) == static_cast<int>(gridDim.x) - 1) {
+            prm.scratch[0] = 0;
+            prm.scratch[1] = 0;
+            prm.scratch[2] = 0;
+        }
     }
 }
 
@@ -1507,6 +1700,96 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
     })
 #undef B200_LAUNCH_REDUCE
     return after_launch("peer_reduce_shard");
+}
+
+// ------------------------------------------------------------------------------------------------
+// b200_peer_spec_step: gradient mean + speculative step in one kernel per rank (see peer_spec_step_kernel)
+// ------------------------------------------------------------------------------------------------
+}  // extern "C" (templates need C++ linkage)
+
+template <int G, int S, int C>
+static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const PeerStepParams& in, int32_t n_reducers,
+                                 cudaStream_t st) {
+    constexpr int kThreads = 256;
+    PeerStepParams prm = in;
+#define B200_LAUNCH_STEP(W_)                                                                              \
+    {                                                                                                     \
+        auto kernel = peer_spec_step_kernel<G, S, C, kThreads, W_>;                                       \
+        static int occ_dev[64];                                                                           \
+        int& occ = occ_dev[current_device_slot()];                                                        \
+        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);                                       \
+        int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                          \
+        const int cap = g_peer_max_ctas.load();                                                           \
+        if (cap > 0 && blocks > cap) blocks = cap;                                                        \
+        if (blocks > n_tiles + n_reducers) blocks = n_tiles + n_reducers;                                 \
+        if (blocks < 2) blocks = 2;                                                                       \
+        prm.n_reducers = n_reducers < blocks - 1 ? n_reducers : static_cast<int>(blocks - 1);            \
+        if (prm.n_reducers < 1) prm.n_reducers = 1;                                                       \
+        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(dev_table, prm);                       \
+    }
+    if (prm.world <= 2) B200_LAUNCH_STEP(2)
+    else if (prm.world <= 4) B200_LAUNCH_STEP(4)
+    else B200_LAUNCH_STEP(8)
+#undef B200_LAUNCH_STEP
+    return after_launch("peer_spec_step");
+}
+
+extern "C" {
+
+int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                            int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
+                            const float* dev_inv_scale, int32_t* dev_flag, const int32_t* dev_parity,
+                            const b200_step_sync* sync, const b200_peer_pull* pull, const void* const* peer_grads,
+                            void* reduced, float factor, const b200_peer_sync* psync, int32_t n_reducers,
+                            int64_t chunk_elems, void* dev_scratch, int64_t scratch_bytes, void* stream) {
+    if (!dev_table || n_tiles <= 0) return set_error(B200_EINVAL, "peer_spec_step: empty table");
+    if (!dev_parity || !dev_flag || !pull || !peer_grads || !reduced || !psync || !dev_scratch)
+        return set_error(B200_EINVAL, "peer_spec_step: NULL argument");
+    PeerStepParams prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = to_pull(pull, prm.spec.pull, "peer_spec_step")) return rc;
+    if (prm.spec.pull.world < 2) return set_error(B200_EINVAL, "peer_spec_step: needs world >= 2 (use b200_fused_adam_spec)");
+    if (int rc = fill_adam_consts("peer_spec_step", groups, n_groups, prm.spec.grp)) return rc;
+    if (int rc = to_peer_sync(psync, prm.sync, "peer_spec_step")) return rc;
+    if (psync->world != prm.spec.pull.world) return set_error(B200_EINVAL, "peer_spec_step: sync->world != pull->world");
+    if (chunk_elems < 8 || chunk_elems % 8) return set_error(B200_EINVAL, "peer_spec_step: chunk_elems must be a multiple of 8");
+    prm.spec.pull.first_tile = 0;                        // the table is already ordered for this rank
+    prm.spec.inv_scale = inv_scale;
+    prm.spec.dev_inv_scale = dev_inv_scale;
+    prm.spec.flag = dev_flag;
+    prm.spec.parity = dev_parity;
+    prm.spec.sync = to_sync(sync);
+    prm.spec.sync.read_only = 1;
+    prm.world = prm.spec.pull.world;
+    prm.begin = prm.spec.pull.bounds[psync->rank];
+    prm.end = prm.spec.pull.bounds[psync->rank + 1];
+    prm.chunk_elems = chunk_elems;
+    prm.factor = factor;
+    prm.reduced = reduced;
+    prm.scratch = static_cast<int32_t*>(dev_scratch);
+    long long max_chunks = 0;
+    for (int r = 0; r < prm.world; r++) {
+        const long long c = (prm.spec.pull.bounds[r + 1] - prm.spec.pull.bounds[r] + chunk_elems - 1) / chunk_elems;
+        if (c > max_chunks) max_chunks = c;
+    }
+    if (max_chunks >= (1 << kProgShift))
+        return set_error(B200_ESIZE, "peer_spec_step: %lld chunks per shard, at most %d (raise chunk_elems)", max_chunks,
+                         (1 << kProgShift) - 1);
+    if (scratch_bytes < static_cast<int64_t>(8 + max_chunks) * 4)
+        return set_error(B200_ESIZE, "peer_spec_step: scratch must hold %lld bytes (zeroed once)", (8 + max_chunks) * 4);
+    for (int r = 0; r < B200_MAX_PEERS; r++) prm.grads.p[r] = r < prm.world ? peer_grads[r] : nullptr;
+    for (int r = 0; r < prm.world; r++)
+        if (!prm.grads.p[r]) return set_error(B200_EINVAL, "peer_spec_step: gradient buffer %d is NULL", r);
+    if (n_reducers < 1) n_reducers = 1;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (grad_dtype == B200_F16 && state_dtype == B200_F32 && copy_dtype == B200_F16)
+        return launch_peer_spec_step<B200_F16, B200_F32, B200_F16>(dev_table, n_tiles, prm, n_reducers, st);
+    if (grad_dtype == B200_BF16 && state_dtype == B200_F32 && copy_dtype == B200_BF16)
+        return launch_peer_spec_step<B200_BF16, B200_F32, B200_BF16>(dev_table, n_tiles, prm, n_reducers, st);
+    if (grad_dtype == B200_F32 && state_dtype == B200_F32 && copy_dtype == B200_NONE)
+        return launch_peer_spec_step<B200_F32, B200_F32, B200_NONE>(dev_table, n_tiles, prm, n_reducers, st);
+    return set_error(B200_EDTYPE, "peer_spec_step: (grad,state,copy) dtypes (%d,%d,%d) not instantiated", grad_dtype,
+                     state_dtype, copy_dtype);
 }
 
 int32_t b200_set_peer_grid(int32_t max_ctas) {

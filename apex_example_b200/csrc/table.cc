@@ -2,8 +2,10 @@
 // described in include/apex_b200.h.  Pure host code (no CUDA calls), so it is unit-tested on
 // machines without a GPU.  Replaces the per-call packing loop of apex's
 // csrc/multi_tensor_apply.cuh.
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <vector>
 
 #include "apex_b200.h"
 
@@ -97,6 +99,50 @@ int64_t b200_table_build(void* host_image, int64_t image_bytes, int32_t n_tensor
     h->total_elems = total;
     h->image_bytes = static_cast<uint64_t>(need);
     return n_tiles;
+}
+
+// Tile order for b200_peer_spec_step.  The update role of that kernel consumes reduced gradient tiles while
+// the ranks' reduce roles are still producing them, chunk by chunk, each over its own shard.  To never wait
+// for data that is far from ready, the tiles are visited CHUNK-MAJOR: first the tiles whose gradients lie in
+// chunk 0 of any shard, then chunk 1 of any shard, ...; inside a chunk index the shards are visited starting
+// with this rank's own (so at any moment the ranks pull from different owners).  A tile that straddles two
+// chunks is keyed on the later one.  Pure host code, stable, O(n_tiles log n_tiles).
+int32_t b200_table_order_for_peer_step(void* host_image, const void* local_base, int32_t grad_elem_size,
+                                       const int64_t* bounds, int32_t world, int32_t rank, int64_t chunk_elems) {
+    if (!host_image || !local_base || !bounds || world < 1 || world > B200_MAX_PEERS || rank < 0 || rank >= world ||
+        chunk_elems < 8 || (grad_elem_size != 2 && grad_elem_size != 4))
+        return b200::set_error(B200_EINVAL, "table_order_for_peer_step: bad argument");
+    char* base = static_cast<char*>(host_image);
+    b200_table_header* h = reinterpret_cast<b200_table_header*>(base);
+    if (h->magic != kMagic) return b200::set_error(B200_EINVAL, "table_order_for_peer_step: not a table image");
+    const b200_table_row* rows = reinterpret_cast<const b200_table_row*>(base + h->rows_off);
+    b200_table_tile* tiles = reinterpret_cast<b200_table_tile*>(base + h->tiles_off);
+    struct Key {
+        int64_t chunk, owner_rot, flat;
+        b200_table_tile tile;
+    };
+    std::vector<Key> keys(h->n_tiles);
+    for (uint32_t i = 0; i < h->n_tiles; i++) {
+        const b200_table_row& r = rows[tiles[i].tensor];
+        const int64_t start = static_cast<int64_t>(tiles[i].tile) * h->tile_elems;
+        const int64_t n = std::min<int64_t>(h->tile_elems, r.numel - start);
+        const int64_t flat = (static_cast<const char*>(r.ptr[0]) - static_cast<const char*>(local_base)) / grad_elem_size + start;
+        if (flat < bounds[0] || flat + n > bounds[world])
+            return b200::set_error(B200_EINVAL, "table_order_for_peer_step: tile %u lies outside the flat gradient buffer", i);
+        int owner = 0;
+        for (int k = 1; k < world; k++) owner += flat >= bounds[k] ? 1 : 0;
+        if (flat + n > bounds[owner + 1])
+            return b200::set_error(B200_EINVAL, "table_order_for_peer_step: tile %u straddles a shard boundary "
+                                                "(use tile-aligned shards)", i);
+        keys[i] = Key{(flat + n - 1 - bounds[owner]) / chunk_elems, (owner - rank + world) % world, flat, tiles[i]};
+    }
+    std::stable_sort(keys.begin(), keys.end(), [](const Key& a, const Key& b) {
+        if (a.chunk != b.chunk) return a.chunk < b.chunk;
+        if (a.owner_rot != b.owner_rot) return a.owner_rot < b.owner_rot;
+        return a.flat < b.flat;
+    });
+    for (uint32_t i = 0; i < h->n_tiles; i++) tiles[i] = keys[i].tile;
+    return 0;
 }
 
 }  // extern "C"

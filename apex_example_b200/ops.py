@@ -263,3 +263,23 @@ def spec_repair(table: TensorTable, state_dtype, copy_dtype, dev_found_inf, dev_
     _require_cuda(table)
     _lib.check(_lib.load().b200_spec_repair(table.ptr, table.n_tiles, dtype_code(state_dtype), dtype_code(copy_dtype),
                                             _addr(dev_found_inf), _addr(dev_parity), _stream()), "spec_repair")
+
+
+def peer_spec_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup], dev_flag, dev_parity,
+                   pull, peer_grad_ptrs, reduced: torch.Tensor, factor: float, psync, n_reducers: int, chunk_elems: int,
+                   scratch: torch.Tensor, inv_scale: float = 1.0, dev_inv_scale=None, sync: StepSync | None = None):
+    """Gradient mean across ranks + speculative Adam step in ONE kernel (b200_peer_spec_step)."""
+    _require_cuda(table)
+    arr = (AdamGroup * len(groups))(*groups)
+    ptrs = (ctypes.c_void_p * len(peer_grad_ptrs))(*peer_grad_ptrs)
+    _lib.check(_lib.load().b200_peer_spec_step(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                               dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                               _addr(dev_flag), _addr(dev_parity),
+                                               ctypes.byref(sync) if sync is not None else None, ctypes.byref(pull), ptrs,
+                                               reduced.data_ptr(), factor, ctypes.byref(psync), n_reducers, chunk_elems,
+                                               scratch.data_ptr(), scratch.numel() * scratch.element_size(), _stream()),
+               "peer_spec_step")
+
+
+def new_peer_step_scratch(device, max_chunks: int = 4095) -> torch.Tensor:
+    return torch.zeros(8 + max_chunks + 1, dtype=torch.int32, device=device)

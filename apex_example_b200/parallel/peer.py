@@ -195,3 +195,34 @@ class PeerGradientReducer:
         ops.peer_reduce_shard(self._grad_ptrs, b.local["reduced"], self.bounds[b.rank], self.bounds[b.rank + 1],
                               self.factor, overflow_flag)
         b.barrier(overflow_flag)                        # all shards written; flags OR-ed across ranks
+
+
+class PeerSpecStep:
+    """Gradient mean + speculative Adam step as ONE kernel per rank (b200_peer_spec_step): reducer CTAs walk
+    this rank's shard chunk by chunk and publish their progress, the other CTAs update tiles as soon as the
+    owner of their gradient has reduced them — NVLink time and HBM time overlap instead of adding up.
+    ``table`` must list its gradient column as views of ``buffers.local["grads"]``; it is re-ordered in place."""
+
+    def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, n_reducers: int = 48,
+                 chunk_elems: int = 1 << 20):
+        self.buf = buffers
+        self.bounds = list(bounds)
+        assert len(self.bounds) == buffers.world + 1
+        self.factor = (1.0 / buffers.world) if gradient_average else 1.0
+        self.n_reducers, self.chunk_elems = int(n_reducers), int(chunk_elems)
+        self.epoch = 0
+        self._pads = buffers.signal_pads()
+        self._grad_ptrs = buffers.ptrs("grads")
+        g = buffers.local["grads"]
+        self.pull = ops.make_peer_pull(g.data_ptr(), self.bounds, buffers.ptrs("reduced"), g.element_size())
+        self.table = table.order_for_peer_step(g.data_ptr(), g.element_size(), self.bounds, buffers.rank, self.chunk_elems)
+        self.scratch = ops.new_peer_step_scratch(buffers.device)
+
+    def step(self, grad_dtype, state_dtype, copy_dtype, groups, dev_flag, dev_parity, dev_inv_scale=None, inv_scale=1.0,
+             sync=None):
+        b = self.buf
+        self.epoch += 1
+        psync = ops.make_peer_sync(self._pads, b.rank, self.epoch)
+        ops.peer_spec_step(self.table, grad_dtype, state_dtype, copy_dtype, groups, dev_flag, dev_parity, self.pull,
+                           self._grad_ptrs, b.local["reduced"], self.factor, psync, self.n_reducers, self.chunk_elems,
+                           self.scratch, inv_scale=inv_scale, dev_inv_scale=dev_inv_scale, sync=sync)

@@ -139,6 +139,16 @@ class TensorTable:
     def ptr(self) -> int:
         return self.dev.data_ptr()
 
+    def order_for_peer_step(self, local_base_ptr: int, grad_elem_size: int, bounds, rank: int, chunk_elems: int):
+        """Re-order the tile list for b200_peer_spec_step (chunk-major, this rank's shard first) and upload
+        the image again.  ``bounds`` are the world+1 tile-aligned shard offsets of the flat gradient buffer."""
+        b = (ctypes.c_int64 * len(bounds))(*[int(x) for x in bounds])
+        _lib.check(_lib.load().b200_table_order_for_peer_step(self.image.data_ptr(), local_base_ptr, grad_elem_size, b,
+                                                              len(bounds) - 1, rank, chunk_elems),
+                   "table_order_for_peer_step")
+        self.dev.copy_(self.image, non_blocking=True)
+        return self
+
 
 def signature_of(columns) -> tuple:
     """Cheap identity of a list of columns: the device addresses (sizes are fixed per parameter)."""

@@ -62,9 +62,11 @@ def workload_sizes(name):
 
 def config_dict(desc, world, collective="peer", note=None, step_mode="spec"):
     """The `config` object both arms print (the driver compares them)."""
-    spec = step_mode == "spec" and world == 1
+    spec = step_mode == "spec" and (world == 1 or collective == "peer")
     if world == 1:
         coll = "none"
+    elif collective == "peer" and spec:
+        coll = "peer-memory reduce-scatter fused with the speculative update in one kernel (chunk-wise progress flags)"
     elif collective == "peer":
         coll = "peer-memory reduce-scatter + pull-in-optimizer"
     else:
@@ -258,9 +260,9 @@ def parity_block(ctx, sabotage=False):
     wflag = oracle.peer_reduce(host_all, want_mean, 0, n, factor) if world > 1 else oracle.check(host_all[0])
     if world == 1:
         want_mean = host_all[0]
-    if ctx["path"] == "peer":
+    if ctx["path"] in ("peer", "peer-spec"):
         b0, b1 = ctx["bounds"][rank], ctx["bounds"][rank + 1]
-        got = reducer.buf.local["reduced"][b0:b1].cpu()
+        got = ctx["pbufs"].local["reduced"][b0:b1].cpu()
         res["mean_bit_exact"] = bool(torch.equal(got.view(torch.int16), want_mean[b0:b1].view(torch.int16)))
         step_grad = want_mean
     elif world > 1:
@@ -310,6 +312,8 @@ def parity_block(ctx, sabotage=False):
     res["skip_agreed"] = bool(skipped and untouched and halved)
     del snap
     mean_good = res["mean_ok"] if ctx["path"] == "nccl" else res["mean_bit_exact"]
+    if ctx["path"] == "peer-spec":
+        res["overflow_seen_by"] = "every rank's own update role (it inspects every reduced gradient it pulls)"
     good = res["state_bit_exact"] and res["skip_agreed"] and mean_good
     if world > 1:
         t = torch.tensor([1 if good else 0], device=dev)
@@ -365,6 +369,8 @@ def main():
                     help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
                          "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
                          "check pass -> scaler update -> update in place")
+    ap.add_argument("--reducers", type=int, default=48, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
+    ap.add_argument("--chunk-elems", type=int, default=1 << 20, help="spec mode, N>1: progress granularity of the reduce role")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
                          "'nccl' = ncclAllReduce per bucket + epilogue kernel")
@@ -408,6 +414,7 @@ def main():
             use_peer = False
             peer_note = "peer access not available between all GPUs: fell back to NCCL"
     reducer, bounds = None, None
+    spec = args.step_mode == "spec" and (world == 1 or use_peer)
     if use_peer:
         from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
         from apex_example_b200.tables import tile_aligned_shards
@@ -417,7 +424,8 @@ def main():
             acc += s_
         pbufs = PeerBuffers(n, torch.float16)
         bounds, first_tiles = tile_aligned_shards(offs, sizes, n, world, return_first_tiles=True)
-        reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles, barrier=args.peer_barrier)
+        if not spec:                               # the fused speculative step brings its own hand-shake
+            reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles, barrier=args.peer_barrier)
         gflat = pbufs.local["grads"]
     else:
         gflat = torch.empty(n, dtype=torch.float16, device=dev)
@@ -427,7 +435,6 @@ def main():
 
     grads = list(torch.split(gflat, sizes))
     copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
-    spec = args.step_mode == "spec" and world == 1
     if spec:
         # double-buffered state: every p / m / v tensor is followed by its shadow copy (b200_spec_shadow_delta)
         pb = [ops.spec_state_like(c.float(), fill=c.float()) for c in copy]
@@ -440,6 +447,10 @@ def main():
         m = [torch.zeros(s, device=dev) for s in sizes]
         v = [torch.zeros(s, device=dev) for s in sizes]
     table = TensorTable([grads, p, m, v, copy])
+    stepper = None
+    if spec and use_peer:
+        from apex_example_b200.parallel.peer import PeerSpecStep
+        stepper = PeerSpecStep(pbufs, bounds, table, n_reducers=args.reducers, chunk_elems=args.chunk_elems)
 
     def current_cols():
         """p, m, v, copy as they are current right now (synchronises in spec mode to read the parity)."""
@@ -473,8 +484,16 @@ def main():
                 ev[0].record()
             grp = [ops.AdamGroup(HYPER["lr"], HYPER["beta1"], HYPER["beta2"], HYPER["eps"], HYPER["weight_decay"],
                                  step_no[0], 1, 1)]
-            ops.fused_adam_spec(table, torch.float16, torch.float32, torch.float16, grp, acc_ref, parity_word,
-                                dev_inv_scale=inv_loss_ref)
+            if stepper is not None:
+                # N > 1: ONE kernel does the gradient mean (reducer CTAs, chunk-wise progress) AND the update
+                if factor_override is not None:
+                    keep, stepper.factor = stepper.factor, factor_override
+                stepper.step(torch.float16, torch.float32, torch.float16, grp, acc_ref, parity_word, dev_inv_scale=inv_loss_ref)
+                if factor_override is not None:
+                    stepper.factor = keep
+            else:
+                ops.fused_adam_spec(table, torch.float16, torch.float32, torch.float16, grp, acc_ref, parity_word,
+                                    dev_inv_scale=inv_loss_ref)
             if ev is not None:
                 ev[1].record()
             ops.spec_commit(state, True, 2000, 2.0, 0.0, 2.0 ** 24, parity_word)
@@ -526,7 +545,8 @@ def main():
     parity = None
     if args.parity:
         ctx = dict(world=world, rank=rank, dev=dev, n=n, sizes=sizes, gflat=gflat, state=state, reducer=reducer,
-                   cols=current_cols, path="peer" if use_peer else ("nccl" if world > 1 else ("single-spec" if spec else "single")),
+                   pbufs=pbufs if use_peer else None,
+                   cols=current_cols, path=("peer-spec" if spec else "peer") if use_peer else ("nccl" if world > 1 else ("single-spec" if spec else "single")),
                    bounds=bounds, step=step, step_no=step_no)
         parity = parity_block(ctx, sabotage=args.parity_sabotage)
         step_no[0] -= 1                               # the skipped step did not count
@@ -534,7 +554,7 @@ def main():
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "parity block failed", "parity": parity}), flush=True)
             if use_peer:
-                del reducer
+                del reducer, stepper, table
                 pbufs.close()
             if world > 1:
                 dist.destroy_process_group()
@@ -597,13 +617,19 @@ def main():
             "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
     cm = sum(check_ms) / len(check_ms)
-    if spec:
+    if spec and world > 1:
+        roof["kernel"] = ("peer_spec_step_kernel<f16,f32,f16> (b200_peer_spec_step: reduce-scatter + mean over NVLink by the "
+                          "reducer CTAs, check + unscale + AdamW + copy by the others, one launch)")
+        roof["nvlink"] = {"bytes_in_per_gpu": 2 * n * 2 * (world - 1) // world, "note": "(N-1)/N of the gradient bytes twice: "
+                          "peers' gradients into the reduce role, reduced shards into the update role",
+                          "inbound_gbs": 2 * n * 2 * (world - 1) / world / (adam_avg_ms * 1e-3) / 1e9, "nvlink_peak_gbs_per_dir": 900.0}
+    elif spec:
         roof["kernel"] = "tile_kernel<AdamSpecOp<f16,f32,f16>> (b200_fused_adam_spec: check + unscale + AdamW + copy in one pass)"
         roof["other_kernels"] = {"note": "no separate overflow-check pass: spec_commit (1 thread) and spec_repair (exits at once) follow"}
     elif world == 1:
         roof["other_kernels"] = {"multi_tensor_check": {"ms_avg": cm, "achieved_gbs": 2 * n / (cm * 1e-3) / 1e9,
                                                         "algorithmic_bytes_per_launch": 2 * n}}
-    else:
+    elif not spec:
         # gradient mean: every rank receives (N-1)/N of the buffer over NVLink in the reduce phase and
         # again while the optimizer pulls the reduced shards; bus bandwidth as NCCL defines it
         nbytes = n * 2
@@ -627,7 +653,7 @@ def main():
     if spec:
         del pb, mb, vb
     if use_peer:
-        del reducer, gflat
+        del reducer, gflat, stepper
         pbufs.close()
     else:
         del gflat

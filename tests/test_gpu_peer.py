@@ -208,6 +208,81 @@ def _worker_ipc(rank, world, port, barrier="nccl", repeats=1):
     dist.destroy_process_group()
 
 
+def _worker_fused(rank, world, port, repeats):
+    """Real ranks: b200_peer_spec_step over CUDA-IPC buffers, against the oracle, incl. a one-rank overflow."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from apex_example_b200.parallel.peer import PeerBuffers, PeerSpecStep
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 600000]
+    offs, total = _layout(sizes)
+    bounds = tile_aligned_shards(offs, sizes, total, world)
+    bufs = PeerBuffers(total, torch.float16)
+    S = 256.0
+    gen = torch.Generator().manual_seed(7)
+    hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+    hm, hv = [torch.zeros(n) for n in sizes], [torch.zeros(n) for n in sizes]
+    hc = [h.half() for h in hp]
+    st = {k: [ops.spec_state_like(h.cuda(), fill=h.cuda()) for h in lst] for k, lst in (("p", hp), ("m", hm), ("v", hv))}
+    dc = [h.cuda() for h in hc]
+    g_local = bufs.local["grads"]
+    table = TensorTable([[g_local[o:o + n] for o, n in zip(offs, sizes)]] + [[a for a, _ in st[k]] for k in "pmv"] + [dc])
+    stepper = PeerSpecStep(bufs, bounds, table, n_reducers=24, chunk_elems=32768)
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    ops.scaler_init(state, S)
+    fs = state.view(torch.float32)
+    parity = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def launch(step_no, lr=1e-3, wd=0.01):
+        stepper.step(torch.float16, torch.float32, torch.float16, [ops.AdamGroup(lr, 0.9, 0.999, 1e-8, wd, step_no, 1, 1)],
+                     state[ops.IDX_OVERFLOW_ACC:], parity, dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
+        ops.spec_commit(state, True, 2000, 2.0, 0.0, 2.0 ** 24, parity)
+        ops.spec_repair(stepper.table, torch.float32, torch.float16, state[ops.IDX_FOUND_INF:], parity)
+
+    scale, good, par = S, 0, 0
+    for it in range(4):
+        host_all = [(torch.randn(total, generator=torch.Generator().manual_seed(100 * it + r)) * 1e-2 * scale).half()
+                    for r in range(world)]
+        if it == 1:
+            host_all[world - 1][total - 1] = float("inf")          # overflow on the LAST rank only
+        g_local.copy_(host_all[rank])
+        launch(good + 1)
+        torch.cuda.synchronize()
+        want = torch.zeros(total, dtype=torch.float16)
+        wflag = oracle.peer_reduce(host_all, want, 0, total, 1.0 / world)
+        assert wflag == (1 if it == 1 else 0)
+        assert int(state.cpu()[ops.IDX_FOUND_INF]) == wflag, f"rank {rank}: skip decision at iteration {it}"
+        if not wflag:
+            good += 1
+            par ^= 1
+            for i, (o, n) in enumerate(zip(offs, sizes)):
+                oracle.adam(want[o:o + n].clone(), hp[i], hm[i], hv[i], hc[i], lr=1e-3, weight_decay=0.01, step=good,
+                            inv_scale=1.0 / scale)
+        else:
+            scale /= 2
+        assert int(parity) == par
+        for k, h in (("p", hp), ("m", hm), ("v", hv)):
+            assert_lists_bit_equal([ops.spec_current(a, b, par) for a, b in st[k]], h, f"{k} (rank {rank}, it {it})")
+        assert_lists_bit_equal(dc, hc, f"copy (rank {rank}, it {it})")
+    for _ in range(repeats):                 # hammer the progress protocol: back-to-back steps, no host sync
+        launch(good + 1, lr=0.0, wd=0.0)
+    torch.cuda.synchronize()
+    bufs.check_signals()
+    del table, stepper
+    bufs.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_real_rank_fused_reduce_and_speculative_step(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run under gpurun --gpus {world})")
+    mp.spawn(_worker_fused, args=(world, _free_port(), 100), nprocs=world, join=True)
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("barrier,repeats", [("nccl", 1), ("signal", 200)])
 def test_real_rank_ipc_reduce_and_fused_pull(barrier, repeats, world):

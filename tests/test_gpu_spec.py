@@ -100,3 +100,88 @@ def test_speculative_step_never_writes_outside_its_two_copies():
     torch.cuda.synchronize()
     assert int(parity) == 1
     assert all(bool((x == 777.0).all()) for x in pads)
+
+
+# ---- fused gradient mean + speculative step (b200_peer_spec_step) ---------------------------------------------
+def _layout(sizes):
+    offs, off = [], 0
+    for n in sizes:
+        off += (-off) % 16
+        offs.append(off)
+        off += n
+    return offs, off
+
+
+@pytest.mark.parametrize("world,chunk", [(2, 8192), (4, 4096), (4, 1 << 20), (8, 16384)])
+def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
+    """All `world` ranks live on ONE GPU: each has its own buffers, state, signal pad, scratch and stream, and
+    its kernel (grid capped to 12 CTAs so that all of them are resident together) really waits for the others'
+    progress words.  Two steps (the second flips parity back) + one overflow step injected on the last rank."""
+    from apex_example_b200.tables import tile_aligned_shards
+    ops.set_peer_grid(12)
+    try:
+        gen = torch.Generator().manual_seed(40 + world)
+        sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 33000]
+        offs, total = _layout(sizes)
+        bounds = tile_aligned_shards(offs, sizes, total, world)
+        S = 256.0
+        pads = torch.zeros(world, 32, dtype=torch.int32, device="cuda")
+        pad_ptrs = [pads.data_ptr() + 128 * r for r in range(world)]
+        grads = [torch.zeros(total, dtype=torch.float16, device="cuda") for _ in range(world)]
+        reduced = [torch.full((total,), float("nan"), dtype=torch.float16, device="cuda") for _ in range(world)]
+        hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+        hm, hv = [torch.zeros(n) for n in sizes], [torch.zeros(n) for n in sizes]
+        hc = [h.half() for h in hp]
+        ranks = []
+        for r in range(world):
+            st = {k: [ops.spec_state_like(h.cuda(), fill=h.cuda()) for h in lst] for k, lst in (("p", hp), ("m", hm), ("v", hv))}
+            dc = [h.cuda() for h in hc]
+            cols = [[grads[r][o:o + n] for o, n in zip(offs, sizes)]] + [[a for a, _ in st[k]] for k in "pmv"] + [dc]
+            table = TensorTable(cols).order_for_peer_step(grads[r].data_ptr(), 2, bounds, r, chunk)
+            state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+            ops.scaler_init(state, S)
+            ranks.append(dict(st=st, dc=dc, table=table, state=state, parity=torch.zeros(1, dtype=torch.int32, device="cuda"),
+                              scratch=ops.new_peer_step_scratch("cuda"), stream=torch.cuda.Stream(),
+                              pull=ops.make_peer_pull(grads[r].data_ptr(), bounds, [t.data_ptr() for t in reduced], 2)))
+        torch.cuda.synchronize()
+        scale, good, par = S, 0, 0
+        for it in range(4):
+            host_g = [(torch.randn(total, generator=gen) * 1e-2 * scale).half() for _ in range(world)]
+            if it == 2:
+                host_g[world - 1][total - 3] = float("inf")
+            for r in range(world):
+                grads[r].copy_(host_g[r])
+            torch.cuda.synchronize()
+            for r, rk in enumerate(ranks):
+                with torch.cuda.stream(rk["stream"]):
+                    fs = rk["state"].view(torch.float32)
+                    ops.peer_spec_step(rk["table"], torch.float16, torch.float32, torch.float16,
+                                       [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, good + 1, 1, 1)],
+                                       rk["state"][ops.IDX_OVERFLOW_ACC:], rk["parity"], rk["pull"],
+                                       [g.data_ptr() for g in grads], reduced[r], 1.0 / world,
+                                       ops.make_peer_sync(pad_ptrs, r, it + 1), 3, chunk, rk["scratch"],
+                                       dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
+                    ops.spec_commit(rk["state"], True, 2000, 2.0, 0.0, 2.0 ** 24, rk["parity"])
+                    ops.spec_repair(rk["table"], torch.float32, torch.float16, rk["state"][ops.IDX_FOUND_INF:], rk["parity"])
+            torch.cuda.synchronize()
+            assert int(pads[:, 16].abs().sum()) == 0, "a bounded wait timed out"
+            want = torch.zeros(total, dtype=torch.float16)
+            wflag = oracle.peer_reduce(host_g, want, 0, total, 1.0 / world)
+            assert wflag == (1 if it == 2 else 0)
+            if not wflag:
+                good += 1
+                par ^= 1
+                for i, (o, n) in enumerate(zip(offs, sizes)):
+                    oracle.adam(want[o:o + n].clone(), hp[i], hm[i], hv[i], hc[i], lr=1e-3, weight_decay=0.01, step=good,
+                                inv_scale=1.0 / scale)
+            else:
+                scale /= 2
+            for r, rk in enumerate(ranks):
+                assert int(rk["state"][ops.IDX_FOUND_INF]) == wflag, f"rank {r}, iteration {it}"
+                assert int(rk["parity"]) == par
+                for k, h in (("p", hp), ("m", hm), ("v", hv)):
+                    assert_lists_bit_equal([ops.spec_current(a, b, par) for a, b in rk["st"][k]], h, f"{k} (rank {r}, it {it})")
+                assert_lists_bit_equal(rk["dc"], hc, f"copy (rank {r}, it {it})")
+        assert good == 3
+    finally:
+        ops.set_peer_grid(0)
