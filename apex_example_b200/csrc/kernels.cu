@@ -1067,7 +1067,7 @@ struct PeerStepParams {
 };
 
 template <int G, int S, int C, int kThreads, int kWorld>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 2)          // two CTAs per SM, like the plain step kernel: <= 128 registers
 peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ PeerStepParams prm) {
     using Op = AdamSpecOp<G, S, C>;
     using GT = typename Elem<G>::type;
