@@ -46,6 +46,8 @@ class PeerSync(ctypes.Structure):            # b200_peer_sync
 
 
 SIGNAL_PAD_BYTES = 128
+PEER_STEP_MAX_CHUNKS = 1024
+PEER_STEP_PAD_BYTES = 128 + MAX_PEERS * PEER_STEP_MAX_CHUNKS * 4     # signal pad followed by the progress board
 
 
 class PeerPull(ctypes.Structure):            # b200_peer_pull
@@ -122,7 +124,7 @@ SIGNATURES = {
     "b200_peer_spec_step": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup), c_int32,
                                       c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                       ctypes.POINTER(PeerPull), ctypes.POINTER(c_void_p), c_void_p, c_float,
-                                      ctypes.POINTER(PeerSync), c_int32, c_int64, c_void_p, c_int64, c_void_p]),
+                                      ctypes.POINTER(PeerSync), c_int64, c_void_p, c_int64, c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

@@ -1031,19 +1031,31 @@ peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __
 // ============================================================================================
 // With an in-place update the reduce-scatter has to finish on every rank before the first state element may
 // be written (an overflow anywhere must stop every write everywhere), so NVLink time and HBM time add up.
-// The speculative update writes only shadow state, so nothing has to wait: the first `n_reducers` CTAs to
-// start take the REDUCE role — they walk this rank's shard chunk by chunk (mean + rounding exactly as
-// b200_peer_reduce_shard) and after each chunk publish "rank r: c chunks done" to every rank's signal pad —
-// while all other CTAs (and the reducers, once their shard is done) take the UPDATE role: they draw tiles
-// from a shared counter, wait until the owner of a tile's gradient has published its chunk, pull the reduced
-// gradient over NVLink and run the speculative Adam pass on it.  The table lists the tiles chunk-major
-// (b200_table_order_for_peer_step) so consumers trail producers by construction.  Every rank inspects every
+// The speculative update writes only shadow state, so nothing has to wait, and every CTA does both jobs at
+// once: per iteration it (1) starts the loads of one reduce PIECE (2048 elements of this rank's shard from
+// every rank's gradient buffer) as cp.async copies into shared memory — no registers are held while they
+// cross NVLink —, (2) runs the speculative Adam pass on one update tile, whose HBM traffic hides the NVLink
+// round trip, and (3) folds the piece (mean + roundings exactly as b200_peer_reduce_shard) into this rank's
+// `reduced` buffer.  Pieces and tiles are drawn from two shared counters.  When the last piece of a chunk is
+// folded the chunk is announced on every rank's progress board (an array of epoch flags that follows the
+// signal pad in peer memory); a tile is processed only after the owner of its gradient has announced the
+// chunk it lies in, and a CTA blocks on that only when there are no pieces left to hand out (so producers
+// can never be starved by waiting consumers).  The table lists the tiles chunk-major
+// (b200_table_order_for_peer_step): consumers trail producers by construction.  Every rank inspects every
 // reduced gradient it pulls, so each rank's overflow flag is complete on its own: no flag exchange.
-constexpr int kProgShift = 12;      // progress word = (epoch << 12) | chunks done; compared modulo 2^32
+constexpr int kPieceElems = 256 * kVec;
 
-__device__ __forceinline__ void wait_progress(const int32_t* p, uint32_t want, int32_t* error) {
+__device__ __forceinline__ int32_t* peer_board(b200_peer_signal_pad* pad) {
+    return reinterpret_cast<int32_t*>(pad) + sizeof(b200_peer_signal_pad) / 4;
+}
+
+__device__ __forceinline__ bool epoch_reached(const int32_t* p, int32_t epoch) {
+    return static_cast<int32_t>(static_cast<uint32_t>(ld_acquire_sys(p)) - static_cast<uint32_t>(epoch)) >= 0;
+}
+
+__device__ __forceinline__ void wait_epoch(const int32_t* p, int32_t epoch, int32_t* error) {
     const long long t0 = clock64();
-    while (static_cast<int32_t>(static_cast<uint32_t>(ld_acquire_sys(p)) - want) < 0) {
+    while (!epoch_reached(p, epoch)) {
         __nanosleep(32);
         if (clock64() - t0 > 60000000000ll) {
             *reinterpret_cast<volatile int32_t*>(error) = 1;
@@ -1054,76 +1066,98 @@ __device__ __forceinline__ void wait_progress(const int32_t* p, uint32_t want, i
 }
 
 struct PeerStepParams {
-    SpecParams spec;                // update role; spec.pull says where each shard's reduced gradients live
-    PeerBufs grads;                 // reduce role: every rank's flat gradient buffer
+    SpecParams spec;                // update half; spec.pull says where each shard's reduced gradients live
+    PeerBufs grads;                 // reduce half: every rank's flat gradient buffer
     void* reduced;                  // this rank's reduced buffer
     long long begin, end;           // this rank's shard
-    long long chunk_elems;
+    long long chunk_elems;          // announcement granularity, a multiple of kPieceElems
     float factor;
     int world;
-    int n_reducers;
     PeerSync sync;
-    int32_t* scratch;               // [0] role tickets [1] tile tickets [2] exits [8 + c] arrivals at chunk c
+    int32_t* scratch;               // [1] tile tickets [2] exits [3] piece tickets [8 + c] pieces of chunk c folded
 };
+
+template <int DT>
+__device__ __forceinline__ void lds8(const void* smem, Raw8<DT>& raw) {
+    const uint4* q = reinterpret_cast<const uint4*>(smem);
+    const uint4 a = q[0];
+    raw.r[0] = a.x; raw.r[1] = a.y; raw.r[2] = a.z; raw.r[3] = a.w;
+    if constexpr (DT == B200_F32) {
+        const uint4 b = q[1];
+        raw.r[4] = b.x; raw.r[5] = b.y; raw.r[6] = b.z; raw.r[7] = b.w;
+    }
+}
 
 template <int G, int S, int C, int kThreads, int kWorld>
 __global__ void __launch_bounds__(kThreads, 2)          // two CTAs per SM, like the plain step kernel: <= 128 registers
 peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ PeerStepParams prm) {
+    static_assert(kThreads * kVec == kPieceElems, "one 8-element group per thread and piece");
     using Op = AdamSpecOp<G, S, C>;
     using GT = typename Elem<G>::type;
     constexpr int kU = 2 * Op::kUnrollMul;
     constexpr uint32_t kNone = 0xffffffffu;
+    constexpr int kCopies = static_cast<int>(sizeof(GT)) * kVec / 16;      // 16-byte cp.async per thread, rank and piece
+    extern __shared__ __align__(16) unsigned char s_stage[];               // kWorld x kPieceElems gradient elements
     __shared__ __align__(16) RowSlot s_slot[2];
     __shared__ uint32_t s_tile[2];
-    __shared__ uint32_t s_idx[2];           // list index of the tile in each slot (kNone: no more tiles)
-    __shared__ int s_role;
+    __shared__ uint32_t s_idx[2];           // tile (index into the table's list) of the iteration using the slot
+    __shared__ uint32_t s_pc[2];            // reduce piece that iteration starts and folds
+    __shared__ int s_go[2];                 // 1: the tile's gradient has been announced, process it
     b200_peer_signal_pad* mine = prm.sync.pad[prm.sync.rank];
+    const int32_t* board = peer_board(mine);
     unsigned* tile_ctr = reinterpret_cast<unsigned*>(prm.scratch + 1);
-    if (threadIdx.x == 0) s_role = atomicAdd(prm.scratch, 1);
-    __syncthreads();
-    const int ticket = s_role;
+    unsigned* piece_ctr = reinterpret_cast<unsigned*>(prm.scratch + 3);
+    const int32_t epoch = prm.sync.epoch;
     bool bad = false;
 
-    if (ticket < prm.n_reducers) {
-        // ---- reduce role --------------------------------------------------------------------------------
-        if (ticket == 0 && threadIdx.x < prm.sync.world)
-            st_release_sys(&prm.sync.pad[threadIdx.x]->ready[prm.sync.rank], prm.sync.epoch);
-        if (threadIdx.x < prm.sync.world) wait_at_least(&mine->ready[threadIdx.x], prm.sync.epoch, &mine->error);
-        __syncthreads();
-        const bool dead = wait_failed(&mine->error);        // a rank never arrived: read nobody's buffer, poison the step
-        bad |= dead;
-        const long long n_chunks = (prm.end - prm.begin + prm.chunk_elems - 1) / prm.chunk_elems;
-        const int64_t gtid = static_cast<int64_t>(ticket) * kThreads + threadIdx.x;
-        const int64_t stride = static_cast<int64_t>(prm.n_reducers) * kThreads;
-        bool rbad = false;                                   // non-finite means are seen again by whoever pulls them
-        for (long long c = 0; c < n_chunks; c++) {
-            const int64_t cb = prm.begin + c * prm.chunk_elems;
-            const int64_t ce = cb + prm.chunk_elems < prm.end ? cb + prm.chunk_elems : prm.end;
-            if (!dead) reduce_span<G, kThreads, kWorld>(prm.grads, prm.world, prm.reduced, cb, ce, prm.factor, gtid, stride, rbad);
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                __threadfence();
-                if (atomicAdd(prm.scratch + 8 + c, 1) == prm.n_reducers - 1) {
-                    prm.scratch[8 + c] = 0;                  // ready for the next step
-                    __threadfence_system();
-                    const int32_t val = static_cast<int32_t>((static_cast<uint32_t>(prm.sync.epoch) << kProgShift) |
-                                                             static_cast<uint32_t>(c + 1));
-                    for (int r = 0; r < prm.sync.world; r++) st_release_sys(&prm.sync.pad[r]->progress[prm.sync.rank], val);
-                }
-            }
-        }
-    }
+    // every rank's gradients of this epoch must be in place before anybody's buffer is read
+    if (blockIdx.x == 0 && threadIdx.x < prm.sync.world)
+        st_release_sys(&prm.sync.pad[threadIdx.x]->ready[prm.sync.rank], epoch);
+    if (threadIdx.x < prm.sync.world) wait_at_least(&mine->ready[threadIdx.x], epoch, &mine->error);
+    __syncthreads();
+    const bool dead = wait_failed(&mine->error);            // a rank never arrived: read nobody's buffer, poison the step
+    bad |= dead;
 
-    // ---- update role (every CTA; reducers join once their shard is done) ---------------------------------------
+    const long long shard = prm.end - prm.begin;
+    const uint32_t n_pieces = static_cast<uint32_t>((shard + kPieceElems - 1) / kPieceElems);
+    const bool vec_ok = (prm.begin % kVec) == 0;             // cp.async needs 16-byte aligned sources
     const TableView tv = open_table(table);
     int win = 0;
     Op::prologue(prm.spec, win);
     const bool loader = threadIdx.x < 4;
-    uint32_t ahead = kNone;                     // thread 0: the ticket drawn one iteration early
+
+    // thread 0 only: tickets drawn one iteration ahead, and the last (owner, chunk) seen announced
+    uint32_t ahead_tile = kNone, ahead_piece = kNone;
+    int seen_owner = -1;
+    long long seen_chunk = -1;
+    auto tile_ready = [&](int sl, bool block) -> int {      // thread 0, after ITS OWN 16 bytes of the row have arrived
+        const char* g0 = reinterpret_cast<const char*>(s_slot[sl].row.ptr[0]);
+        const long long flat = (g0 - prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT)) +
+                               static_cast<long long>(s_tile[sl]) * tv.tile_elems;
+        int owner = 0;
+#pragma unroll
+        for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
+        long long last = flat + tv.tile_elems;               // the tile may be shorter (end of its tensor): a chunk late at worst
+        if (last > prm.spec.pull.bounds[owner + 1]) last = prm.spec.pull.bounds[owner + 1];
+        const long long chunk = (last - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
+        if (owner == seen_owner && chunk == seen_chunk) return 1;
+        const int32_t* f = board + owner * B200_PEER_STEP_MAX_CHUNKS + chunk;
+        if (block) wait_epoch(f, epoch, &mine->error);
+        if (epoch_reached(f, epoch) || wait_failed(&mine->error)) {
+            seen_owner = owner;
+            seen_chunk = chunk;
+            return 1;
+        }
+        return 0;
+    };
+
     if (threadIdx.x == 0) {
-        const uint32_t a = atomicAdd(tile_ctr, 1u);
-        ahead = atomicAdd(tile_ctr, 1u);
-        s_idx[0] = a < tv.n_tiles ? a : kNone;
+        const uint32_t t0 = atomicAdd(tile_ctr, 1u);
+        const uint32_t p0 = atomicAdd(piece_ctr, 1u);
+        s_idx[0] = t0 < tv.n_tiles ? t0 : kNone;
+        s_pc[0] = p0 < n_pieces ? p0 : kNone;
+        ahead_tile = t0 < tv.n_tiles ? atomicAdd(tile_ctr, 1u) : kNone;
+        ahead_piece = p0 < n_pieces ? atomicAdd(piece_ctr, 1u) : kNone;
     }
     __syncthreads();
     if (loader && s_idx[0] != kNone) {
@@ -1133,80 +1167,132 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         if (threadIdx.x == 0) s_tile[0] = e.y;
         cp_async_wait_all();
     }
+    if (threadIdx.x == 0) s_go[0] = s_idx[0] != kNone ? tile_ready(0, s_pc[0] == kNone) : 0;
     __syncthreads();
-    uint32_t known[kWorld];                     // progress already observed per owner (saves the acquire load)
-#pragma unroll
-    for (int r = 0; r < kWorld; r++) known[r] = static_cast<uint32_t>(prm.sync.epoch) << kProgShift;
+
     int slot = 0;
-    while (s_idx[slot] != kNone) {
-        // next tile: ticket drawn last iteration -> entry -> row into the other slot; draw the ticket after that
-        if (threadIdx.x == 0) s_idx[slot ^ 1] = ahead < tv.n_tiles ? ahead : kNone;
+    while (s_idx[slot] != kNone || s_pc[slot] != kNone) {
+        const uint32_t tile = s_idx[slot], pc = s_pc[slot];
+        const bool go = tile != kNone && s_go[slot] != 0;
+        // ---- the other slot: the next tile (the same one again if it was not ready) and the next piece
         if (threadIdx.x < 32) {
-            const uint32_t nxt = __shfl_sync(0xffffffffu, ahead, 0);
-            if (loader && nxt < tv.n_tiles) {
+            uint32_t nxt = kNone;
+            if (threadIdx.x == 0) {
+                const bool keep = tile != kNone && !go;
+                nxt = keep ? tile : (ahead_tile < tv.n_tiles ? ahead_tile : kNone);
+                s_idx[slot ^ 1] = nxt;
+                s_pc[slot ^ 1] = ahead_piece < n_pieces ? ahead_piece : kNone;
+            }
+            nxt = __shfl_sync(0xffffffffu, nxt, 0);
+            if (loader && nxt != kNone) {
                 const uint2 e = __ldg(reinterpret_cast<const uint2*>(tv.tiles + nxt));
                 cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
                            reinterpret_cast<const char*>(tv.rows + e.x) + threadIdx.x * 16);
                 if (threadIdx.x == 0) s_tile[slot ^ 1] = e.y;
             }
-            if (threadIdx.x == 0 && nxt < tv.n_tiles) ahead = atomicAdd(tile_ctr, 1u);
-        }
-        const b200_table_row row = s_slot[slot].row;
-        const uint32_t tile_idx = s_tile[slot];
-        const int64_t start = static_cast<int64_t>(tile_idx) * tv.tile_elems;
-        const int64_t left = row.numel - start;
-        const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left) : static_cast<int>(tv.tile_elems);
-        // flow control: the owner of this tile's gradient must have published the chunk its last element lies in
-        {
-            const long long flat = (reinterpret_cast<const char*>(reinterpret_cast<const GT*>(row.ptr[0]) + start) -
-                                    prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT));
-            int owner = 0;
-#pragma unroll
-            for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
-            const uint32_t want = (static_cast<uint32_t>(prm.sync.epoch) << kProgShift) |
-                                  static_cast<uint32_t>((flat + n - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems + 1);
-            uint32_t have = known[0];
-#pragma unroll
-            for (int k = 1; k < kWorld; k++) have = owner == k ? known[k] : have;
-            if (static_cast<int32_t>(have - want) < 0) {
-                wait_progress(&mine->progress[owner], want, &mine->error);
-                const uint32_t now = static_cast<uint32_t>(ld_acquire_sys(&mine->progress[owner]));
-#pragma unroll
-                for (int k = 0; k < kWorld; k++) known[k] = owner == k ? now : known[k];
-                bad |= wait_failed(&mine->error);
+            if (threadIdx.x == 0) {                          // tickets for the iteration after the next one
+                if (go && ahead_tile < tv.n_tiles) ahead_tile = atomicAdd(tile_ctr, 1u);
+                if (tile == kNone) ahead_tile = kNone;
+                if (ahead_piece < n_pieces) ahead_piece = atomicAdd(piece_ctr, 1u);
             }
         }
-        const typename Op::Ctx ctx = Op::make_ctx(prm.spec, row, win, start);
-        if (row.flags & 1u) {
-            const int n8 = n & ~(kVec - 1);
-            for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kU) {
-                int64_t idx[kU];
-                bool act[kU];
+        // ---- (1) start this iteration's reduce piece: every rank's slice -> shared memory, asynchronously
+        const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
+        const long long pe = pb + kPieceElems < prm.end ? pb + kPieceElems : prm.end;
+        const bool piece = pc != kNone && !dead;
+        const bool staged = piece && vec_ok && pe - pb == kPieceElems;
+        if (staged) {
 #pragma unroll
-                for (int u = 0; u < kU; u++) {
-                    const int off = base + u * kThreads * kVec;
-                    act[u] = off < n8;
-                    idx[u] = start + off;
+            for (int r = 0; r < kWorld; r++) {
+                if (r < prm.world) {
+                    const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
+                                      threadIdx.x * (kVec * sizeof(GT));
+                    unsigned char* dst = s_stage + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT);
+#pragma unroll
+                    for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
                 }
-                Op::template vec<kU>(row, ctx, idx, act, bad);
             }
-            const int tail = n - n8;
-            if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
-        } else {
-            for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
         }
-        if (loader) cp_async_wait_all();
+        // ---- (2) the update tile (its HBM traffic hides the NVLink round trip of the piece)
+        if (go) {
+            const b200_table_row row = s_slot[slot].row;
+            const int64_t start = static_cast<int64_t>(s_tile[slot]) * tv.tile_elems;
+            const int64_t left = row.numel - start;
+            const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left) : static_cast<int>(tv.tile_elems);
+            const typename Op::Ctx ctx = Op::make_ctx(prm.spec, row, win, start);
+            if (row.flags & 1u) {
+                const int n8 = n & ~(kVec - 1);
+                for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kU) {
+                    int64_t idx[kU];
+                    bool act[kU];
+#pragma unroll
+                    for (int u = 0; u < kU; u++) {
+                        const int off = base + u * kThreads * kVec;
+                        act[u] = off < n8;
+                        idx[u] = start + off;
+                    }
+                    Op::template vec<kU>(row, ctx, idx, act, bad);
+                }
+                const int tail = n - n8;
+                if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
+            } else {
+                for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
+            }
+        }
+        // ---- (3) fold the piece: fp32 sum in rank order, one rounding, x factor, second rounding
+        bool rbad = false;                                   // a non-finite mean is seen again by whoever pulls it
+        cp_async_wait_all();                                 // this thread's slices (and its part of the next row)
+        if (staged) {
+            float acc[kVec];
+            Raw8<G> raw;
+            lds8<G>(s_stage + (threadIdx.x * kVec) * sizeof(GT), raw);
+            unpack8<G>(raw, acc);
+#pragma unroll
+            for (int r = 1; r < kWorld; r++) {
+                if (r < prm.world) {
+                    float f[kVec];
+                    lds8<G>(s_stage + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT), raw);
+                    unpack8<G>(raw, f);
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < kVec; i++) acc[i] = __fmul_rn(round_through<G>(acc[i]), prm.factor);
+            store8<G>(prm.reduced, pb + threadIdx.x * kVec, acc);
+        } else if (piece) {                                  // ragged last piece / unaligned shard: plain loads
+            reduce_span<G, kThreads, kWorld>(prm.grads, prm.world, prm.reduced, pb, pe, prm.factor, threadIdx.x, kThreads, rbad);
+        }
+        __syncthreads();
+        // ---- (4) thread 0: count the folded piece (announce its chunk if it was the last), then see whether
+        //          the next tile may run; blocking is allowed only when the next iteration has no piece to start
+        if (threadIdx.x == 0) {
+            if (pc != kNone) {
+                const long long c = (pb - prm.begin) / prm.chunk_elems;
+                const long long c_end = (c + 1) * prm.chunk_elems < shard ? (c + 1) * prm.chunk_elems : shard;
+                const int in_chunk = static_cast<int>((c_end - c * prm.chunk_elems + kPieceElems - 1) / kPieceElems);
+                __threadfence();
+                if (atomicAdd(prm.scratch + 8 + c, 1) == in_chunk - 1) {
+                    prm.scratch[8 + c] = 0;                  // ready for the next step
+                    __threadfence_system();
+                    for (int r = 0; r < prm.sync.world; r++)
+                        st_release_sys(peer_board(prm.sync.pad[r]) + prm.sync.rank * B200_PEER_STEP_MAX_CHUNKS + c, epoch);
+                }
+            }
+            s_go[slot ^ 1] = s_idx[slot ^ 1] != kNone ? tile_ready(slot ^ 1, s_pc[slot ^ 1] == kNone) : 0;
+        }
         __syncthreads();
         slot ^= 1;
     }
+    bad |= wait_failed(&mine->error);
     Op::finish(prm.spec, bad);
     // the last CTA to leave resets the tickets (the next launch is ordered after this one on the stream)
     __syncthreads();
     if (threadIdx.x == 0) {
         if (atomicAdd(prm.scratch + 2, 1) == static_cast<int>(gridDim.x) - 1) {
-            prm.scratch[0] = 0;
             prm.scratch[1] = 0;
             prm.scratch[2] = 0;
+            prm.scratch[3] = 0;
         }
     }
 }
@@ -1708,24 +1794,32 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
 }  // extern "C" (templates need C++ linkage)
 
 template <int G, int S, int C>
-static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const PeerStepParams& in, int32_t n_reducers,
+static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const PeerStepParams& prm, int64_t n_pieces,
                                  cudaStream_t st) {
     constexpr int kThreads = 256;
-    PeerStepParams prm = in;
+    const size_t smem = static_cast<size_t>(prm.world <= 2 ? 2 : prm.world <= 4 ? 4 : 8) * kPieceElems * sizeof(typename Elem<G>::type);
 #define B200_LAUNCH_STEP(W_)                                                                              \
     {                                                                                                     \
         auto kernel = peer_spec_step_kernel<G, S, C, kThreads, W_>;                                       \
         static int occ_dev[64];                                                                           \
         int& occ = occ_dev[current_device_slot()];                                                        \
-        if (occ == 0) occ = resident_ctas_per_sm(kernel, kThreads);                                       \
+        if (occ == 0) {                                                                                   \
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)); \
+            if (e != cudaSuccess) return cuda_fail(e, "peer_spec_step: cudaFuncSetAttribute");            \
+            int n = 0;                                                                                    \
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, smem) != cudaSuccess || n < 1) { \
+                cudaGetLastError();                                                                       \
+                n = 1;                                                                                    \
+            }                                                                                             \
+            occ = n;                                                                                      \
+        }                                                                                                 \
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                          \
         const int cap = g_peer_max_ctas.load();                                                           \
         if (cap > 0 && blocks > cap) blocks = cap;                                                        \
-        if (blocks > n_tiles + n_reducers) blocks = n_tiles + n_reducers;                                 \
-        if (blocks < 2) blocks = 2;                                                                       \
-        prm.n_reducers = n_reducers < blocks - 1 ? n_reducers : static_cast<int>(blocks - 1);            \
-        if (prm.n_reducers < 1) prm.n_reducers = 1;                                                       \
-        kernel<<<static_cast<unsigned>(blocks), kThreads, 0, st>>>(dev_table, prm);                       \
+        const int64_t work = n_tiles > n_pieces ? n_tiles : n_pieces;                                     \
+        if (blocks > work) blocks = work;                                                                 \
+        if (blocks < 1) blocks = 1;                                                                       \
+        kernel<<<static_cast<unsigned>(blocks), kThreads, smem, st>>>(dev_table, prm);                    \
     }
     if (prm.world <= 2) B200_LAUNCH_STEP(2)
     else if (prm.world <= 4) B200_LAUNCH_STEP(4)
@@ -1740,8 +1834,8 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
                             int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
                             const float* dev_inv_scale, int32_t* dev_flag, const int32_t* dev_parity,
                             const b200_step_sync* sync, const b200_peer_pull* pull, const void* const* peer_grads,
-                            void* reduced, float factor, const b200_peer_sync* psync, int32_t n_reducers,
-                            int64_t chunk_elems, void* dev_scratch, int64_t scratch_bytes, void* stream) {
+                            void* reduced, float factor, const b200_peer_sync* psync, int64_t chunk_elems,
+                            void* dev_scratch, int64_t scratch_bytes, void* stream) {
     if (!dev_table || n_tiles <= 0) return set_error(B200_EINVAL, "peer_spec_step: empty table");
     if (!dev_parity || !dev_flag || !pull || !peer_grads || !reduced || !psync || !dev_scratch)
         return set_error(B200_EINVAL, "peer_spec_step: NULL argument");
@@ -1752,7 +1846,8 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
     if (int rc = fill_adam_consts("peer_spec_step", groups, n_groups, prm.spec.grp)) return rc;
     if (int rc = to_peer_sync(psync, prm.sync, "peer_spec_step")) return rc;
     if (psync->world != prm.spec.pull.world) return set_error(B200_EINVAL, "peer_spec_step: sync->world != pull->world");
-    if (chunk_elems < 8 || chunk_elems % 8) return set_error(B200_EINVAL, "peer_spec_step: chunk_elems must be a multiple of 8");
+    if (chunk_elems < kPieceElems || chunk_elems % kPieceElems)
+        return set_error(B200_EINVAL, "peer_spec_step: chunk_elems must be a multiple of %d", kPieceElems);
     prm.spec.pull.first_tile = 0;                        // the table is already ordered for this rank
     prm.spec.inv_scale = inv_scale;
     prm.spec.dev_inv_scale = dev_inv_scale;
@@ -1772,22 +1867,22 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
         const long long c = (prm.spec.pull.bounds[r + 1] - prm.spec.pull.bounds[r] + chunk_elems - 1) / chunk_elems;
         if (c > max_chunks) max_chunks = c;
     }
-    if (max_chunks >= (1 << kProgShift))
-        return set_error(B200_ESIZE, "peer_spec_step: %lld chunks per shard, at most %d (raise chunk_elems)", max_chunks,
-                         (1 << kProgShift) - 1);
+    if (max_chunks > B200_PEER_STEP_MAX_CHUNKS)
+        return set_error(B200_ESIZE, "peer_spec_step: %lld chunks per shard, the progress board holds %d (raise chunk_elems)",
+                         max_chunks, B200_PEER_STEP_MAX_CHUNKS);
     if (scratch_bytes < static_cast<int64_t>(8 + max_chunks) * 4)
         return set_error(B200_ESIZE, "peer_spec_step: scratch must hold %lld bytes (zeroed once)", (8 + max_chunks) * 4);
     for (int r = 0; r < B200_MAX_PEERS; r++) prm.grads.p[r] = r < prm.world ? peer_grads[r] : nullptr;
     for (int r = 0; r < prm.world; r++)
         if (!prm.grads.p[r]) return set_error(B200_EINVAL, "peer_spec_step: gradient buffer %d is NULL", r);
-    if (n_reducers < 1) n_reducers = 1;
+    const int64_t n_pieces = (prm.end - prm.begin + kPieceElems - 1) / kPieceElems;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (grad_dtype == B200_F16 && state_dtype == B200_F32 && copy_dtype == B200_F16)
-        return launch_peer_spec_step<B200_F16, B200_F32, B200_F16>(dev_table, n_tiles, prm, n_reducers, st);
+        return launch_peer_spec_step<B200_F16, B200_F32, B200_F16>(dev_table, n_tiles, prm, n_pieces, st);
     if (grad_dtype == B200_BF16 && state_dtype == B200_F32 && copy_dtype == B200_BF16)
-        return launch_peer_spec_step<B200_BF16, B200_F32, B200_BF16>(dev_table, n_tiles, prm, n_reducers, st);
+        return launch_peer_spec_step<B200_BF16, B200_F32, B200_BF16>(dev_table, n_tiles, prm, n_pieces, st);
     if (grad_dtype == B200_F32 && state_dtype == B200_F32 && copy_dtype == B200_NONE)
-        return launch_peer_spec_step<B200_F32, B200_F32, B200_NONE>(dev_table, n_tiles, prm, n_reducers, st);
+        return launch_peer_spec_step<B200_F32, B200_F32, B200_NONE>(dev_table, n_tiles, prm, n_pieces, st);
     return set_error(B200_EDTYPE, "peer_spec_step: (grad,state,copy) dtypes (%d,%d,%d) not instantiated", grad_dtype,
                      state_dtype, copy_dtype);
 }

@@ -95,6 +95,7 @@ class PeerBuffers:
         as addresses valid in this process (b200_peer_signal_pad, zero-initialised by the allocator)."""
         if self.signal_ptrs is None:
             self._n_pads = count
+            self._real_pads = count          # how many of them are signal pads (the rest may be a progress board)
             lib = _lib.load()
             with torch.cuda.device(self.device):
                 ptr = ctypes.c_void_p()
@@ -122,7 +123,7 @@ class PeerBuffers:
 
     def check_signals(self):
         """Raise if a bounded in-kernel wait gave up (synchronises)."""
-        if self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:, 16].any().item()):
+        if self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:self._real_pads, 16].any().item()):
             raise RuntimeError("libapex_b200: a cross-GPU wait timed out (a rank did not reach the step)")
 
     def barrier(self, flag: torch.Tensor | None = None):
@@ -140,7 +141,7 @@ class PeerBuffers:
         lib = _lib.load()
         with torch.cuda.device(self.device):
             torch.cuda.synchronize()
-            timed_out = self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:, 16].any().item())
+            timed_out = self.signal_ptrs is not None and bool(self._signal_view.view(-1, 32)[:self._real_pads, 16].any().item())
             for p in self._opened:
                 lib.b200_peer_close(p)
             self._opened = []
@@ -198,20 +199,29 @@ class PeerGradientReducer:
 
 
 class PeerSpecStep:
-    """Gradient mean + speculative Adam step as ONE kernel per rank (b200_peer_spec_step): reducer CTAs walk
-    this rank's shard chunk by chunk and publish their progress, the other CTAs update tiles as soon as the
-    owner of their gradient has reduced them — NVLink time and HBM time overlap instead of adding up.
-    ``table`` must list its gradient column as views of ``buffers.local["grads"]``; it is re-ordered in place."""
+    """Gradient mean + speculative Adam step as ONE kernel per rank (b200_peer_spec_step): every CTA keeps one
+    reduce piece of this rank's shard in flight (cp.async into shared memory) while it updates a tile, and a
+    tile is updated as soon as the owner of its gradient has announced the chunk it lies in — NVLink time and
+    HBM time overlap instead of adding up.  ``table`` must list its gradient column as views of
+    ``buffers.local["grads"]``; it is re-ordered in place.  Must be the first user of the buffers' signal pads
+    (the progress board lives right behind the pad)."""
 
-    def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, n_reducers: int = 48,
-                 chunk_elems: int = 1 << 20):
+    def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, chunk_elems: int | None = None):
         self.buf = buffers
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1
         self.factor = (1.0 / buffers.world) if gradient_average else 1.0
-        self.n_reducers, self.chunk_elems = int(n_reducers), int(chunk_elems)
+        shard = max(b - a for a, b in zip(self.bounds, self.bounds[1:]))
+        if chunk_elems is None:
+            chunk_elems = 1 << 19
+        min_chunk = -(-shard // _lib.PEER_STEP_MAX_CHUNKS)
+        chunk_elems = max(int(chunk_elems), min_chunk)
+        self.chunk_elems = -(-chunk_elems // 2048) * 2048
         self.epoch = 0
-        self._pads = buffers.signal_pads()
+        if buffers.signal_ptrs is not None and buffers._n_pads < _lib.PEER_STEP_PAD_BYTES // 128:
+            raise RuntimeError("PeerSpecStep must allocate the signal pads itself (pad + progress board)")
+        self._pads = buffers.signal_pads(count=_lib.PEER_STEP_PAD_BYTES // 128)
+        buffers._real_pads = 1               # one signal pad; the other 128-byte units are the progress board
         self._grad_ptrs = buffers.ptrs("grads")
         g = buffers.local["grads"]
         self.pull = ops.make_peer_pull(g.data_ptr(), self.bounds, buffers.ptrs("reduced"), g.element_size())
@@ -224,5 +234,5 @@ class PeerSpecStep:
         self.epoch += 1
         psync = ops.make_peer_sync(self._pads, b.rank, self.epoch)
         ops.peer_spec_step(self.table, grad_dtype, state_dtype, copy_dtype, groups, dev_flag, dev_parity, self.pull,
-                           self._grad_ptrs, b.local["reduced"], self.factor, psync, self.n_reducers, self.chunk_elems,
+                           self._grad_ptrs, b.local["reduced"], self.factor, psync, self.chunk_elems,
                            self.scratch, inv_scale=inv_scale, dev_inv_scale=dev_inv_scale, sync=sync)

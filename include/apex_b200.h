@@ -328,9 +328,7 @@ typedef struct b200_peer_signal_pad {
     int32_t done[B200_MAX_PEERS];           /* done[r]:  (epoch << 1) | overflow bit of rank r */
     int32_t error;                          /* set when a bounded wait gave up */
     int32_t local_flag, ticket;             /* kernel-internal */
-    int32_t progress[B200_MAX_PEERS];       /* progress[r]: (epoch << 12) | chunks of rank r's shard reduced so far
-                                               (b200_peer_spec_step) */
-    int32_t reserved[5];
+    int32_t reserved[13];
 } b200_peer_signal_pad;                     /* 128 bytes */
 
 typedef struct b200_peer_sync {
@@ -419,19 +417,26 @@ int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_d
  * b200_peer_reduce_shard followed by b200_fused_adam_peer costs NVLink time PLUS HBM time: the
  * in-place update may not start before every rank has reduced (and inspected) its whole shard.
  * With the speculative update (b200_fused_adam_spec) nothing is destroyed, so both halves run at
- * the same time inside one kernel: the first `n_reducers` CTAs reduce this rank's shard chunk by
- * chunk (`chunk_elems` elements; arithmetic exactly as b200_peer_reduce_shard) and publish their
- * progress to every rank's signal pad; all other CTAs — and the reducers once they are done — draw
- * tiles from a shared counter, wait for the owning rank's progress, pull the reduced gradient over
- * NVLink and run the speculative Adam pass.  Every rank inspects every reduced gradient it pulls,
- * so *dev_flag is complete without a flag exchange; follow with b200_spec_commit and
+ * the same time inside one kernel, in every CTA: per iteration a CTA starts the loads of one
+ * 2048-element PIECE of this rank's shard from every rank's gradient buffer as cp.async copies
+ * into shared memory, runs the speculative Adam pass on one update tile while they cross NVLink,
+ * then folds the piece (arithmetic exactly as b200_peer_reduce_shard) into `reduced`.  When the
+ * last piece of a `chunk_elems`-element chunk is folded, the chunk is announced to every rank:
+ * each rank's signal pad is FOLLOWED by a progress board of B200_MAX_PEERS x
+ * B200_PEER_STEP_MAX_CHUNKS int32 epoch flags (board[owner][chunk]), i.e. the pad allocation must
+ * be B200_PEER_STEP_PAD_BYTES long and zeroed.  A tile is updated only after the owner of its
+ * gradient has announced the chunk it lies in.  Every rank inspects every reduced gradient it
+ * pulls, so *dev_flag is complete without a flag exchange; follow with b200_spec_commit and
  * b200_spec_repair exactly as after b200_fused_adam_spec.
  *
  * Requirements: shards that never cut a tile (tables.tile_aligned_shards); the table's tile list
  * ordered by b200_table_order_for_peer_step (chunk-major, own shard first) with the same
- * chunk_elems; `dev_scratch` >= (8 + chunks per shard) * 4 bytes, zeroed once; `psync->epoch`
- * growing by one per step on every rank; at most 4095 chunks per shard.
+ * chunk_elems (a multiple of 2048, at most B200_PEER_STEP_MAX_CHUNKS chunks per shard);
+ * `dev_scratch` >= (8 + chunks per shard) * 4 bytes, zeroed once; `psync->epoch` growing by one per
+ * step on every rank.
  * ------------------------------------------------------------------------------------------ */
+#define B200_PEER_STEP_MAX_CHUNKS 1024
+#define B200_PEER_STEP_PAD_BYTES  (128 + B200_MAX_PEERS * B200_PEER_STEP_MAX_CHUNKS * 4)
 int32_t b200_table_order_for_peer_step(void* host_image, const void* local_base, int32_t grad_elem_size,
                                        const int64_t* bounds, int32_t world, int32_t rank, int64_t chunk_elems);
 
@@ -441,8 +446,7 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles,
                             float inv_scale, const float* dev_inv_scale,
                             int32_t* dev_flag, const int32_t* dev_parity, const b200_step_sync* sync,
                             const b200_peer_pull* pull, const void* const* peer_grads, void* reduced,
-                            float factor, const b200_peer_sync* psync,
-                            int32_t n_reducers, int64_t chunk_elems,
+                            float factor, const b200_peer_sync* psync, int64_t chunk_elems,
                             void* dev_scratch, int64_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------

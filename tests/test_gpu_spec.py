@@ -112,11 +112,11 @@ def _layout(sizes):
     return offs, off
 
 
-@pytest.mark.parametrize("world,chunk", [(2, 8192), (4, 4096), (4, 1 << 20), (8, 16384)])
+@pytest.mark.parametrize("world,chunk", [(2, 8192), (4, 2048), (4, 1 << 20), (8, 16384)])
 def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
     """All `world` ranks live on ONE GPU: each has its own buffers, state, signal pad, scratch and stream, and
     its kernel (grid capped to 12 CTAs so that all of them are resident together) really waits for the others'
-    progress words.  Two steps (the second flips parity back) + one overflow step injected on the last rank."""
+    progress flags.  Two steps (the second flips parity back) + one overflow step injected on the last rank."""
     from apex_example_b200.tables import tile_aligned_shards
     ops.set_peer_grid(12)
     try:
@@ -125,8 +125,8 @@ def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
         offs, total = _layout(sizes)
         bounds = tile_aligned_shards(offs, sizes, total, world)
         S = 256.0
-        pads = torch.zeros(world, 32, dtype=torch.int32, device="cuda")
-        pad_ptrs = [pads.data_ptr() + 128 * r for r in range(world)]
+        pads = torch.zeros(world, ops.PEER_STEP_PAD_WORDS, dtype=torch.int32, device="cuda")   # pad + progress board
+        pad_ptrs = [pads.data_ptr() + 4 * ops.PEER_STEP_PAD_WORDS * r for r in range(world)]
         grads = [torch.zeros(total, dtype=torch.float16, device="cuda") for _ in range(world)]
         reduced = [torch.full((total,), float("nan"), dtype=torch.float16, device="cuda") for _ in range(world)]
         hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
@@ -159,7 +159,7 @@ def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
                                        [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, good + 1, 1, 1)],
                                        rk["state"][ops.IDX_OVERFLOW_ACC:], rk["parity"], rk["pull"],
                                        [g.data_ptr() for g in grads], reduced[r], 1.0 / world,
-                                       ops.make_peer_sync(pad_ptrs, r, it + 1), 3, chunk, rk["scratch"],
+                                       ops.make_peer_sync(pad_ptrs, r, it + 1), chunk, rk["scratch"],
                                        dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
                     ops.spec_commit(rk["state"], True, 2000, 2.0, 0.0, 2.0 ** 24, rk["parity"])
                     ops.spec_repair(rk["table"], torch.float32, torch.float16, rk["state"][ops.IDX_FOUND_INF:], rk["parity"])
