@@ -1129,7 +1129,7 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
     // thread 0 only: tickets drawn one iteration ahead, and the last (owner, chunk) seen announced
     uint32_t ahead_tile = kNone, ahead_piece = kNone;
     int seen_owner = -1;
-    long long seen_chunk = -1;
+    long long seen_lo = 0, seen_hi = -1;
     auto tile_ready = [&](int sl, bool block) -> int {      // thread 0, after ITS OWN 16 bytes of the row have arrived
         const char* g0 = reinterpret_cast<const char*>(s_slot[sl].row.ptr[0]);
         const long long flat = (g0 - prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT)) +
@@ -1139,16 +1139,20 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
         long long last = flat + tv.tile_elems;               // the tile may be shorter (end of its tensor): a chunk late at worst
         if (last > prm.spec.pull.bounds[owner + 1]) last = prm.spec.pull.bounds[owner + 1];
-        const long long chunk = (last - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
-        if (owner == seen_owner && chunk == seen_chunk) return 1;
-        const int32_t* f = board + owner * B200_PEER_STEP_MAX_CHUNKS + chunk;
-        if (block) wait_epoch(f, epoch, &mine->error);
-        if (epoch_reached(f, epoch) || wait_failed(&mine->error)) {
-            seen_owner = owner;
-            seen_chunk = chunk;
-            return 1;
+        // pieces are folded by whichever CTA draws them, so chunks complete in any order: every chunk the tile
+        // touches has to be announced (one or two, chunks are at least a tile long)
+        const long long c0 = (flat - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
+        const long long c1 = (last - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
+        if (owner == seen_owner && c0 >= seen_lo && c1 <= seen_hi) return 1;
+        for (long long c = c0; c <= c1; c++) {
+            const int32_t* f = board + owner * B200_PEER_STEP_MAX_CHUNKS + c;
+            if (block) wait_epoch(f, epoch, &mine->error);
+            if (!epoch_reached(f, epoch) && !wait_failed(&mine->error)) return 0;
         }
-        return 0;
+        seen_owner = owner;
+        seen_lo = c0;
+        seen_hi = c1;
+        return 1;
     };
 
     if (threadIdx.x == 0) {
