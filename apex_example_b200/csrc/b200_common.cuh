@@ -262,6 +262,10 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
     const uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" :: "r"(s), "l"(gmem_src) : "memory");
 }
+__device__ __forceinline__ void cp_async8(volatile void* smem_dst, const void* gmem_src) {
+    const uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(const_cast<void*>(smem_dst)));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(s), "l"(gmem_src) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // The descriptor chain (tile entry -> row -> data) is three dependent memory latencies.  To keep

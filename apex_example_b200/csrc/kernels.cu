@@ -1088,6 +1088,111 @@ __device__ __forceinline__ void lds8(const void* smem, Raw8<DT>& raw) {
     }
 }
 
+// One update tile of the fused step (the body of walk_tiles for one tile).  Kept inlined: ptxas 12.9 crashes on a
+// __noinline__ version; the fused kernel instead keeps its scheduling state in shared memory so that the Adam
+// loop has the registers to itself.
+template <class Op, int kThreads, int kU>
+__device__ __forceinline__ bool step_one_tile(const typename Op::Params& sp, const b200_table_row* row_in, uint32_t tile_idx,
+                                           uint32_t tile_elems, int win) {
+    bool bad = false;
+    const b200_table_row row = *row_in;
+    const int64_t start = static_cast<int64_t>(tile_idx) * tile_elems;
+    const int64_t left = row.numel - start;
+    const int n = left < static_cast<int64_t>(tile_elems) ? static_cast<int>(left) : static_cast<int>(tile_elems);
+    const typename Op::Ctx ctx = Op::make_ctx(sp, row, win, start);
+    if (row.flags & 1u) {
+        const int n8 = n & ~(kVec - 1);
+        for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kU) {
+            int64_t idx[kU];
+            bool act[kU];
+#pragma unroll
+            for (int u = 0; u < kU; u++) {
+                const int off = base + u * kThreads * kVec;
+                act[u] = off < n8;
+                idx[u] = start + off;
+            }
+            Op::template vec<kU>(row, ctx, idx, act, bad);
+        }
+        const int tail = n - n8;
+        if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
+    } else {
+        for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
+    }
+    return bad;
+}
+
+struct StepShared {                     // the fused step's scheduling state (shared memory, not registers)
+    const b200_table_row* rows;
+    const b200_table_tile* tiles;
+    uint32_t n_tiles, tile_elems, n_pieces;
+    int vec_ok, win;
+    uint32_t idx[2];                    // tile (index into the table's list) of the iteration using the slot
+    uint32_t tile[2];                   // ... its tile index inside its tensor
+    uint32_t pc[2];                     // reduce piece that iteration starts and folds
+    int go[2];                          // 1: the tile's gradient has been announced, process it
+    uint32_t idx1;                      // list index of the next iteration's tile
+    uint2 e1[2];                        // e1[s]: (tensor, tile) entry of the tile that goes into slot s next (8-byte cp.async)
+    uint32_t piece_next;                // piece of the next iteration
+    int seen_owner;
+    long long seen_lo, seen_hi;         // chunks of seen_owner already seen announced
+};
+
+// Thread 0: may the tile in slot `sl` run?  Every chunk its gradient touches must have been announced by its owner.
+template <class GT, int kWorld>
+__device__ __forceinline__ int step_tile_ready(const PeerStepParams& prm, const b200_table_row* row, uint32_t tile_idx,
+                                            uint32_t tile_elems, StepShared* sc, bool block) {
+    b200_peer_signal_pad* mine = prm.sync.pad[prm.sync.rank];
+    const char* g0 = reinterpret_cast<const char*>(row->ptr[0]);      // thread 0's own 16 bytes of the row have arrived
+    const long long flat = (g0 - prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT)) +
+                           static_cast<long long>(tile_idx) * tile_elems;
+    int owner = 0;
+#pragma unroll
+    for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
+    long long last = flat + tile_elems;                                // the tile may be shorter (end of its tensor)
+    if (last > prm.spec.pull.bounds[owner + 1]) last = prm.spec.pull.bounds[owner + 1];
+    // pieces are folded by whichever CTA draws them, so chunks complete in any order: every chunk the tile touches
+    // has to be announced (one or two: chunks are at least a tile long)
+    const long long c0 = (flat - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
+    const long long c1 = (last - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
+    if (owner == sc->seen_owner && c0 >= sc->seen_lo && c1 <= sc->seen_hi) return 1;
+    const int32_t* board = peer_board(mine);
+    for (long long c = c0; c <= c1; c++) {
+        const int32_t* f = board + owner * B200_PEER_STEP_MAX_CHUNKS + c;
+        if (block) wait_epoch(f, prm.sync.epoch, &mine->error);
+        if (!epoch_reached(f, prm.sync.epoch) && !wait_failed(&mine->error)) return 0;
+    }
+    sc->seen_owner = owner;
+    sc->seen_lo = c0;
+    sc->seen_hi = c1;
+    return 1;
+}
+
+// A warp has stored its part of a folded piece: count it; the warp that completes a chunk announces it everywhere.
+__device__ __forceinline__ void step_count_piece(const PeerStepParams& prm, long long pb, int warps_per_piece) {
+    __threadfence();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+        const long long shard = prm.end - prm.begin;
+        const long long c = (pb - prm.begin) / prm.chunk_elems;
+        const long long c_end = (c + 1) * prm.chunk_elems < shard ? (c + 1) * prm.chunk_elems : shard;
+        const int in_chunk = static_cast<int>((c_end - c * prm.chunk_elems + kPieceElems - 1) / kPieceElems) * warps_per_piece;
+        if (atomicAdd(prm.scratch + 8 + c, 1) == in_chunk - 1) {
+            prm.scratch[8 + c] = 0;                                    // ready for the next step
+            __threadfence_system();
+            for (int r = 0; r < prm.sync.world; r++)
+                st_release_sys(peer_board(prm.sync.pad[r]) + prm.sync.rank * B200_PEER_STEP_MAX_CHUNKS + c, prm.sync.epoch);
+        }
+    }
+}
+
+#ifdef B200_STEP_PROFILE
+#define B200_PROF_DECL long long prof_t = clock64(), prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; int prof_iters = 0, prof_tiles = 0;
+#define B200_PROF(i) { const long long now_ = clock64(); prof_acc[i] += now_ - prof_t; prof_t = now_; }
+#else
+#define B200_PROF_DECL
+#define B200_PROF(i)
+#endif
+
 template <int G, int S, int C, int kThreads, int kWorld>
 __global__ void __launch_bounds__(kThreads, 2)          // two CTAs per SM, like the plain step kernel: <= 128 registers
 peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ PeerStepParams prm) {
@@ -1099,206 +1204,215 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
     constexpr int kCopies = static_cast<int>(sizeof(GT)) * kVec / 16;      // 16-byte cp.async per thread, rank and piece
     extern __shared__ __align__(16) unsigned char s_stage[];               // kWorld x kPieceElems gradient elements
     __shared__ __align__(16) RowSlot s_slot[2];
-    __shared__ uint32_t s_tile[2];
-    __shared__ uint32_t s_idx[2];           // tile (index into the table's list) of the iteration using the slot
-    __shared__ uint32_t s_pc[2];            // reduce piece that iteration starts and folds
-    __shared__ int s_go[2];                 // 1: the tile's gradient has been announced, process it
-    b200_peer_signal_pad* mine = prm.sync.pad[prm.sync.rank];
-    const int32_t* board = peer_board(mine);
-    unsigned* tile_ctr = reinterpret_cast<unsigned*>(prm.scratch + 1);
-    unsigned* piece_ctr = reinterpret_cast<unsigned*>(prm.scratch + 3);
-    const int32_t epoch = prm.sync.epoch;
+    __shared__ StepShared s_sh;
     bool bad = false;
 
     // every rank's gradients of this epoch must be in place before anybody's buffer is read
     if (blockIdx.x == 0 && threadIdx.x < prm.sync.world)
-        st_release_sys(&prm.sync.pad[threadIdx.x]->ready[prm.sync.rank], epoch);
-    if (threadIdx.x < prm.sync.world) wait_at_least(&mine->ready[threadIdx.x], epoch, &mine->error);
+        st_release_sys(&prm.sync.pad[threadIdx.x]->ready[prm.sync.rank], prm.sync.epoch);
+    if (threadIdx.x < prm.sync.world)
+        wait_at_least(&prm.sync.pad[prm.sync.rank]->ready[threadIdx.x], prm.sync.epoch, &prm.sync.pad[prm.sync.rank]->error);
     __syncthreads();
-    const bool dead = wait_failed(&mine->error);            // a rank never arrived: read nobody's buffer, poison the step
+    const bool dead = wait_failed(&prm.sync.pad[prm.sync.rank]->error);     // a rank never arrived: read nobody's buffer
     bad |= dead;
 
-    const long long shard = prm.end - prm.begin;
-    const uint32_t n_pieces = static_cast<uint32_t>((shard + kPieceElems - 1) / kPieceElems);
-    const bool vec_ok = (prm.begin % kVec) == 0;             // cp.async needs 16-byte aligned sources
-    const TableView tv = open_table(table);
-    int win = 0;
-    Op::prologue(prm.spec, win);
-    const bool loader = threadIdx.x < 4;
-
-    // thread 0 only: tickets drawn one iteration ahead, and the last (owner, chunk) seen announced
-    uint32_t ahead_tile = kNone, ahead_piece = kNone;
-    int seen_owner = -1;
-    long long seen_lo = 0, seen_hi = -1;
-    auto tile_ready = [&](int sl, bool block) -> int {      // thread 0, after ITS OWN 16 bytes of the row have arrived
-        const char* g0 = reinterpret_cast<const char*>(s_slot[sl].row.ptr[0]);
-        const long long flat = (g0 - prm.spec.pull.local_base) / static_cast<long long>(sizeof(GT)) +
-                               static_cast<long long>(s_tile[sl]) * tv.tile_elems;
-        int owner = 0;
-#pragma unroll
-        for (int k = 1; k < kWorld; k++) owner += (k < prm.world && flat >= prm.spec.pull.bounds[k]) ? 1 : 0;
-        long long last = flat + tv.tile_elems;               // the tile may be shorter (end of its tensor): a chunk late at worst
-        if (last > prm.spec.pull.bounds[owner + 1]) last = prm.spec.pull.bounds[owner + 1];
-        // pieces are folded by whichever CTA draws them, so chunks complete in any order: every chunk the tile
-        // touches has to be announced (one or two, chunks are at least a tile long)
-        const long long c0 = (flat - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
-        const long long c1 = (last - 1 - prm.spec.pull.bounds[owner]) / prm.chunk_elems;
-        if (owner == seen_owner && c0 >= seen_lo && c1 <= seen_hi) return 1;
-        for (long long c = c0; c <= c1; c++) {
-            const int32_t* f = board + owner * B200_PEER_STEP_MAX_CHUNKS + c;
-            if (block) wait_epoch(f, epoch, &mine->error);
-            if (!epoch_reached(f, epoch) && !wait_failed(&mine->error)) return 0;
-        }
-        seen_owner = owner;
-        seen_lo = c0;
-        seen_hi = c1;
-        return 1;
-    };
-
+    // Everything the scheduling needs lives in shared memory (read through a volatile pointer), so that the Adam
+    // loop below has the register file to itself — next to a register-resident scheduler it spills its loads.
+    // Tiles and pieces are handed out by static striding (CTA b takes b, b + G, ...): both lists are walked
+    // chunk-major by the whole grid, so consumers trail producers, and no ticket has to be waited for.
+    volatile StepShared* sh = &s_sh;
     if (threadIdx.x == 0) {
-        const uint32_t t0 = atomicAdd(tile_ctr, 1u);
-        const uint32_t p0 = atomicAdd(piece_ctr, 1u);
-        s_idx[0] = t0 < tv.n_tiles ? t0 : kNone;
-        s_pc[0] = p0 < n_pieces ? p0 : kNone;
-        ahead_tile = t0 < tv.n_tiles ? atomicAdd(tile_ctr, 1u) : kNone;
-        ahead_piece = p0 < n_pieces ? atomicAdd(piece_ctr, 1u) : kNone;
+        const TableView tv0 = open_table(table);
+        int w = 0;
+        Op::prologue(prm.spec, w);
+        s_sh.rows = tv0.rows;
+        s_sh.tiles = tv0.tiles;
+        s_sh.n_tiles = tv0.n_tiles;
+        s_sh.tile_elems = tv0.tile_elems;
+        s_sh.n_pieces = static_cast<uint32_t>((prm.end - prm.begin + kPieceElems - 1) / kPieceElems);
+        s_sh.vec_ok = (prm.begin % kVec) == 0;               // cp.async needs 16-byte aligned sources
+        s_sh.win = w;
+        s_sh.seen_owner = -1;
+        s_sh.seen_lo = 0;
+        s_sh.seen_hi = -1;
+        s_sh.idx[0] = blockIdx.x < tv0.n_tiles ? blockIdx.x : kNone;
+        s_sh.idx1 = blockIdx.x + gridDim.x;                  // the next iteration's tile; its entry goes to e1[1]
+        s_sh.pc[0] = blockIdx.x < s_sh.n_pieces ? blockIdx.x : kNone;
+        s_sh.piece_next = blockIdx.x + gridDim.x;
+        if (s_sh.idx1 < tv0.n_tiles) cp_async8(&s_sh.e1[1], tv0.tiles + s_sh.idx1);
     }
     __syncthreads();
-    if (loader && s_idx[0] != kNone) {
-        const uint2 e = __ldg(reinterpret_cast<const uint2*>(tv.tiles + s_idx[0]));
-        cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
-                   reinterpret_cast<const char*>(tv.rows + e.x) + threadIdx.x * 16);
-        if (threadIdx.x == 0) s_tile[0] = e.y;
+    if (threadIdx.x < 4) {
+        const uint32_t a = sh->idx[0];
+        if (a != kNone) {
+            const uint2 e = __ldg(reinterpret_cast<const uint2*>(s_sh.tiles + a));
+            cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
+                       reinterpret_cast<const char*>(s_sh.rows + e.x) + threadIdx.x * 16);
+            if (threadIdx.x == 0) sh->tile[0] = e.y;
+        }
         cp_async_wait_all();
     }
-    if (threadIdx.x == 0) s_go[0] = s_idx[0] != kNone ? tile_ready(0, s_pc[0] == kNone) : 0;
+    if (threadIdx.x == 0)
+        sh->go[0] = sh->idx[0] != kNone ? step_tile_ready<GT, kWorld>(prm, &s_slot[0].row, sh->tile[0], sh->tile_elems, &s_sh,
+                                                                      sh->pc[0] == kNone) : 0;
     __syncthreads();
 
     int slot = 0;
-    while (s_idx[slot] != kNone || s_pc[slot] != kNone) {
-        const uint32_t tile = s_idx[slot], pc = s_pc[slot];
-        const bool go = tile != kNone && s_go[slot] != 0;
-        // ---- the other slot: the next tile (the same one again if it was not ready) and the next piece
-        if (threadIdx.x < 32) {
-            uint32_t nxt = kNone;
-            if (threadIdx.x == 0) {
-                const bool keep = tile != kNone && !go;
-                nxt = keep ? tile : (ahead_tile < tv.n_tiles ? ahead_tile : kNone);
-                s_idx[slot ^ 1] = nxt;
-                s_pc[slot ^ 1] = ahead_piece < n_pieces ? ahead_piece : kNone;
-            }
-            nxt = __shfl_sync(0xffffffffu, nxt, 0);
-            if (loader && nxt != kNone) {
-                const uint2 e = __ldg(reinterpret_cast<const uint2*>(tv.tiles + nxt));
-                cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
-                           reinterpret_cast<const char*>(tv.rows + e.x) + threadIdx.x * 16);
-                if (threadIdx.x == 0) s_tile[slot ^ 1] = e.y;
-            }
-            if (threadIdx.x == 0) {                          // tickets for the iteration after the next one
-                if (go && ahead_tile < tv.n_tiles) ahead_tile = atomicAdd(tile_ctr, 1u);
-                if (tile == kNone) ahead_tile = kNone;
-                if (ahead_piece < n_pieces) ahead_piece = atomicAdd(piece_ctr, 1u);
-            }
+    uint32_t uncounted = kNone;             // piece folded in the previous iteration, not yet counted (see below)
+    B200_PROF_DECL
+    B200_PROF(0)
+    while (sh->idx[slot] != kNone || sh->pc[slot] != kNone) {
+        // Counting a folded piece needs a fence behind its stores.  Right after the fold that fence would also wait
+        // for the tile's own stores (a full write round trip per iteration); one iteration later they have long
+        // landed.  Only when no piece is left to hand out — the one case in which thread 0 may block below — is
+        // the piece counted at once, so that nobody can wait for a chunk whose last piece sits uncounted.
+        const bool count_now = sh->piece_next >= sh->n_pieces;
+        if (uncounted != kNone) {
+            step_count_piece(prm, prm.begin + static_cast<long long>(uncounted) * kPieceElems, kThreads / 32);
+            uncounted = kNone;
         }
-        // ---- (1) start this iteration's reduce piece: every rank's slice -> shared memory, asynchronously
-        const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
-        const long long pe = pb + kPieceElems < prm.end ? pb + kPieceElems : prm.end;
-        const bool piece = pc != kNone && !dead;
-        const bool staged = piece && vec_ok && pe - pb == kPieceElems;
-        if (staged) {
-#pragma unroll
-            for (int r = 0; r < kWorld; r++) {
-                if (r < prm.world) {
-                    const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
-                                      threadIdx.x * (kVec * sizeof(GT));
-                    unsigned char* dst = s_stage + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT);
-#pragma unroll
-                    for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
+#ifdef B200_STEP_PROFILE
+        prof_iters++;
+        prof_tiles += (sh->idx[slot] != kNone && sh->go[slot]) ? 1 : 0;
+#endif
+        // ---- the other slot: the next tile (this one again if it was not ready) and the next piece; everything
+        //      fetched here goes to shared memory asynchronously (cp.async), nothing is waited for
+        if (threadIdx.x < 4) {
+            const uint32_t tile = sh->idx[slot];
+            const bool keep = tile != kNone && sh->go[slot] == 0;
+            if (keep) {
+                reinterpret_cast<uint4*>(&s_slot[slot ^ 1].row)[threadIdx.x] = reinterpret_cast<const uint4*>(&s_slot[slot].row)[threadIdx.x];
+                if (threadIdx.x == 0) {
+                    sh->idx[slot ^ 1] = tile;
+                    sh->tile[slot ^ 1] = sh->tile[slot];
+                    sh->e1[slot].x = sh->e1[slot ^ 1].x;     // the prefetched entry now belongs to the other slot
+                    sh->e1[slot].y = sh->e1[slot ^ 1].y;
                 }
-            }
-        }
-        // ---- (2) the update tile (its HBM traffic hides the NVLink round trip of the piece)
-        if (go) {
-            const b200_table_row row = s_slot[slot].row;
-            const int64_t start = static_cast<int64_t>(s_tile[slot]) * tv.tile_elems;
-            const int64_t left = row.numel - start;
-            const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left) : static_cast<int>(tv.tile_elems);
-            const typename Op::Ctx ctx = Op::make_ctx(prm.spec, row, win, start);
-            if (row.flags & 1u) {
-                const int n8 = n & ~(kVec - 1);
-                for (int base = threadIdx.x * kVec; base < n8; base += kThreads * kVec * kU) {
-                    int64_t idx[kU];
-                    bool act[kU];
-#pragma unroll
-                    for (int u = 0; u < kU; u++) {
-                        const int off = base + u * kThreads * kVec;
-                        act[u] = off < n8;
-                        idx[u] = start + off;
-                    }
-                    Op::template vec<kU>(row, ctx, idx, act, bad);
-                }
-                const int tail = n - n8;
-                if (static_cast<int>(threadIdx.x) < tail) Op::scalar(row, ctx, start + n8 + threadIdx.x, bad);
             } else {
-                for (int i = threadIdx.x; i < n; i += kThreads) Op::scalar(row, ctx, start + i, bad);
+                const uint32_t idx1 = sh->idx1;
+                if (idx1 < sh->n_tiles)
+                    cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
+                               reinterpret_cast<const char*>(s_sh.rows + sh->e1[slot ^ 1].x) + threadIdx.x * 16);
+                if (threadIdx.x == 0) {
+                    sh->idx[slot ^ 1] = idx1 < sh->n_tiles ? idx1 : kNone;
+                    sh->tile[slot ^ 1] = sh->e1[slot ^ 1].y;
+                    const uint32_t nxt = idx1 < sh->n_tiles ? idx1 + gridDim.x : kNone;
+                    sh->idx1 = nxt;
+                    if (nxt < sh->n_tiles) cp_async8(&s_sh.e1[slot], s_sh.tiles + nxt);
+                }
+            }
+            if (threadIdx.x == 0) {
+                const uint32_t pn = sh->piece_next;
+                sh->pc[slot ^ 1] = pn < sh->n_pieces ? pn : kNone;
+                if (pn < sh->n_pieces) sh->piece_next = pn + gridDim.x;
             }
         }
+        B200_PROF(1)
+        // ---- (1) start this iteration's reduce piece: every rank's slice -> shared memory, asynchronously
+        {
+            // `lane` is made opaque to the compiler in every iteration: otherwise it hoists the per-thread source and
+            // destination addresses of this block and of the fold below out of the loop, keeps them live across the
+            // Adam pass and spills that pass's freshly loaded operands (which serialises its loads)
+            uint32_t lane = threadIdx.x;
+            asm volatile("" : "+r"(lane));
+            const uint32_t pc = sh->pc[slot];
+            const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
+#if defined(B200_STEP_VARIANT) && B200_STEP_VARIANT >= 2     // timing experiment: no reduce traffic at all (results are wrong)
+            const bool staged = false;
+#else
+            const bool staged = pc != kNone && !dead && sh->vec_ok && pb + kPieceElems <= prm.end;
+#endif
+            if (staged) {
+#pragma unroll
+                for (int r = 0; r < kWorld; r++) {
+                    if (r < prm.world) {
+                        const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
+                                          lane * (kVec * sizeof(GT));
+                        unsigned char* dst = s_stage + (static_cast<size_t>(r) * kPieceElems + lane * kVec) * sizeof(GT);
+#pragma unroll
+                        for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
+                    }
+                }
+            }
+        }
+        B200_PROF(2)
+        // ---- (2) the update tile (its HBM traffic hides the NVLink round trip of the piece)
+        if (sh->idx[slot] != kNone && sh->go[slot] != 0)
+            bad |= step_one_tile<Op, kThreads, kU>(prm.spec, &s_slot[slot].row, sh->tile[slot], sh->tile_elems, sh->win);
+        B200_PROF(3)
         // ---- (3) fold the piece: fp32 sum in rank order, one rounding, x factor, second rounding
-        bool rbad = false;                                   // a non-finite mean is seen again by whoever pulls it
         cp_async_wait_all();                                 // this thread's slices (and its part of the next row)
-        if (staged) {
-            float acc[kVec];
-            Raw8<G> raw;
-            lds8<G>(s_stage + (threadIdx.x * kVec) * sizeof(GT), raw);
-            unpack8<G>(raw, acc);
+        {
+            uint32_t lane = threadIdx.x;
+            asm volatile("" : "+r"(lane));
+            const uint32_t pc = sh->pc[slot];
+            const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
+            const long long pe = pb + kPieceElems < prm.end ? pb + kPieceElems : prm.end;
+#if defined(B200_STEP_VARIANT) && B200_STEP_VARIANT >= 2
+            const bool piece = false;
+#else
+            const bool piece = pc != kNone && !dead;
+#endif
+            const bool staged = piece && sh->vec_ok && pe - pb == kPieceElems;
+            if (staged) {
+                float acc[kVec];
+                Raw8<G> raw;
+                lds8<G>(s_stage + (lane * kVec) * sizeof(GT), raw);
+                unpack8<G>(raw, acc);
 #pragma unroll
-            for (int r = 1; r < kWorld; r++) {
-                if (r < prm.world) {
-                    float f[kVec];
-                    lds8<G>(s_stage + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT), raw);
-                    unpack8<G>(raw, f);
+                for (int r = 1; r < kWorld; r++) {
+                    if (r < prm.world) {
+                        float f[kVec];
+                        lds8<G>(s_stage + (static_cast<size_t>(r) * kPieceElems + lane * kVec) * sizeof(GT), raw);
+                        unpack8<G>(raw, f);
 #pragma unroll
-                    for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
+                        for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < kVec; i++) acc[i] = __fmul_rn(round_through<G>(acc[i]), prm.factor);
+                store8<G>(prm.reduced, pb + lane * kVec, acc);
+            } else if (piece) {
+                // ragged last piece / shard that does not start on an 8-element boundary: element by element
+                // (kept tiny on purpose — a vectorised fallback here costs the Adam pass above its registers)
+                for (int i = 0; i < kVec; i++) {
+                    const long long e = pb + static_cast<long long>(lane) * kVec + i;
+                    if (e < pe) {
+                        float x[kWorld];
+#pragma unroll
+                        for (int r = 0; r < kWorld; r++) x[r] = r < prm.world ? load1<G>(prm.grads.p[r], e) : 0.0f;
+                        store1<G>(prm.reduced, e, peer_mean<G, kWorld>(x, prm.world, prm.factor));
+                    }
                 }
             }
-#pragma unroll
-            for (int i = 0; i < kVec; i++) acc[i] = __fmul_rn(round_through<G>(acc[i]), prm.factor);
-            store8<G>(prm.reduced, pb + threadIdx.x * kVec, acc);
-        } else if (piece) {                                  // ragged last piece / unaligned shard: plain loads
-            reduce_span<G, kThreads, kWorld>(prm.grads, prm.world, prm.reduced, pb, pe, prm.factor, threadIdx.x, kThreads, rbad);
-        }
-        __syncthreads();
-        // ---- (4) thread 0: count the folded piece (announce its chunk if it was the last), then see whether
-        //          the next tile may run; blocking is allowed only when the next iteration has no piece to start
-        if (threadIdx.x == 0) {
             if (pc != kNone) {
-                const long long c = (pb - prm.begin) / prm.chunk_elems;
-                const long long c_end = (c + 1) * prm.chunk_elems < shard ? (c + 1) * prm.chunk_elems : shard;
-                const int in_chunk = static_cast<int>((c_end - c * prm.chunk_elems + kPieceElems - 1) / kPieceElems);
-                __threadfence();
-                if (atomicAdd(prm.scratch + 8 + c, 1) == in_chunk - 1) {
-                    prm.scratch[8 + c] = 0;                  // ready for the next step
-                    __threadfence_system();
-                    for (int r = 0; r < prm.sync.world; r++)
-                        st_release_sys(peer_board(prm.sync.pad[r]) + prm.sync.rank * B200_PEER_STEP_MAX_CHUNKS + c, epoch);
-                }
+                if (count_now) step_count_piece(prm, pb, kThreads / 32);
+                else uncounted = pc;
             }
-            s_go[slot ^ 1] = s_idx[slot ^ 1] != kNone ? tile_ready(slot ^ 1, s_pc[slot ^ 1] == kNone) : 0;
         }
+        B200_PROF(4)
+        // ---- (4) thread 0: may the next tile run?  Blocking is allowed only when the next iteration has no piece
+        //          to start (producers must never be starved by waiting consumers)
+        if (threadIdx.x == 0) {
+            sh->go[slot ^ 1] = sh->idx[slot ^ 1] != kNone ? step_tile_ready<GT, kWorld>(prm, &s_slot[slot ^ 1].row, sh->tile[slot ^ 1],
+                                                                                    sh->tile_elems, &s_sh, sh->pc[slot ^ 1] == kNone) : 0;
+        }
+        B200_PROF(6)
         __syncthreads();
+        B200_PROF(7)
         slot ^= 1;
     }
-    bad |= wait_failed(&mine->error);
-    Op::finish(prm.spec, bad);
-    // the last CTA to leave resets the tickets (the next launch is ordered after this one on the stream)
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        if (atomicAdd(prm.scratch + 2, 1) == static_cast<int>(gridDim.x) - 1) {
-            prm.scratch[1] = 0;
-            prm.scratch[2] = 0;
-            prm.scratch[3] = 0;
-        }
+    if (uncounted != kNone) step_count_piece(prm, prm.begin + static_cast<long long>(uncounted) * kPieceElems, kThreads / 32);
+#ifdef B200_STEP_PROFILE
+    if (threadIdx.x == 0 && blockIdx.x < 512) {           // scratch[2048 + 20 * cta ...]: cycles per phase, iterations, tiles
+        long long* out = reinterpret_cast<long long*>(prm.scratch + 2048) + 10 * blockIdx.x;
+        for (int i = 0; i < 8; i++) out[i] = prof_acc[i];
+        out[8] = prof_iters;
+        out[9] = prof_tiles;
     }
+#endif
+    bad |= wait_failed(&prm.sync.pad[prm.sync.rank]->error);
+    Op::finish(prm.spec, bad);
 }
 
 // ============================================================================================

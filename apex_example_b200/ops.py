@@ -282,7 +282,7 @@ def peer_spec_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, grou
 
 
 def new_peer_step_scratch(device) -> torch.Tensor:
-    return torch.zeros(8 + _lib.PEER_STEP_MAX_CHUNKS, dtype=torch.int32, device=device)
+    return torch.zeros(2048 + 20 * 512, dtype=torch.int32, device=device)     # tickets, chunk counters (+ room for profile builds)
 
 
 PEER_STEP_PAD_WORDS = _lib.PEER_STEP_PAD_BYTES // 4      # int32 words of a signal pad + progress board
