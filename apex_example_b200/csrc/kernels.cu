@@ -1237,8 +1237,11 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         s_sh.seen_hi = -1;
         s_sh.idx[0] = blockIdx.x < tv0.n_tiles ? blockIdx.x : kNone;
         s_sh.idx1 = blockIdx.x + gridDim.x;                  // the next iteration's tile; its entry goes to e1[1]
-        s_sh.pc[0] = blockIdx.x < s_sh.n_pieces ? blockIdx.x : kNone;
-        s_sh.piece_next = blockIdx.x + gridDim.x;
+        // pieces are drawn from a shared counter (a CTA whose tile is not ready yet folds pieces faster than one
+        // that also updates a tile; with a static split the fast ones would run dry while chunks wait for the slow)
+        const uint32_t p0 = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
+        s_sh.pc[0] = p0 < s_sh.n_pieces ? p0 : kNone;
+        s_sh.piece_next = p0 < s_sh.n_pieces ? atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u) : kNone;
         if (s_sh.idx1 < tv0.n_tiles) cp_async8(&s_sh.e1[1], tv0.tiles + s_sh.idx1);
     }
     __syncthreads();
@@ -1276,7 +1279,9 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         prof_tiles += (sh->idx[slot] != kNone && sh->go[slot]) ? 1 : 0;
 #endif
         // ---- the other slot: the next tile (this one again if it was not ready) and the next piece; everything
-        //      fetched here goes to shared memory asynchronously (cp.async), nothing is waited for
+        //      fetched here goes to shared memory asynchronously (cp.async); the next piece ticket stays in a register
+        //      of thread 0 until the end of the iteration, so nothing is waited for
+        uint32_t fresh_piece = kNone;
         if (threadIdx.x < 4) {
             const uint32_t tile = sh->idx[slot];
             const bool keep = tile != kNone && sh->go[slot] == 0;
@@ -1304,7 +1309,7 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
             if (threadIdx.x == 0) {
                 const uint32_t pn = sh->piece_next;
                 sh->pc[slot ^ 1] = pn < sh->n_pieces ? pn : kNone;
-                if (pn < sh->n_pieces) sh->piece_next = pn + gridDim.x;
+                if (pn < sh->n_pieces) fresh_piece = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
             }
         }
         B200_PROF(1)
@@ -1394,6 +1399,7 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         // ---- (4) thread 0: may the next tile run?  Blocking is allowed only when the next iteration has no piece
         //          to start (producers must never be starved by waiting consumers)
         if (threadIdx.x == 0) {
+            if (fresh_piece != kNone) sh->piece_next = fresh_piece;
             sh->go[slot ^ 1] = sh->idx[slot ^ 1] != kNone ? step_tile_ready<GT, kWorld>(prm, &s_slot[slot ^ 1].row, sh->tile[slot ^ 1],
                                                                                     sh->tile_elems, &s_sh, sh->pc[slot ^ 1] == kNone) : 0;
         }
@@ -1413,6 +1419,14 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
 #endif
     bad |= wait_failed(&prm.sync.pad[prm.sync.rank]->error);
     Op::finish(prm.spec, bad);
+    // the last CTA to leave resets the piece tickets (the next launch is ordered after this one on the stream)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (atomicAdd(prm.scratch + 2, 1) == static_cast<int>(gridDim.x) - 1) {
+            prm.scratch[2] = 0;
+            prm.scratch[3] = 0;
+        }
+    }
 }
 
 // ============================================================================================
