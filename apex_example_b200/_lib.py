@@ -124,7 +124,7 @@ SIGNATURES = {
     "b200_peer_spec_step": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup), c_int32,
                                       c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                       ctypes.POINTER(PeerPull), ctypes.POINTER(c_void_p), c_void_p, c_float,
-                                      ctypes.POINTER(PeerSync), c_int64, c_void_p, c_int64, c_void_p]),
+                                      ctypes.POINTER(PeerSync), c_int32, c_int64, c_void_p, c_int64, c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

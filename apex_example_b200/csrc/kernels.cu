@@ -1044,6 +1044,8 @@ peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __
 // (b200_table_order_for_peer_step): consumers trail producers by construction.  Every rank inspects every
 // reduced gradient it pulls, so each rank's overflow flag is complete on its own: no flag exchange.
 constexpr int kPieceElems = 256 * kVec;
+constexpr int kRunPieces = 16;                              // pieces a reducer CTA folds between two fences
+constexpr long long kRunElems = static_cast<long long>(kRunPieces) * kPieceElems;
 
 __device__ __forceinline__ int32_t* peer_board(b200_peer_signal_pad* pad) {
     return reinterpret_cast<int32_t*>(pad) + sizeof(b200_peer_signal_pad) / 4;
@@ -1073,8 +1075,10 @@ struct PeerStepParams {
     long long chunk_elems;          // announcement granularity, a multiple of kPieceElems
     float factor;
     int world;
+    int n_reducers;                 // CTAs [0, n_reducers) reduce, the others update
+    int n_stages;                   // pieces a reducer CTA keeps in flight (shared-memory stages)
     PeerSync sync;
-    int32_t* scratch;               // [1] tile tickets [2] exits [3] piece tickets [8 + c] pieces of chunk c folded
+    int32_t* scratch;               // [2] exits [3] run tickets [8 + c] pieces of chunk c folded
 };
 
 template <int DT>
@@ -1200,7 +1204,6 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
     using Op = AdamSpecOp<G, S, C>;
     using GT = typename Elem<G>::type;
     constexpr int kU = 2 * Op::kUnrollMul;
-    constexpr uint32_t kNone = 0xffffffffu;
     constexpr int kCopies = static_cast<int>(sizeof(GT)) * kVec / 16;      // 16-byte cp.async per thread, rank and piece
     extern __shared__ __align__(16) unsigned char s_stage[];               // kWorld x kPieceElems gradient elements
     __shared__ __align__(16) RowSlot s_slot[2];
@@ -1216,210 +1219,151 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
     const bool dead = wait_failed(&prm.sync.pad[prm.sync.rank]->error);     // a rank never arrived: read nobody's buffer
     bad |= dead;
 
-    // Everything the scheduling needs lives in shared memory (read through a volatile pointer), so that the Adam
-    // loop below has the register file to itself — next to a register-resident scheduler it spills its loads.
-    // Tiles and pieces are handed out by static striding (CTA b takes b, b + G, ...): both lists are walked
-    // chunk-major by the whole grid, so consumers trail producers, and no ticket has to be waited for.
-    volatile StepShared* sh = &s_sh;
-    if (threadIdx.x == 0) {
-        const TableView tv0 = open_table(table);
-        int w = 0;
-        Op::prologue(prm.spec, w);
-        s_sh.rows = tv0.rows;
-        s_sh.tiles = tv0.tiles;
-        s_sh.n_tiles = tv0.n_tiles;
-        s_sh.tile_elems = tv0.tile_elems;
-        s_sh.n_pieces = static_cast<uint32_t>((prm.end - prm.begin + kPieceElems - 1) / kPieceElems);
-        s_sh.vec_ok = (prm.begin % kVec) == 0;               // cp.async needs 16-byte aligned sources
-        s_sh.win = w;
-        s_sh.seen_owner = -1;
-        s_sh.seen_lo = 0;
-        s_sh.seen_hi = -1;
-        s_sh.idx[0] = blockIdx.x < tv0.n_tiles ? blockIdx.x : kNone;
-        s_sh.idx1 = blockIdx.x + gridDim.x;                  // the next iteration's tile; its entry goes to e1[1]
-        // pieces are drawn from a shared counter (a CTA whose tile is not ready yet folds pieces faster than one
-        // that also updates a tile; with a static split the fast ones would run dry while chunks wait for the slow)
-        const uint32_t p0 = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
-        s_sh.pc[0] = p0 < s_sh.n_pieces ? p0 : kNone;
-        s_sh.piece_next = p0 < s_sh.n_pieces ? atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u) : kNone;
-        if (s_sh.idx1 < tv0.n_tiles) cp_async8(&s_sh.e1[1], tv0.tiles + s_sh.idx1);
-    }
-    __syncthreads();
-    if (threadIdx.x < 4) {
-        const uint32_t a = sh->idx[0];
-        if (a != kNone) {
-            const uint2 e = __ldg(reinterpret_cast<const uint2*>(s_sh.tiles + a));
-            cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
-                       reinterpret_cast<const char*>(s_sh.rows + e.x) + threadIdx.x * 16);
-            if (threadIdx.x == 0) sh->tile[0] = e.y;
-        }
-        cp_async_wait_all();
-    }
-    if (threadIdx.x == 0)
-        sh->go[0] = sh->idx[0] != kNone ? step_tile_ready<GT, kWorld>(prm, &s_slot[0].row, sh->tile[0], sh->tile_elems, &s_sh,
-                                                                      sh->pc[0] == kNone) : 0;
-    __syncthreads();
-
-    int slot = 0;
-    uint32_t uncounted = kNone;             // piece folded in the previous iteration, not yet counted (see below)
-    B200_PROF_DECL
-    B200_PROF(0)
-    while (sh->idx[slot] != kNone || sh->pc[slot] != kNone) {
-        // Counting a folded piece needs a fence behind its stores.  Right after the fold that fence would also wait
-        // for the tile's own stores (a full write round trip per iteration); one iteration later they have long
-        // landed.  Only when no piece is left to hand out — the one case in which thread 0 may block below — is
-        // the piece counted at once, so that nobody can wait for a chunk whose last piece sits uncounted.
-        const bool count_now = sh->piece_next >= sh->n_pieces;
-        if (uncounted != kNone) {
-            step_count_piece(prm, prm.begin + static_cast<long long>(uncounted) * kPieceElems, kThreads / 32);
-            uncounted = kNone;
-        }
-#ifdef B200_STEP_PROFILE
-        prof_iters++;
-        prof_tiles += (sh->idx[slot] != kNone && sh->go[slot]) ? 1 : 0;
-#endif
-        // ---- the other slot: the next tile (this one again if it was not ready) and the next piece; everything
-        //      fetched here goes to shared memory asynchronously (cp.async); the next piece ticket stays in a register
-        //      of thread 0 until the end of the iteration, so nothing is waited for
-        uint32_t fresh_piece = kNone;
-        if (threadIdx.x < 4) {
-            const uint32_t tile = sh->idx[slot];
-            const bool keep = tile != kNone && sh->go[slot] == 0;
-            if (keep) {
-                reinterpret_cast<uint4*>(&s_slot[slot ^ 1].row)[threadIdx.x] = reinterpret_cast<const uint4*>(&s_slot[slot].row)[threadIdx.x];
-                if (threadIdx.x == 0) {
-                    sh->idx[slot ^ 1] = tile;
-                    sh->tile[slot ^ 1] = sh->tile[slot];
-                    sh->e1[slot].x = sh->e1[slot ^ 1].x;     // the prefetched entry now belongs to the other slot
-                    sh->e1[slot].y = sh->e1[slot ^ 1].y;
+    if (static_cast<int>(blockIdx.x) < prm.n_reducers) {
+        // ================= REDUCE role: this rank's shard, one RUN of kRunPieces pieces at a time ==============
+        // The slices of a piece (2048 elements from every rank) are staged in shared memory by cp.async, kStages
+        // pieces deep, so a reducer CTA keeps kStages x world x 4 KB in flight without holding registers; a run is
+        // counted (one fence for all its stores) when it is done, and the CTA that completes a chunk announces it.
+        const int n_stage = prm.n_stages;
+        const size_t stage_bytes = static_cast<size_t>(kWorld) * kPieceElems * sizeof(GT);
+        const long long shard = prm.end - prm.begin;
+        const long long n_runs = (shard + kRunElems - 1) / kRunElems;
+        const bool vec_ok = (prm.begin % kVec) == 0;                  // cp.async needs 16-byte aligned sources
+        __shared__ long long s_run;
+        for (;;) {
+            __syncthreads();
+            if (threadIdx.x == 0) s_run = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
+            __syncthreads();
+            const long long run = s_run;
+            if (run >= n_runs) break;
+            const long long rb = prm.begin + run * kRunElems;
+            const long long re = rb + kRunElems < prm.end ? rb + kRunElems : prm.end;
+            const int n_pc = static_cast<int>((re - rb + kPieceElems - 1) / kPieceElems);
+            auto issue = [&](int j) {                                  // piece j of the run -> stage j % n_stage
+                const long long pb = rb + static_cast<long long>(j) * kPieceElems;
+                if (j < n_pc && !dead && vec_ok && pb + kPieceElems <= re) {
+                    unsigned char* st = s_stage + (j % n_stage) * stage_bytes;
+#pragma unroll
+                    for (int r = 0; r < kWorld; r++) {
+                        if (r < prm.world) {
+                            const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
+                                              threadIdx.x * (kVec * sizeof(GT));
+                            unsigned char* dst = st + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT);
+#pragma unroll
+                            for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
+                        }
+                    }
                 }
-            } else {
-                const uint32_t idx1 = sh->idx1;
-                if (idx1 < sh->n_tiles)
-                    cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
-                               reinterpret_cast<const char*>(s_sh.rows + sh->e1[slot ^ 1].x) + threadIdx.x * 16);
-                if (threadIdx.x == 0) {
-                    sh->idx[slot ^ 1] = idx1 < sh->n_tiles ? idx1 : kNone;
-                    sh->tile[slot ^ 1] = sh->e1[slot ^ 1].y;
-                    const uint32_t nxt = idx1 < sh->n_tiles ? idx1 + gridDim.x : kNone;
-                    sh->idx1 = nxt;
-                    if (nxt < sh->n_tiles) cp_async8(&s_sh.e1[slot], s_sh.tiles + nxt);
+                cp_async_commit();                                     // one group per piece, empty ones included
+            };
+            for (int j = 0; j < n_stage - 1; j++) issue(j);
+            for (int j = 0; j < n_pc; j++) {
+                issue(j + n_stage - 1);
+                cp_async_wait_pending(n_stage - 1, n_stage);           // piece j's slices have landed
+                const long long pb = rb + static_cast<long long>(j) * kPieceElems;
+                const long long pe = pb + kPieceElems < re ? pb + kPieceElems : re;
+                if (!dead) {
+                    if (vec_ok && pe - pb == kPieceElems) {
+                        const unsigned char* st = s_stage + (j % n_stage) * stage_bytes;
+                        float acc[kVec];
+                        Raw8<G> raw;
+                        lds8<G>(st + (threadIdx.x * kVec) * sizeof(GT), raw);
+                        unpack8<G>(raw, acc);
+#pragma unroll
+                        for (int r = 1; r < kWorld; r++) {
+                            if (r < prm.world) {
+                                float f[kVec];
+                                lds8<G>(st + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT), raw);
+                                unpack8<G>(raw, f);
+#pragma unroll
+                                for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
+                            }
+                        }
+#pragma unroll
+                        for (int i = 0; i < kVec; i++) acc[i] = __fmul_rn(round_through<G>(acc[i]), prm.factor);
+                        store8<G>(prm.reduced, pb + threadIdx.x * kVec, acc);
+                    } else {                                           // ragged last piece / unaligned shard
+                        for (int i = 0; i < kVec; i++) {
+                            const long long e = pb + static_cast<long long>(threadIdx.x) * kVec + i;
+                            if (e < pe) {
+                                float x[kWorld];
+#pragma unroll
+                                for (int r = 0; r < kWorld; r++) x[r] = r < prm.world ? load1<G>(prm.grads.p[r], e) : 0.0f;
+                                store1<G>(prm.reduced, e, peer_mean<G, kWorld>(x, prm.world, prm.factor));
+                            }
+                        }
+                    }
                 }
             }
+            // the run is folded: one fence for all of its stores, then count its pieces towards its chunk
+            __threadfence();
+            __syncthreads();
             if (threadIdx.x == 0) {
-                const uint32_t pn = sh->piece_next;
-                sh->pc[slot ^ 1] = pn < sh->n_pieces ? pn : kNone;
-                if (pn < sh->n_pieces) fresh_piece = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
-            }
-        }
-        B200_PROF(1)
-        // ---- (1) start this iteration's reduce piece: every rank's slice -> shared memory, asynchronously
-        {
-            // `lane` is made opaque to the compiler in every iteration: otherwise it hoists the per-thread source and
-            // destination addresses of this block and of the fold below out of the loop, keeps them live across the
-            // Adam pass and spills that pass's freshly loaded operands (which serialises its loads)
-            uint32_t lane = threadIdx.x;
-            asm volatile("" : "+r"(lane));
-            const uint32_t pc = sh->pc[slot];
-            const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
-#if defined(B200_STEP_VARIANT) && B200_STEP_VARIANT >= 2     // timing experiment: no reduce traffic at all (results are wrong)
-            const bool staged = false;
-#else
-            const bool staged = pc != kNone && !dead && sh->vec_ok && pb + kPieceElems <= prm.end;
-#endif
-            if (staged) {
-#pragma unroll
-                for (int r = 0; r < kWorld; r++) {
-                    if (r < prm.world) {
-                        const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
-                                          lane * (kVec * sizeof(GT));
-                        unsigned char* dst = s_stage + (static_cast<size_t>(r) * kPieceElems + lane * kVec) * sizeof(GT);
-#pragma unroll
-                        for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
-                    }
+                const long long c = (rb - prm.begin) / prm.chunk_elems;
+                const long long c_end = (c + 1) * prm.chunk_elems < shard ? (c + 1) * prm.chunk_elems : shard;
+                const int in_chunk = static_cast<int>((c_end - c * prm.chunk_elems + kPieceElems - 1) / kPieceElems);
+                if (atomicAdd(prm.scratch + 8 + c, n_pc) + n_pc == in_chunk) {
+                    prm.scratch[8 + c] = 0;                            // ready for the next step
+                    __threadfence_system();
+                    for (int r = 0; r < prm.sync.world; r++)
+                        st_release_sys(peer_board(prm.sync.pad[r]) + prm.sync.rank * B200_PEER_STEP_MAX_CHUNKS + c, prm.sync.epoch);
                 }
             }
         }
-        B200_PROF(2)
-        // ---- (2) the update tile (its HBM traffic hides the NVLink round trip of the piece)
-        if (sh->idx[slot] != kNone && sh->go[slot] != 0)
-            bad |= step_one_tile<Op, kThreads, kU>(prm.spec, &s_slot[slot].row, sh->tile[slot], sh->tile_elems, sh->win);
-        B200_PROF(3)
-        // ---- (3) fold the piece: fp32 sum in rank order, one rounding, x factor, second rounding
-        cp_async_wait_all();                                 // this thread's slices (and its part of the next row)
-        {
-            uint32_t lane = threadIdx.x;
-            asm volatile("" : "+r"(lane));
-            const uint32_t pc = sh->pc[slot];
-            const long long pb = prm.begin + static_cast<long long>(pc) * kPieceElems;
-            const long long pe = pb + kPieceElems < prm.end ? pb + kPieceElems : prm.end;
-#if defined(B200_STEP_VARIANT) && B200_STEP_VARIANT >= 2
-            const bool piece = false;
-#else
-            const bool piece = pc != kNone && !dead;
-#endif
-            const bool staged = piece && sh->vec_ok && pe - pb == kPieceElems;
-            if (staged) {
-                float acc[kVec];
-                Raw8<G> raw;
-                lds8<G>(s_stage + (lane * kVec) * sizeof(GT), raw);
-                unpack8<G>(raw, acc);
-#pragma unroll
-                for (int r = 1; r < kWorld; r++) {
-                    if (r < prm.world) {
-                        float f[kVec];
-                        lds8<G>(s_stage + (static_cast<size_t>(r) * kPieceElems + lane * kVec) * sizeof(GT), raw);
-                        unpack8<G>(raw, f);
-#pragma unroll
-                        for (int i = 0; i < kVec; i++) acc[i] = __fadd_rn(acc[i], f[i]);
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < kVec; i++) acc[i] = __fmul_rn(round_through<G>(acc[i]), prm.factor);
-                store8<G>(prm.reduced, pb + lane * kVec, acc);
-            } else if (piece) {
-                // ragged last piece / shard that does not start on an 8-element boundary: element by element
-                // (kept tiny on purpose — a vectorised fallback here costs the Adam pass above its registers)
-                for (int i = 0; i < kVec; i++) {
-                    const long long e = pb + static_cast<long long>(lane) * kVec + i;
-                    if (e < pe) {
-                        float x[kWorld];
-#pragma unroll
-                        for (int r = 0; r < kWorld; r++) x[r] = r < prm.world ? load1<G>(prm.grads.p[r], e) : 0.0f;
-                        store1<G>(prm.reduced, e, peer_mean<G, kWorld>(x, prm.world, prm.factor));
-                    }
+    } else {
+        // ================= UPDATE role: the speculative Adam pass over the (chunk-major) tile list ==============
+        // Static striding over the update CTAs, next row prefetched with cp.async (as walk_tiles does); before the
+        // barrier that hands a row over, thread 0 waits until the owner of that tile's gradient has announced the
+        // chunk(s) it lies in.  Update CTAs never produce anything a reducer waits for, so blocking is safe.
+        const TableView tv = open_table(table);
+        int win = 0;
+        Op::prologue(prm.spec, win);
+        const uint32_t Gu = gridDim.x - prm.n_reducers;
+        uint32_t t = blockIdx.x - prm.n_reducers;
+        const bool loader = threadIdx.x < 4;
+        if (t < tv.n_tiles) {
+            uint2 tl_next = make_uint2(0u, 0u);
+            if (loader) {
+                const uint2 tl0 = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t));
+                cp_async16(reinterpret_cast<char*>(&s_slot[0].row) + threadIdx.x * 16,
+                           reinterpret_cast<const char*>(tv.rows + tl0.x) + threadIdx.x * 16);
+                if (threadIdx.x == 0) s_sh.tile[0] = tl0.y;
+                if (t + Gu < tv.n_tiles) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t + Gu));
+                cp_async_wait_all();
+                if (threadIdx.x == 0) {
+                    s_sh.seen_owner = -1;
+                    s_sh.seen_lo = 0;
+                    s_sh.seen_hi = -1;
+                    step_tile_ready<GT, kWorld>(prm, &s_slot[0].row, s_sh.tile[0], tv.tile_elems, &s_sh, true);
                 }
             }
-            if (pc != kNone) {
-                if (count_now) step_count_piece(prm, pb, kThreads / 32);
-                else uncounted = pc;
+            __syncthreads();
+            int slot = 0;
+            for (;;) {
+                const bool has_next = t + Gu < tv.n_tiles;
+                if (loader && has_next) {
+                    cp_async16(reinterpret_cast<char*>(&s_slot[slot ^ 1].row) + threadIdx.x * 16,
+                               reinterpret_cast<const char*>(tv.rows + tl_next.x) + threadIdx.x * 16);
+                    if (threadIdx.x == 0) s_sh.tile[slot ^ 1] = tl_next.y;
+                    const uint32_t t2 = t + 2 * Gu;
+                    if (t2 < tv.n_tiles && t2 > t) tl_next = __ldg(reinterpret_cast<const uint2*>(tv.tiles + t2));
+                }
+                bad |= step_one_tile<Op, kThreads, kU>(prm.spec, &s_slot[slot].row, s_sh.tile[slot], tv.tile_elems, win);
+                if (!has_next) break;
+                if (loader) {
+                    cp_async_wait_all();
+                    if (threadIdx.x == 0)
+                        step_tile_ready<GT, kWorld>(prm, &s_slot[slot ^ 1].row, s_sh.tile[slot ^ 1], tv.tile_elems, &s_sh, true);
+                }
+                __syncthreads();
+                slot ^= 1;
+                t += Gu;
             }
         }
-        B200_PROF(4)
-        // ---- (4) thread 0: may the next tile run?  Blocking is allowed only when the next iteration has no piece
-        //          to start (producers must never be starved by waiting consumers)
-        if (threadIdx.x == 0) {
-            if (fresh_piece != kNone) sh->piece_next = fresh_piece;
-            sh->go[slot ^ 1] = sh->idx[slot ^ 1] != kNone ? step_tile_ready<GT, kWorld>(prm, &s_slot[slot ^ 1].row, sh->tile[slot ^ 1],
-                                                                                    sh->tile_elems, &s_sh, sh->pc[slot ^ 1] == kNone) : 0;
-        }
-        B200_PROF(6)
-        __syncthreads();
-        B200_PROF(7)
-        slot ^= 1;
     }
-    if (uncounted != kNone) step_count_piece(prm, prm.begin + static_cast<long long>(uncounted) * kPieceElems, kThreads / 32);
-#ifdef B200_STEP_PROFILE
-    if (threadIdx.x == 0 && blockIdx.x < 512) {           // scratch[2048 + 20 * cta ...]: cycles per phase, iterations, tiles
-        long long* out = reinterpret_cast<long long*>(prm.scratch + 2048) + 10 * blockIdx.x;
-        for (int i = 0; i < 8; i++) out[i] = prof_acc[i];
-        out[8] = prof_iters;
-        out[9] = prof_tiles;
-    }
-#endif
     bad |= wait_failed(&prm.sync.pad[prm.sync.rank]->error);
     Op::finish(prm.spec, bad);
-    // the last CTA to leave resets the piece tickets (the next launch is ordered after this one on the stream)
+    // the last CTA to leave resets the run tickets (the next launch is ordered after this one on the stream)
     __syncthreads();
     if (threadIdx.x == 0) {
         if (atomicAdd(prm.scratch + 2, 1) == static_cast<int>(gridDim.x) - 1) {
@@ -1926,10 +1870,16 @@ int32_t b200_peer_reduce_shard(const void* const* peer_bufs, int32_t world, void
 }  // extern "C" (templates need C++ linkage)
 
 template <int G, int S, int C>
-static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const PeerStepParams& prm, int64_t n_pieces,
+static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const PeerStepParams& in, int32_t n_reducers,
                                  cudaStream_t st) {
     constexpr int kThreads = 256;
-    const size_t smem = static_cast<size_t>(prm.world <= 2 ? 2 : prm.world <= 4 ? 4 : 8) * kPieceElems * sizeof(typename Elem<G>::type);
+    PeerStepParams prm = in;
+    // a reducer CTA keeps n_stages pieces (world x 4 or 8 KB each) in flight; two CTAs per SM share 227 KB
+    const size_t stage = static_cast<size_t>(prm.world <= 2 ? 2 : prm.world <= 4 ? 4 : 8) * kPieceElems * sizeof(typename Elem<G>::type);
+    prm.n_stages = static_cast<int>(96 * 1024 / stage);
+    if (prm.n_stages > 6) prm.n_stages = 6;
+    if (prm.n_stages < 2) prm.n_stages = 2;
+    const size_t smem = stage * prm.n_stages;
 #define B200_LAUNCH_STEP(W_)                                                                              \
     {                                                                                                     \
         auto kernel = peer_spec_step_kernel<G, S, C, kThreads, W_>;                                       \
@@ -1948,9 +1898,10 @@ static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const P
         int64_t blocks = static_cast<int64_t>(sm_count()) * occ;                                          \
         const int cap = g_peer_max_ctas.load();                                                           \
         if (cap > 0 && blocks > cap) blocks = cap;                                                        \
-        const int64_t work = n_tiles > n_pieces ? n_tiles : n_pieces;                                     \
-        if (blocks > work) blocks = work;                                                                 \
-        if (blocks < 1) blocks = 1;                                                                       \
+        if (blocks > n_tiles + n_reducers) blocks = n_tiles + n_reducers;                                 \
+        if (blocks < 2) blocks = 2;                                                                       \
+        prm.n_reducers = n_reducers < blocks - 1 ? n_reducers : static_cast<int>(blocks - 1);            \
+        if (prm.n_reducers < 1) prm.n_reducers = 1;                                                       \
         kernel<<<static_cast<unsigned>(blocks), kThreads, smem, st>>>(dev_table, prm);                    \
     }
     if (prm.world <= 2) B200_LAUNCH_STEP(2)
@@ -1966,8 +1917,8 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
                             int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
                             const float* dev_inv_scale, int32_t* dev_flag, const int32_t* dev_parity,
                             const b200_step_sync* sync, const b200_peer_pull* pull, const void* const* peer_grads,
-                            void* reduced, float factor, const b200_peer_sync* psync, int64_t chunk_elems,
-                            void* dev_scratch, int64_t scratch_bytes, void* stream) {
+                            void* reduced, float factor, const b200_peer_sync* psync, int32_t n_reducers,
+                            int64_t chunk_elems, void* dev_scratch, int64_t scratch_bytes, void* stream) {
     if (!dev_table || n_tiles <= 0) return set_error(B200_EINVAL, "peer_spec_step: empty table");
     if (!dev_parity || !dev_flag || !pull || !peer_grads || !reduced || !psync || !dev_scratch)
         return set_error(B200_EINVAL, "peer_spec_step: NULL argument");
@@ -1978,8 +1929,9 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
     if (int rc = fill_adam_consts("peer_spec_step", groups, n_groups, prm.spec.grp)) return rc;
     if (int rc = to_peer_sync(psync, prm.sync, "peer_spec_step")) return rc;
     if (psync->world != prm.spec.pull.world) return set_error(B200_EINVAL, "peer_spec_step: sync->world != pull->world");
-    if (chunk_elems < kPieceElems || chunk_elems % kPieceElems)
-        return set_error(B200_EINVAL, "peer_spec_step: chunk_elems must be a multiple of %d", kPieceElems);
+    if (chunk_elems < kRunElems || chunk_elems % kRunElems)
+        return set_error(B200_EINVAL, "peer_spec_step: chunk_elems must be a multiple of %lld", kRunElems);
+    if (n_reducers < 1) n_reducers = 1;
     prm.spec.pull.first_tile = 0;                        // the table is already ordered for this rank
     prm.spec.inv_scale = inv_scale;
     prm.spec.dev_inv_scale = dev_inv_scale;
@@ -2007,14 +1959,13 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles, int32_t grad
     for (int r = 0; r < B200_MAX_PEERS; r++) prm.grads.p[r] = r < prm.world ? peer_grads[r] : nullptr;
     for (int r = 0; r < prm.world; r++)
         if (!prm.grads.p[r]) return set_error(B200_EINVAL, "peer_spec_step: gradient buffer %d is NULL", r);
-    const int64_t n_pieces = (prm.end - prm.begin + kPieceElems - 1) / kPieceElems;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (grad_dtype == B200_F16 && state_dtype == B200_F32 && copy_dtype == B200_F16)
-        return launch_peer_spec_step<B200_F16, B200_F32, B200_F16>(dev_table, n_tiles, prm, n_pieces, st);
+        return launch_peer_spec_step<B200_F16, B200_F32, B200_F16>(dev_table, n_tiles, prm, n_reducers, st);
     if (grad_dtype == B200_BF16 && state_dtype == B200_F32 && copy_dtype == B200_BF16)
-        return launch_peer_spec_step<B200_BF16, B200_F32, B200_BF16>(dev_table, n_tiles, prm, n_pieces, st);
+        return launch_peer_spec_step<B200_BF16, B200_F32, B200_BF16>(dev_table, n_tiles, prm, n_reducers, st);
     if (grad_dtype == B200_F32 && state_dtype == B200_F32 && copy_dtype == B200_NONE)
-        return launch_peer_spec_step<B200_F32, B200_F32, B200_NONE>(dev_table, n_tiles, prm, n_pieces, st);
+        return launch_peer_spec_step<B200_F32, B200_F32, B200_NONE>(dev_table, n_tiles, prm, n_reducers, st);
     return set_error(B200_EDTYPE, "peer_spec_step: (grad,state,copy) dtypes (%d,%d,%d) not instantiated", grad_dtype,
                      state_dtype, copy_dtype);
 }

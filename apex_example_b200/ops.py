@@ -266,7 +266,7 @@ def spec_repair(table: TensorTable, state_dtype, copy_dtype, dev_found_inf, dev_
 
 
 def peer_spec_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup], dev_flag, dev_parity,
-                   pull, peer_grad_ptrs, reduced: torch.Tensor, factor: float, psync, chunk_elems: int,
+                   pull, peer_grad_ptrs, reduced: torch.Tensor, factor: float, psync, n_reducers: int, chunk_elems: int,
                    scratch: torch.Tensor, inv_scale: float = 1.0, dev_inv_scale=None, sync: StepSync | None = None):
     """Gradient mean across ranks + speculative Adam step in ONE kernel (b200_peer_spec_step)."""
     _require_cuda(table)
@@ -276,7 +276,7 @@ def peer_spec_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, grou
                                                dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
                                                _addr(dev_flag), _addr(dev_parity),
                                                ctypes.byref(sync) if sync is not None else None, ctypes.byref(pull), ptrs,
-                                               reduced.data_ptr(), factor, ctypes.byref(psync), chunk_elems,
+                                               reduced.data_ptr(), factor, ctypes.byref(psync), n_reducers, chunk_elems,
                                                scratch.data_ptr(), scratch.numel() * scratch.element_size(), _stream()),
                "peer_spec_step")
 

@@ -206,7 +206,8 @@ class PeerSpecStep:
     ``buffers.local["grads"]``; it is re-ordered in place.  Must be the first user of the buffers' signal pads
     (the progress board lives right behind the pad)."""
 
-    def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, chunk_elems: int | None = None):
+    def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, chunk_elems: int | None = None,
+                 n_reducers: int = 32):
         self.buf = buffers
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1
@@ -216,7 +217,8 @@ class PeerSpecStep:
             chunk_elems = 1 << 19
         min_chunk = -(-shard // _lib.PEER_STEP_MAX_CHUNKS)
         chunk_elems = max(int(chunk_elems), min_chunk)
-        self.chunk_elems = -(-chunk_elems // 2048) * 2048
+        self.chunk_elems = -(-chunk_elems // 32768) * 32768
+        self.n_reducers = int(n_reducers)
         self.epoch = 0
         if buffers.signal_ptrs is not None and buffers._n_pads < _lib.PEER_STEP_PAD_BYTES // 128:
             raise RuntimeError("PeerSpecStep must allocate the signal pads itself (pad + progress board)")
@@ -234,5 +236,5 @@ class PeerSpecStep:
         self.epoch += 1
         psync = ops.make_peer_sync(self._pads, b.rank, self.epoch)
         ops.peer_spec_step(self.table, grad_dtype, state_dtype, copy_dtype, groups, dev_flag, dev_parity, self.pull,
-                           self._grad_ptrs, b.local["reduced"], self.factor, psync, self.chunk_elems,
+                           self._grad_ptrs, b.local["reduced"], self.factor, psync, self.n_reducers, self.chunk_elems,
                            self.scratch, inv_scale=inv_scale, dev_inv_scale=dev_inv_scale, sync=sync)

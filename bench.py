@@ -369,6 +369,7 @@ def main():
                     help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
                          "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
                          "check pass -> scaler update -> update in place")
+    ap.add_argument("--reducers", type=int, default=32, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
     ap.add_argument("--chunk-elems", type=int, default=0, help="spec mode, N>1: elements per announced chunk of the fused kernel (0 = default)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
@@ -449,7 +450,7 @@ def main():
     stepper = None
     if spec and use_peer:
         from apex_example_b200.parallel.peer import PeerSpecStep
-        stepper = PeerSpecStep(pbufs, bounds, table, chunk_elems=args.chunk_elems or None)
+        stepper = PeerSpecStep(pbufs, bounds, table, chunk_elems=args.chunk_elems or None, n_reducers=args.reducers)
 
     def current_cols():
         """p, m, v, copy as they are current right now (synchronises in spec mode to read the parity)."""

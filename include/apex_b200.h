@@ -417,21 +417,21 @@ int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_d
  * b200_peer_reduce_shard followed by b200_fused_adam_peer costs NVLink time PLUS HBM time: the
  * in-place update may not start before every rank has reduced (and inspected) its whole shard.
  * With the speculative update (b200_fused_adam_spec) nothing is destroyed, so both halves run at
- * the same time inside one kernel, in every CTA: per iteration a CTA starts the loads of one
- * 2048-element PIECE of this rank's shard from every rank's gradient buffer as cp.async copies
- * into shared memory, runs the speculative Adam pass on one update tile while they cross NVLink,
- * then folds the piece (arithmetic exactly as b200_peer_reduce_shard) into `reduced`.  When the
- * last piece of a `chunk_elems`-element chunk is folded, the chunk is announced to every rank:
- * each rank's signal pad is FOLLOWED by a progress board of B200_MAX_PEERS x
- * B200_PEER_STEP_MAX_CHUNKS int32 epoch flags (board[owner][chunk]), i.e. the pad allocation must
- * be B200_PEER_STEP_PAD_BYTES long and zeroed.  A tile is updated only after the owner of its
- * gradient has announced the chunk it lies in.  Every rank inspects every reduced gradient it
- * pulls, so *dev_flag is complete without a flag exchange; follow with b200_spec_commit and
- * b200_spec_repair exactly as after b200_fused_adam_spec.
+ * the same time inside one kernel: the first `n_reducers` CTAs REDUCE this rank's shard — runs of
+ * sixteen 2048-element pieces, every rank's slice of a piece staged in shared memory by cp.async,
+ * several pieces deep, arithmetic exactly as b200_peer_reduce_shard — and when the last piece of
+ * a `chunk_elems`-element chunk is folded the chunk is announced to every rank: each rank's signal
+ * pad is FOLLOWED by a progress board of B200_MAX_PEERS x B200_PEER_STEP_MAX_CHUNKS int32 epoch
+ * flags (board[owner][chunk]), i.e. the pad allocation must be B200_PEER_STEP_PAD_BYTES long and
+ * zeroed.  All other CTAs UPDATE: they stride over the tile list, wait until the owner of a tile's
+ * gradient has announced the chunk(s) it lies in, pull the reduced gradient over NVLink and run the
+ * speculative Adam pass.  Every rank inspects every reduced gradient it pulls, so *dev_flag is
+ * complete without a flag exchange; follow with b200_spec_commit and b200_spec_repair exactly as
+ * after b200_fused_adam_spec.
  *
  * Requirements: shards that never cut a tile (tables.tile_aligned_shards); the table's tile list
  * ordered by b200_table_order_for_peer_step (chunk-major, own shard first) with the same
- * chunk_elems (a multiple of 2048, at most B200_PEER_STEP_MAX_CHUNKS chunks per shard);
+ * chunk_elems (a multiple of 32768, at most B200_PEER_STEP_MAX_CHUNKS chunks per shard);
  * `dev_scratch` >= (8 + chunks per shard) * 4 bytes, zeroed once; `psync->epoch` growing by one per
  * step on every rank.
  * ------------------------------------------------------------------------------------------ */
@@ -446,7 +446,8 @@ int32_t b200_peer_spec_step(const void* dev_table, int64_t n_tiles,
                             float inv_scale, const float* dev_inv_scale,
                             int32_t* dev_flag, const int32_t* dev_parity, const b200_step_sync* sync,
                             const b200_peer_pull* pull, const void* const* peer_grads, void* reduced,
-                            float factor, const b200_peer_sync* psync, int64_t chunk_elems,
+                            float factor, const b200_peer_sync* psync,
+                            int32_t n_reducers, int64_t chunk_elems,
                             void* dev_scratch, int64_t scratch_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------

@@ -230,7 +230,7 @@ def _worker_fused(rank, world, port, repeats):
     dc = [h.cuda() for h in hc]
     g_local = bufs.local["grads"]
     table = TensorTable([[g_local[o:o + n] for o, n in zip(offs, sizes)]] + [[a for a, _ in st[k]] for k in "pmv"] + [dc])
-    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=32768)
+    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=32768, n_reducers=24)
     state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
     ops.scaler_init(state, S)
     fs = state.view(torch.float32)

@@ -112,7 +112,7 @@ def _layout(sizes):
     return offs, off
 
 
-@pytest.mark.parametrize("world,chunk", [(2, 8192), (4, 2048), (4, 1 << 20), (8, 16384)])
+@pytest.mark.parametrize("world,chunk", [(2, 32768), (4, 65536), (4, 1 << 20), (8, 32768)])
 def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
     """All `world` ranks live on ONE GPU: each has its own buffers, state, signal pad, scratch and stream, and
     its kernel (grid capped to 12 CTAs so that all of them are resident together) really waits for the others'
@@ -121,7 +121,7 @@ def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
     ops.set_peer_grid(12)
     try:
         gen = torch.Generator().manual_seed(40 + world)
-        sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 33000]
+        sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 330000]
         offs, total = _layout(sizes)
         bounds = tile_aligned_shards(offs, sizes, total, world)
         S = 256.0
@@ -159,7 +159,7 @@ def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
                                        [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, good + 1, 1, 1)],
                                        rk["state"][ops.IDX_OVERFLOW_ACC:], rk["parity"], rk["pull"],
                                        [g.data_ptr() for g in grads], reduced[r], 1.0 / world,
-                                       ops.make_peer_sync(pad_ptrs, r, it + 1), chunk, rk["scratch"],
+                                       ops.make_peer_sync(pad_ptrs, r, it + 1), 3, chunk, rk["scratch"],
                                        dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
                     ops.spec_commit(rk["state"], True, 2000, 2.0, 0.0, 2.0 ** 24, rk["parity"])
                     ops.spec_repair(rk["table"], torch.float32, torch.float16, rk["state"][ops.IDX_FOUND_INF:], rk["parity"])

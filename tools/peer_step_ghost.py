@@ -53,7 +53,7 @@ def main():
         epoch[0] += 1
         ops.peer_spec_step(table, torch.float16, torch.float32, torch.float16, [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, k, 1, 1)],
                            state[ops.IDX_OVERFLOW_ACC:], parity, pull, [g.data_ptr() for g in grads], reduced[0], 0.5,
-                           ops.make_peer_sync(pad_ptrs, 0, epoch[0]), chunk, scratch, dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
+                           ops.make_peer_sync(pad_ptrs, 0, epoch[0]), int(os.environ.get('REDUCERS', '32')), chunk, scratch, dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:])
 
     def plain_spec(k):
         ops.fused_adam_spec(plain, torch.float16, torch.float32, torch.float16, [ops.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.01, k, 1, 1)],
