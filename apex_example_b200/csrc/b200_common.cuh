@@ -267,7 +267,7 @@ __device__ __forceinline__ void cp_async8(volatile void* smem_dst, const void* g
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(s), "l"(gmem_src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-// wait until at most `pending` of the committed groups are still in flight (pending < 8)
+// wait until at most `pending` of the committed groups are still in flight (pending < 12)
 __device__ __forceinline__ void cp_async_wait_pending(int pending, int /*max*/) {
     switch (pending) {
     case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
@@ -277,7 +277,11 @@ __device__ __forceinline__ void cp_async_wait_pending(int pending, int /*max*/) 
     case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
     case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
     case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
-    default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+    case 7: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+    case 8: asm volatile("cp.async.wait_group 8;" ::: "memory"); break;
+    case 9: asm volatile("cp.async.wait_group 9;" ::: "memory"); break;
+    case 10: asm volatile("cp.async.wait_group 10;" ::: "memory"); break;
+    default: asm volatile("cp.async.wait_group 11;" ::: "memory"); break;
     }
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }

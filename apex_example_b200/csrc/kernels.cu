@@ -1877,7 +1877,7 @@ static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const P
     // a reducer CTA keeps n_stages pieces (world x 4 or 8 KB each) in flight; two CTAs per SM share 227 KB
     const size_t stage = static_cast<size_t>(prm.world <= 2 ? 2 : prm.world <= 4 ? 4 : 8) * kPieceElems * sizeof(typename Elem<G>::type);
     prm.n_stages = static_cast<int>(96 * 1024 / stage);
-    if (prm.n_stages > 6) prm.n_stages = 6;
+    if (prm.n_stages > 12) prm.n_stages = 12;
     if (prm.n_stages < 2) prm.n_stages = 2;
     const size_t smem = stage * prm.n_stages;
 #define B200_LAUNCH_STEP(W_)                                                                              \
