@@ -266,6 +266,37 @@ __device__ __forceinline__ void cp_async8(volatile void* smem_dst, const void* g
     const uint32_t s = static_cast<uint32_t>(__cvta_generic_to_shared(const_cast<void*>(smem_dst)));
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(s), "l"(gmem_src) : "memory");
 }
+// ---- mbarrier + bulk asynchronous copy (TMA without a tensor map, no multicast): one thread moves KBs ----
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(a), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" :: "r"(a), "r"(parity) : "memory");
+}
+// global -> this CTA's shared memory, `bytes` a multiple of 16, both addresses 16-byte aligned; completion is
+// signalled on `bar` as transaction bytes
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, unsigned bytes, uint64_t* bar) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+    const uint32_t b = static_cast<uint32_t>(__cvta_generic_to_shared(bar));
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(d), "l"(gmem_src), "r"(bytes), "r"(b) : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 // wait until at most `pending` of the committed groups are still in flight (pending < 12)
 __device__ __forceinline__ void cp_async_wait_pending(int pending, int /*max*/) {

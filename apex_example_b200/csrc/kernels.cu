@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <type_traits>
@@ -1044,7 +1045,7 @@ peer_gather_kernel(const __grid_constant__ PeerBufs reduced, int world, void* __
 // (b200_table_order_for_peer_step): consumers trail producers by construction.  Every rank inspects every
 // reduced gradient it pulls, so each rank's overflow flag is complete on its own: no flag exchange.
 constexpr int kPieceElems = 256 * kVec;
-constexpr int kRunPieces = 16;                              // pieces a reducer CTA folds between two fences
+constexpr int kRunPieces = 64;                              // pieces a reducer CTA folds between two fences
 constexpr long long kRunElems = static_cast<long long>(kRunPieces) * kPieceElems;
 
 __device__ __forceinline__ int32_t* peer_board(b200_peer_signal_pad* pad) {
@@ -1204,8 +1205,7 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
     using Op = AdamSpecOp<G, S, C>;
     using GT = typename Elem<G>::type;
     constexpr int kU = 2 * Op::kUnrollMul;
-    constexpr int kCopies = static_cast<int>(sizeof(GT)) * kVec / 16;      // 16-byte cp.async per thread, rank and piece
-    extern __shared__ __align__(16) unsigned char s_stage[];               // kWorld x kPieceElems gradient elements
+    extern __shared__ __align__(128) unsigned char s_stage[];              // reducer stages: kWorld slices of one piece each
     __shared__ __align__(16) RowSlot s_slot[2];
     __shared__ StepShared s_sh;
     bool bad = false;
@@ -1225,11 +1225,18 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
         // pieces deep, so a reducer CTA keeps kStages x world x 4 KB in flight without holding registers; a run is
         // counted (one fence for all its stores) when it is done, and the CTA that completes a chunk announces it.
         const int n_stage = prm.n_stages;
-        const size_t stage_bytes = static_cast<size_t>(kWorld) * kPieceElems * sizeof(GT);
+        const size_t stage_bytes = static_cast<size_t>(kWorld) * kPieceElems * sizeof(GT);      // one slice per rank
         const long long shard = prm.end - prm.begin;
         const long long n_runs = (shard + kRunElems - 1) / kRunElems;
         const bool vec_ok = (prm.begin % kVec) == 0;                  // cp.async needs 16-byte aligned sources
         __shared__ long long s_run;
+        __shared__ __align__(8) uint64_t s_bar[12];                    // one mbarrier per stage
+        if (threadIdx.x == 0) {
+            for (int i = 0; i < n_stage; i++) mbar_init(&s_bar[i], 1);
+            fence_barrier_init();
+        }
+        uint32_t phase = 0;                                            // bit s: parity the next wait on stage s expects
+        constexpr unsigned kSliceBytes = kPieceElems * sizeof(GT);
         for (;;) {
             __syncthreads();
             if (threadIdx.x == 0) s_run = atomicAdd(reinterpret_cast<unsigned*>(prm.scratch + 3), 1u);
@@ -1239,32 +1246,34 @@ peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ Pe
             const long long rb = prm.begin + run * kRunElems;
             const long long re = rb + kRunElems < prm.end ? rb + kRunElems : prm.end;
             const int n_pc = static_cast<int>((re - rb + kPieceElems - 1) / kPieceElems);
-            auto issue = [&](int j) {                                  // piece j of the run -> stage j % n_stage
-                const long long pb = rb + static_cast<long long>(j) * kPieceElems;
-                if (j < n_pc && !dead && vec_ok && pb + kPieceElems <= re) {
-                    unsigned char* st = s_stage + (j % n_stage) * stage_bytes;
-#pragma unroll
-                    for (int r = 0; r < kWorld; r++) {
-                        if (r < prm.world) {
-                            const char* src = reinterpret_cast<const char*>(reinterpret_cast<const GT*>(prm.grads.p[r]) + pb) +
-                                              threadIdx.x * (kVec * sizeof(GT));
-                            unsigned char* dst = st + (static_cast<size_t>(r) * kPieceElems + threadIdx.x * kVec) * sizeof(GT);
-#pragma unroll
-                            for (int k = 0; k < kCopies; k++) cp_async16(dst + 16 * k, src + 16 * k);
-                        }
-                    }
-                }
-                cp_async_commit();                                     // one group per piece, empty ones included
+            // a piece travels as `world` bulk copies (one per rank, 4 or 8 KB each) issued by ONE thread; they
+            // complete on the stage's mbarrier.  Ragged or unaligned pieces are not staged (element path below).
+            auto staged = [&](int j) {
+                return j < n_pc && !dead && vec_ok && rb + static_cast<long long>(j + 1) * kPieceElems <= re;
             };
-            for (int j = 0; j < n_stage - 1; j++) issue(j);
+            auto issue = [&](int j) {                                  // thread 0: piece j of the run -> stage j % n_stage
+                if (!staged(j)) return;
+                const long long pb = rb + static_cast<long long>(j) * kPieceElems;
+                const int sidx = j % n_stage;
+                unsigned char* st = s_stage + sidx * stage_bytes;
+                mbar_expect_tx(&s_bar[sidx], kSliceBytes * prm.world);
+                for (int r = 0; r < prm.world; r++)
+                    bulk_load(st + static_cast<size_t>(r) * kSliceBytes, reinterpret_cast<const GT*>(prm.grads.p[r]) + pb,
+                              kSliceBytes, &s_bar[sidx]);
+            };
+            if (threadIdx.x == 0)
+                for (int j = 0; j < n_stage - 1; j++) issue(j);
             for (int j = 0; j < n_pc; j++) {
-                issue(j + n_stage - 1);
-                cp_async_wait_pending(n_stage - 1, n_stage);           // piece j's slices have landed
+                __syncthreads();                                       // everybody is done with the stage issued next
+                if (threadIdx.x == 0) issue(j + n_stage - 1);
                 const long long pb = rb + static_cast<long long>(j) * kPieceElems;
                 const long long pe = pb + kPieceElems < re ? pb + kPieceElems : re;
                 if (!dead) {
-                    if (vec_ok && pe - pb == kPieceElems) {
-                        const unsigned char* st = s_stage + (j % n_stage) * stage_bytes;
+                    if (staged(j)) {
+                        const int sidx = j % n_stage;
+                        mbar_wait(&s_bar[sidx], (phase >> sidx) & 1u); // piece j's slices have landed
+                        phase ^= 1u << sidx;
+                        const unsigned char* st = s_stage + sidx * stage_bytes;
                         float acc[kVec];
                         Raw8<G> raw;
                         lds8<G>(st + (threadIdx.x * kVec) * sizeof(GT), raw);
@@ -1877,7 +1886,8 @@ static int launch_peer_spec_step(const void* dev_table, int64_t n_tiles, const P
     // a reducer CTA keeps n_stages pieces (world x 4 or 8 KB each) in flight; two CTAs per SM share 227 KB
     const size_t stage = static_cast<size_t>(prm.world <= 2 ? 2 : prm.world <= 4 ? 4 : 8) * kPieceElems * sizeof(typename Elem<G>::type);
     prm.n_stages = static_cast<int>(96 * 1024 / stage);
-    if (prm.n_stages > 12) prm.n_stages = 12;
+    static const int stage_cap = getenv("B200_STEP_STAGES") ? atoi(getenv("B200_STEP_STAGES")) : 6;   // tuning knob
+    if (prm.n_stages > stage_cap) prm.n_stages = stage_cap;
     if (prm.n_stages < 2) prm.n_stages = 2;
     const size_t smem = stage * prm.n_stages;
 #define B200_LAUNCH_STEP(W_)                                                                              \

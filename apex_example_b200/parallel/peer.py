@@ -217,7 +217,7 @@ class PeerSpecStep:
             chunk_elems = 1 << 19
         min_chunk = -(-shard // _lib.PEER_STEP_MAX_CHUNKS)
         chunk_elems = max(int(chunk_elems), min_chunk)
-        self.chunk_elems = -(-chunk_elems // 32768) * 32768
+        self.chunk_elems = -(-chunk_elems // 131072) * 131072
         self.n_reducers = int(n_reducers)
         self.epoch = 0
         if buffers.signal_ptrs is not None and buffers._n_pads < _lib.PEER_STEP_PAD_BYTES // 128:

@@ -418,7 +418,7 @@ int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_d
  * in-place update may not start before every rank has reduced (and inspected) its whole shard.
  * With the speculative update (b200_fused_adam_spec) nothing is destroyed, so both halves run at
  * the same time inside one kernel: the first `n_reducers` CTAs REDUCE this rank's shard — runs of
- * sixteen 2048-element pieces, every rank's slice of a piece staged in shared memory by cp.async,
+ * 64 pieces of 2048 elements, every rank's slice of a piece staged in shared memory by cp.async,
  * several pieces deep, arithmetic exactly as b200_peer_reduce_shard — and when the last piece of
  * a `chunk_elems`-element chunk is folded the chunk is announced to every rank: each rank's signal
  * pad is FOLLOWED by a progress board of B200_MAX_PEERS x B200_PEER_STEP_MAX_CHUNKS int32 epoch
@@ -431,7 +431,7 @@ int32_t b200_spec_repair(const void* dev_table, int64_t n_tiles, int32_t state_d
  *
  * Requirements: shards that never cut a tile (tables.tile_aligned_shards); the table's tile list
  * ordered by b200_table_order_for_peer_step (chunk-major, own shard first) with the same
- * chunk_elems (a multiple of 32768, at most B200_PEER_STEP_MAX_CHUNKS chunks per shard);
+ * chunk_elems (a multiple of 131072, at most B200_PEER_STEP_MAX_CHUNKS chunks per shard);
  * `dev_scratch` >= (8 + chunks per shard) * 4 bytes, zeroed once; `psync->epoch` growing by one per
  * step on every rank.
  * ------------------------------------------------------------------------------------------ */

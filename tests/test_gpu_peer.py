@@ -217,7 +217,7 @@ def _worker_fused(rank, world, port, repeats):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     from apex_example_b200.parallel.peer import PeerBuffers, PeerSpecStep
-    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 600000]
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 1600000]
     offs, total = _layout(sizes)
     bounds = tile_aligned_shards(offs, sizes, total, world)
     bufs = PeerBuffers(total, torch.float16)
@@ -230,7 +230,7 @@ def _worker_fused(rank, world, port, repeats):
     dc = [h.cuda() for h in hc]
     g_local = bufs.local["grads"]
     table = TensorTable([[g_local[o:o + n] for o, n in zip(offs, sizes)]] + [[a for a, _ in st[k]] for k in "pmv"] + [dc])
-    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=32768, n_reducers=24)
+    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=131072, n_reducers=24)
     state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
     ops.scaler_init(state, S)
     fs = state.view(torch.float32)

@@ -112,7 +112,7 @@ def _layout(sizes):
     return offs, off
 
 
-@pytest.mark.parametrize("world,chunk", [(2, 32768), (4, 65536), (4, 1 << 20), (8, 32768)])
+@pytest.mark.parametrize("world,chunk", [(2, 131072), (4, 262144), (4, 1 << 20), (8, 131072)])
 def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
     """All `world` ranks live on ONE GPU: each has its own buffers, state, signal pad, scratch and stream, and
     its kernel (grid capped to 12 CTAs so that all of them are resident together) really waits for the others'
@@ -121,7 +121,7 @@ def test_fused_peer_step_emulated_ranks_match_oracle(world, chunk):
     ops.set_peer_grid(12)
     try:
         gen = torch.Generator().manual_seed(40 + world)
-        sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 330000]
+        sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 930000]
         offs, total = _layout(sizes)
         bounds = tile_aligned_shards(offs, sizes, total, world)
         S = 256.0
