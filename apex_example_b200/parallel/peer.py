@@ -207,7 +207,7 @@ class PeerSpecStep:
     (the progress board lives right behind the pad)."""
 
     def __init__(self, buffers: PeerBuffers, bounds, table, gradient_average: bool = True, chunk_elems: int | None = None,
-                 n_reducers: int = 32):
+                 n_reducers: int | None = None):
         self.buf = buffers
         self.bounds = list(bounds)
         assert len(self.bounds) == buffers.world + 1
@@ -218,7 +218,8 @@ class PeerSpecStep:
         min_chunk = -(-shard // _lib.PEER_STEP_MAX_CHUNKS)
         chunk_elems = max(int(chunk_elems), min_chunk)
         self.chunk_elems = -(-chunk_elems // 131072) * 131072
-        self.n_reducers = int(n_reducers)
+        # measured on B200 (GPT-2-small list): 32 reducer CTAs are best at 2 ranks, 16 at 8 (profiles/r02_summary.md)
+        self.n_reducers = int(n_reducers) if n_reducers else (32 if buffers.world <= 2 else 24 if buffers.world <= 4 else 16)
         self.epoch = 0
         if buffers.signal_ptrs is not None and buffers._n_pads < _lib.PEER_STEP_PAD_BYTES // 128:
             raise RuntimeError("PeerSpecStep must allocate the signal pads itself (pad + progress board)")

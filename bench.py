@@ -369,7 +369,7 @@ def main():
                     help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
                          "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
                          "check pass -> scaler update -> update in place")
-    ap.add_argument("--reducers", type=int, default=32, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
+    ap.add_argument("--reducers", type=int, default=0, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
     ap.add_argument("--chunk-elems", type=int, default=0, help="spec mode, N>1: elements per announced chunk of the fused kernel (0 = default)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
                     help="N>1: 'peer' = reduce-scatter kernel + optimizer pulling reduced shards over NVLink; "
@@ -450,7 +450,7 @@ def main():
     stepper = None
     if spec and use_peer:
         from apex_example_b200.parallel.peer import PeerSpecStep
-        stepper = PeerSpecStep(pbufs, bounds, table, chunk_elems=args.chunk_elems or None, n_reducers=args.reducers)
+        stepper = PeerSpecStep(pbufs, bounds, table, chunk_elems=args.chunk_elems or None, n_reducers=args.reducers or None)
 
     def current_cols():
         """p, m, v, copy as they are current right now (synchronises in spec mode to read the parity)."""
@@ -618,8 +618,9 @@ def main():
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
     cm = sum(check_ms) / len(check_ms)
     if spec and world > 1:
-        roof["kernel"] = ("peer_spec_step_kernel<f16,f32,f16> (b200_peer_spec_step: every CTA folds reduce-scatter pieces staged "
-                          "over NVLink with cp.async while it runs check + unscale + AdamW + copy on update tiles; one launch)")
+        roof["kernel"] = ("peer_spec_step_kernel<f16,f32,f16> (b200_peer_spec_step: a few reducer CTAs reduce-scatter this rank's shard "
+                          "over NVLink through bulk-copy staged shared memory while all other CTAs run check + unscale + AdamW + "
+                          "copy on tiles whose chunk has been announced; one launch)")
         roof["nvlink"] = {"bytes_in_per_gpu": 2 * n * 2 * (world - 1) // world, "note": "(N-1)/N of the gradient bytes twice: "
                           "peers' gradients into the reduce role, reduced shards into the update role",
                           "inbound_gbs": 2 * n * 2 * (world - 1) / world / (adam_avg_ms * 1e-3) / 1e9, "nvlink_peak_gbs_per_dir": 900.0}

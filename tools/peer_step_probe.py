@@ -38,7 +38,7 @@ def main():
     mb = [ops.spec_state_like(c.float()) for c in copy]
     vb = [ops.spec_state_like(c.float()) for c in copy]
     table = TensorTable([list(torch.split(g, sizes)), [x for x, _ in pb], [x for x, _ in mb], [x for x, _ in vb], copy])
-    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=chunk or None, n_reducers=int(os.environ.get('REDUCERS', '32')))
+    stepper = PeerSpecStep(bufs, bounds, table, chunk_elems=chunk or None, n_reducers=int(os.environ.get('REDUCERS', '0')) or None)
     state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device=dev)
     ops.scaler_init(state, 65536.0)
     fs = state.view(torch.float32)
