@@ -64,7 +64,12 @@ def auto_tile_elems(columns) -> int:
         t = next((x for x in col if x is not None), None)
         if t is not None:
             width += t.element_size()
-    return 32768 if width <= 4 else _lib.TILE_ELEMS
+    if width <= 4:
+        return 32768
+    # all-16-bit lists (amp O3: g, p, m, v in fp16/bf16; 8 bytes per element over the columns): the step kernels
+    # keep 4 groups in flight there, i.e. 8192 elements per trip (measured on the 34k-tensor config-5 list:
+    # 4.57 ms with 4096-element tiles, 3.99 ms with 8192, profiles/r02_summary.md)
+    return 8192 if width <= 8 else _lib.TILE_ELEMS
 
 
 def build_image(columns: Sequence[Sequence[torch.Tensor | None]], groups: Sequence[int] | None = None,
