@@ -26,6 +26,12 @@ class AdamGroup(ctypes.Structure):           # b200_adam_group
                 ("adam_w_mode", c_int32)]
 
 
+class LambGroup(ctypes.Structure):           # b200_lamb_group
+    _fields_ = [("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
+                ("weight_decay", c_double), ("step", c_int64), ("bias_correction", c_int32),
+                ("adam_w_mode", c_int32), ("grad_averaging", c_int32), ("use_nvlamb", c_int32)]
+
+
 class SgdGroup(ctypes.Structure):            # b200_sgd_group
     _fields_ = [("lr", c_double), ("momentum", c_double), ("dampening", c_double),
                 ("weight_decay", c_double), ("step", c_int64), ("nesterov", c_int32),
@@ -91,6 +97,12 @@ SIGNATURES = {
     "b200_multi_tensor_check": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p]),
     "b200_multi_tensor_l2norm": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p, c_int64, c_void_p,
                                            c_void_p]),
+    "b200_l2norm_per_tensor": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_int32, c_void_p, c_void_p,
+                                         c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b200_lamb_stage1": (c_int32, [c_void_p, c_int64, c_int32, c_int32, ctypes.POINTER(LambGroup), c_int32, c_float,
+                                   c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
+    "b200_lamb_stage2": (c_int32, [c_void_p, c_int64, c_int32, c_int32, ctypes.POINTER(LambGroup), c_int32, c_void_p,
+                                   c_void_p, c_void_p, c_void_p]),
     "b200_clip_scale": (c_int32, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "b200_fused_adam": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),

@@ -379,6 +379,199 @@ __global__ void clip_scale_kernel(float* sumsq, const float* dev_inv_scale, floa
 }
 
 // ============================================================================================
+// per-tensor L2 norms (amp_C.multi_tensor_l2norm(per_tensor=True)) and FusedLAMB
+// ============================================================================================
+// Deterministic by construction: one CTA per tile sums its squares in a fixed order, one warp per tensor sums
+// the tensor's tiles in a fixed order, one warp sums the tensors.  No floating-point atomics.
+template <int DT, int kThreads>
+__global__ void __launch_bounds__(kThreads)
+tile_sumsq_kernel(const void* __restrict__ table, int col, const uint32_t* __restrict__ first_tile,
+                  float* __restrict__ tile_ss, int32_t* flag) {
+    const TableView tv = open_table(table);
+    const uint32_t t = blockIdx.x;
+    if (t >= tv.n_tiles) return;
+    const b200_table_tile tl = tv.tiles[t];
+    const b200_table_row& row = tv.rows[tl.tensor];
+    const int64_t start = static_cast<int64_t>(tl.tile) * tv.tile_elems;
+    const int64_t left = row.numel - start;
+    const int n = left < static_cast<int64_t>(tv.tile_elems) ? static_cast<int>(left) : static_cast<int>(tv.tile_elems);
+    float s = 0.0f;
+    bool bad = false;
+    for (int i = threadIdx.x; i < n; i += kThreads) {
+        const float x = load1<DT>(row.ptr[col], start + i);
+        bad |= !is_finite(x);
+        s = __fmaf_rn(x, x, s);
+    }
+    __shared__ float s_warp[kThreads / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float tot = 0.0f;
+        for (int w = 0; w < kThreads / 32; w++) tot += s_warp[w];
+        tile_ss[first_tile[tl.tensor] + tl.tile] = tot;  // natural position: independent of the tile order
+    }
+    if (flag) raise_flag(flag, bad);
+}
+
+// first_tile[t] .. first_tile[t + 1]: the tiles of tensor t in tile_ss (exclusive prefix sum of the tile counts).  Block b handles tensor b (one warp).
+__global__ void tensor_norm_kernel(const float* __restrict__ tile_ss, const uint32_t* __restrict__ first_tile, int n_tensors,
+                                   float* __restrict__ sumsq_out, float* __restrict__ norm_out) {
+    const int t = blockIdx.x;
+    if (t >= n_tensors) return;
+    float s = 0.0f;
+    for (uint32_t i = first_tile[t] + threadIdx.x; i < first_tile[t + 1]; i += 32) s += tile_ss[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (threadIdx.x == 0) {
+        if (sumsq_out) sumsq_out[t] = s;
+        if (norm_out) norm_out[t] = __fsqrt_rn(s);
+    }
+}
+
+__global__ void total_sumsq_kernel(const float* __restrict__ sumsq, int n, float* __restrict__ total) {
+    float s = 0.0f;
+    for (int i = threadIdx.x; i < n; i += 32) s += sumsq[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (threadIdx.x == 0) total[0] += s;                // several lists (dtypes) accumulate into the same total
+}
+
+struct LambConsts {
+    float b1, b3, b2, one_m_b2, bc1, bc2, eps, decay, lr;
+    uint32_t flags;                 // bit0: decoupled decay (adam_w_mode), bit1: trust ratio on even without decay (nvlamb)
+};
+
+struct Lamb1Params {
+    LambConsts grp[B200_MAX_GROUPS];
+    float inv_scale;
+    const float* dev_inv_scale;
+    const int32_t* dev_found_inf;
+    const float* dev_grad_sumsq;    // sum of squares of the (still scaled) gradients of ALL lists
+    float max_grad_norm;
+};
+
+// stage 1: moments and the un-trusted update u (column 4, fp32); p is only read
+template <int G, int S>
+struct Lamb1Op {
+    using Params = Lamb1Params;
+    static constexpr int kUnrollMul = 1;
+    struct Ctx { LambConsts k; float s, clip; };
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int&) {
+        return p.dev_found_inf != nullptr && *reinterpret_cast<const volatile int32_t*>(p.dev_found_inf) != 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int, int64_t) {
+        const float s = p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale;
+        const float gn = __fmul_rn(__fsqrt_rn(__ldg(p.dev_grad_sumsq)), s);     // norm of the unscaled gradients
+        const float clip = (p.max_grad_norm > 0.0f && gn > p.max_grad_norm) ? __fdiv_rn(gn, p.max_grad_norm) : 1.0f;
+        return Ctx{p.grp[r.group], s, clip};
+    }
+    static __device__ __forceinline__ float one(float g_in, float p, float& m, float& v, const Ctx& c) {
+        float g = __fdiv_rn(__fmul_rn(g_in, c.s), c.clip);
+        if (!(c.k.flags & 1u)) g = __fadd_rn(g, __fmul_rn(c.k.decay, p));
+        m = __fadd_rn(__fmul_rn(c.k.b1, m), __fmul_rn(c.k.b3, g));
+        v = __fadd_rn(__fmul_rn(c.k.b2, v), __fmul_rn(__fmul_rn(c.k.one_m_b2, g), g));
+        const float mh = __fdiv_rn(m, c.k.bc1), vh = __fdiv_rn(v, c.k.bc2);
+        float u = __fdiv_rn(mh, __fadd_rn(__fsqrt_rn(vh), c.k.eps));
+        if (c.k.flags & 1u) u = __fadd_rn(u, __fmul_rn(c.k.decay, p));
+        return u;
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            Raw8<G> rg;
+            Raw8<S> rp, rm, rv;
+            load8<G, true>(r.ptr[0], idx[u], rg);
+            load8<S, true>(r.ptr[1], idx[u], rp);
+            load8<S, false>(r.ptr[2], idx[u], rm);
+            load8<S, false>(r.ptr[3], idx[u], rv);
+            float g[kVec], p[kVec], m[kVec], v[kVec], o[kVec];
+            unpack8<G>(rg, g);
+            unpack8<S>(rp, p);
+            unpack8<S>(rm, m);
+            unpack8<S>(rv, v);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) o[i] = one(g[i], p[i], m[i], v[i], c);
+            store8<S>(r.ptr[2], idx[u], m);
+            store8<S>(r.ptr[3], idx[u], v);
+            store8<B200_F32>(r.ptr[4], idx[u], o);
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        float m = load1<S>(r.ptr[2], i), v = load1<S>(r.ptr[3], i);
+        const float u = one(load1<G>(r.ptr[0], i), load1<S>(r.ptr[1], i), m, v, c);
+        store1<S>(r.ptr[2], i, m);
+        store1<S>(r.ptr[3], i, v);
+        store1<B200_F32>(r.ptr[4], i, u);
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
+struct Lamb2Params {
+    LambConsts grp[B200_MAX_GROUPS];
+    const int32_t* dev_found_inf;
+    const float* p_norm;            // per tensor (row index)
+    const float* u_norm;
+};
+
+// stage 2: p -= trust_ratio * u, columns 0 = u (fp32), 1 = p, 2 = model copy (optional)
+template <int S, int C>
+struct Lamb2Op {
+    using Params = Lamb2Params;
+    static constexpr int kUnrollMul = 1;
+    struct Ctx { float ratio; };
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int&) {
+        return p.dev_found_inf != nullptr && *reinterpret_cast<const volatile int32_t*>(p.dev_found_inf) != 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int, int64_t) {
+        const LambConsts& k = p.grp[r.group];
+        float ratio = k.lr;
+        if ((k.flags & 2u) || k.decay != 0.0f) {
+            const float pn = __ldg(p.p_norm + r.reserved), un = __ldg(p.u_norm + r.reserved);
+            if (pn != 0.0f && un != 0.0f) ratio = __fmul_rn(k.lr, __fdiv_rn(pn, un));
+        }
+        return Ctx{ratio};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            Raw8<B200_F32> ru;
+            Raw8<S> rp;
+            load8<B200_F32, true>(r.ptr[0], idx[u], ru);
+            load8<S, false>(r.ptr[1], idx[u], rp);
+            float uu[kVec], p[kVec];
+            unpack8<B200_F32>(ru, uu);
+            unpack8<S>(rp, p);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) p[i] = __fsub_rn(p[i], __fmul_rn(c.ratio, uu[i]));
+            store8<S>(r.ptr[1], idx[u], p);
+            if constexpr (C != B200_NONE) {
+                if constexpr (S != B200_F32) {
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) p[i] = round_through<S>(p[i]);
+                }
+                store8<C>(r.ptr[2], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        const float p = __fsub_rn(load1<S>(r.ptr[1], i), __fmul_rn(c.ratio, load1<B200_F32>(r.ptr[0], i)));
+        store1<S>(r.ptr[1], i, p);
+        if constexpr (C != B200_NONE) store1<C>(r.ptr[2], i, round_through<S>(p));
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
+// ============================================================================================
 // fused unscale + Adam + master->model copy
 // ============================================================================================
 struct AdamConsts {
@@ -1682,6 +1875,99 @@ int32_t b200_fused_adam_peer(const void* dev_table, int64_t n_tiles, int32_t gra
     prm.dev_found_inf = dev_found_inf;
     prm.sync = to_sync(sync);
     return dispatch_step<AdamOp>("fused_adam", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-tensor norms and LAMB
+// ------------------------------------------------------------------------------------------------
+int32_t b200_l2norm_per_tensor(const void* dev_table, int64_t n_tiles, int32_t col, int32_t dtype,
+                               const uint32_t* dev_first_tile, int32_t n_tensors, float* dev_tile_ss,
+                               float* dev_sumsq_per_tensor, float* dev_norm_per_tensor, float* dev_total_sumsq,
+                               int32_t* dev_flag, void* stream) {
+    if (!valid_dt(dtype)) return set_error(B200_EDTYPE, "l2norm_per_tensor: bad dtype");
+    if (col < 0 || col >= B200_MAX_DEPTH) return set_error(B200_EINVAL, "l2norm_per_tensor: bad column");
+    if (n_tensors < 0 || n_tiles < 0 || n_tiles > 0x7fffffffll) return set_error(B200_EINVAL, "l2norm_per_tensor: bad size");
+    if (n_tensors == 0) return 0;
+    if (!dev_table || !dev_first_tile || !dev_tile_ss || !dev_sumsq_per_tensor)
+        return set_error(B200_EINVAL, "l2norm_per_tensor: NULL argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n_tiles > 0) {
+        B200_DISPATCH_DT(dtype, I, (tile_sumsq_kernel<I, 256><<<static_cast<unsigned>(n_tiles), 256, 0, st>>>(
+                                       dev_table, col, dev_first_tile, dev_tile_ss, dev_flag)))
+        g_launches.fetch_add(1);
+    }
+    tensor_norm_kernel<<<n_tensors, 32, 0, st>>>(dev_tile_ss, dev_first_tile, n_tensors, dev_sumsq_per_tensor, dev_norm_per_tensor);
+    g_launches.fetch_add(1);
+    if (dev_total_sumsq) {
+        total_sumsq_kernel<<<1, 32, 0, st>>>(dev_sumsq_per_tensor, n_tensors, dev_total_sumsq);
+        g_launches.fetch_add(1);
+    }
+    return after_launch("l2norm_per_tensor");
+}
+
+static int fill_lamb_consts(const char* name, const b200_lamb_group* groups, int32_t n_groups, LambConsts* grp) {
+    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
+        return set_error(B200_EINVAL, "%s: n_groups must be 1..%d", name, B200_MAX_GROUPS);
+    for (int i = 0; i < n_groups; i++) {
+        const b200_lamb_group& h = groups[i];
+        if (h.step < 1) return set_error(B200_EINVAL, "%s: step must be >= 1", name);
+        LambConsts& k = grp[i];
+        k.b1 = static_cast<float>(h.beta1);
+        k.b3 = h.grad_averaging ? static_cast<float>(1.0 - h.beta1) : 1.0f;
+        k.b2 = static_cast<float>(h.beta2);
+        k.one_m_b2 = static_cast<float>(1.0 - h.beta2);
+        k.bc1 = h.bias_correction ? static_cast<float>(1.0 - std::pow(h.beta1, static_cast<double>(h.step))) : 1.0f;
+        k.bc2 = h.bias_correction ? static_cast<float>(1.0 - std::pow(h.beta2, static_cast<double>(h.step))) : 1.0f;
+        k.eps = static_cast<float>(h.eps);
+        k.decay = static_cast<float>(h.weight_decay);
+        k.lr = static_cast<float>(h.lr);
+        k.flags = (h.adam_w_mode ? 1u : 0u) | (h.use_nvlamb ? 2u : 0u);
+    }
+    return 0;
+}
+
+int32_t b200_lamb_stage1(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                         const b200_lamb_group* groups, int32_t n_groups, float inv_scale, const float* dev_inv_scale,
+                         const int32_t* dev_found_inf, const float* dev_grad_sumsq, float max_grad_norm, void* stream) {
+    if (!dev_grad_sumsq) return set_error(B200_EINVAL, "lamb_stage1: dev_grad_sumsq is NULL");
+    Lamb1Params prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = fill_lamb_consts("lamb_stage1", groups, n_groups, prm.grp)) return rc;
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.dev_found_inf = dev_found_inf;
+    prm.dev_grad_sumsq = dev_grad_sumsq;
+    prm.max_grad_norm = max_grad_norm;
+#define B200_TRY(G_, S_) \
+    if (grad_dtype == G_ && state_dtype == S_) return launch_tiles<Lamb1Op<G_, S_>>("lamb_stage1", dev_table, n_tiles, prm, stream);
+    B200_TRY(B200_F16, B200_F32)
+    B200_TRY(B200_BF16, B200_F32)
+    B200_TRY(B200_F32, B200_F32)
+    B200_TRY(B200_F16, B200_F16)
+    B200_TRY(B200_BF16, B200_BF16)
+#undef B200_TRY
+    return set_error(B200_EDTYPE, "lamb_stage1: (grad,state) dtypes (%d,%d) not instantiated", grad_dtype, state_dtype);
+}
+
+int32_t b200_lamb_stage2(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                         const b200_lamb_group* groups, int32_t n_groups, const int32_t* dev_found_inf,
+                         const float* dev_p_norm, const float* dev_u_norm, void* stream) {
+    if (!dev_p_norm || !dev_u_norm) return set_error(B200_EINVAL, "lamb_stage2: NULL norm array");
+    Lamb2Params prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = fill_lamb_consts("lamb_stage2", groups, n_groups, prm.grp)) return rc;
+    prm.dev_found_inf = dev_found_inf;
+    prm.p_norm = dev_p_norm;
+    prm.u_norm = dev_u_norm;
+#define B200_TRY(S_, C_) \
+    if (state_dtype == S_ && copy_dtype == C_) return launch_tiles<Lamb2Op<S_, C_>>("lamb_stage2", dev_table, n_tiles, prm, stream);
+    B200_TRY(B200_F32, B200_NONE)
+    B200_TRY(B200_F32, B200_F16)
+    B200_TRY(B200_F32, B200_BF16)
+    B200_TRY(B200_F16, B200_NONE)
+    B200_TRY(B200_BF16, B200_NONE)
+#undef B200_TRY
+    return set_error(B200_EDTYPE, "lamb_stage2: (state,copy) dtypes (%d,%d) not instantiated", state_dtype, copy_dtype);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -80,6 +80,7 @@ int64_t b200_table_build(void* host_image, int64_t image_bytes, int32_t n_tensor
         if (g < 0 || g >= B200_MAX_GROUPS) return b200::set_error(B200_EINVAL, "table_build: group %d out of range", g);
         r.group = static_cast<uint32_t>(g);
         r.flags = aligned ? 1u : 0u;
+        r.reserved = static_cast<uint64_t>(t);          // the row's own index (per-tensor quantities: LAMB trust ratios)
         const int64_t k = tiles_of(numel[t], tile_elems);
         for (int64_t i = 0; i < k; i++) {
             tiles[n_tiles].tensor = static_cast<uint32_t>(t);

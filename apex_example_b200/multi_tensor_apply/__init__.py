@@ -112,10 +112,23 @@ _NORM_SCRATCH = {}
 
 def multi_tensor_l2norm(chunk_size, noop_flag, tensor_lists, per_tensor=False):
     """amp_C.multi_tensor_l2norm(chunk_size, noop_flag, [tensors], per_tensor) -> (norm, per_tensor_norms).
-    One read-only pass; the flag is raised on inf/NaN like apex's.  ``per_tensor=True`` (LAMB's
-    trust ratios) is outside this path's scope."""
+    One read-only pass; the flag is raised on inf/NaN like apex's.  ``per_tensor=True`` (LAMB's trust ratios) returns
+    the norm of every tensor too, summed in a fixed order (b200_l2norm_per_tensor)."""
     if per_tensor:
-        raise RuntimeError("multi_tensor_l2norm(per_tensor=True) is not provided by libapex_b200")
+        if len(tensor_lists) != 1:
+            raise RuntimeError("multi_tensor_l2norm expects tensor_lists = [tensors]")
+        tensors = tensor_lists[0]
+        device = tensors[0].device if tensors else noop_flag.device
+        total = torch.zeros(1, device=device)
+        norms = torch.zeros(len(tensors), device=device)
+        if tensors:
+            _check_flag(noop_flag)
+            table = table_for(tensor_lists)
+            ss = torch.empty(len(tensors), device=device)
+            tile_ss = torch.empty(max(table.n_tiles, 1), device=device)
+            ops.l2norm_per_tensor(table, 0, tensors[0].dtype, table.first_tiles(), tile_ss, ss, norms=norms, total=total,
+                                  dev_flag=noop_flag)
+        return total.sqrt_(), norms
     if len(tensor_lists) != 1:
         raise RuntimeError("multi_tensor_l2norm expects tensor_lists = [tensors]")
     tensors = tensor_lists[0]

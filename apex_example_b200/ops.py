@@ -190,6 +190,40 @@ def multi_tensor_l2norm(table: TensorTable, col: int, dtype, sumsq: torch.Tensor
                                                     _addr(dev_flag), _stream()), "multi_tensor_l2norm")
 
 
+LambGroup = _lib.LambGroup
+
+
+def l2norm_per_tensor(table: TensorTable, col: int, dtype, first_tiles: torch.Tensor, tile_ss: torch.Tensor,
+                      sumsq: torch.Tensor, norms: torch.Tensor | None = None, total: torch.Tensor | None = None,
+                      dev_flag=None):
+    """Per-tensor sums of squares (``sumsq``: fp32[n_tensors]) and norms of column ``col``; ADDS the list's total to
+    ``total`` (fp32[1]).  ``first_tiles`` = table.first_tiles(); ``tile_ss`` = fp32 scratch of n_tiles elements."""
+    _require_cuda(table)
+    if tile_ss.numel() < table.n_tiles or sumsq.numel() < table.n_tensors:
+        raise RuntimeError("l2norm_per_tensor: scratch or output too small")
+    _lib.check(_lib.load().b200_l2norm_per_tensor(table.ptr, table.n_tiles, col, dtype_code(dtype), first_tiles.data_ptr(),
+                                                  table.n_tensors, tile_ss.data_ptr(), sumsq.data_ptr(), _addr(norms),
+                                                  _addr(total), _addr(dev_flag), _stream()), "l2norm_per_tensor")
+
+
+def lamb_stage1(table: TensorTable, grad_dtype, state_dtype, groups: Sequence[LambGroup], grad_sumsq: torch.Tensor,
+                max_grad_norm: float, inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+    _require_cuda(table)
+    arr = (LambGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_lamb_stage1(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype), arr,
+                                            len(groups), inv_scale, _addr(dev_inv_scale), _addr(dev_found_inf),
+                                            grad_sumsq.data_ptr(), float(max_grad_norm), _stream()), "lamb_stage1")
+
+
+def lamb_stage2(table: TensorTable, state_dtype, copy_dtype, groups: Sequence[LambGroup], p_norm: torch.Tensor,
+                u_norm: torch.Tensor, dev_found_inf=None):
+    _require_cuda(table)
+    arr = (LambGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_lamb_stage2(table.ptr, table.n_tiles, dtype_code(state_dtype), dtype_code(copy_dtype), arr,
+                                            len(groups), _addr(dev_found_inf), p_norm.data_ptr(), u_norm.data_ptr(),
+                                            _stream()), "lamb_stage2")
+
+
 def new_norm_scratch(device) -> torch.Tensor:
     return torch.zeros(_lib.NORM_SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
 

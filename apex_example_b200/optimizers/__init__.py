@@ -1,4 +1,5 @@
 from .fused_adam import FusedAdam
+from .fused_lamb import FusedLAMB
 from .fused_sgd import FusedSGD
 
-__all__ = ["FusedAdam", "FusedSGD"]
+__all__ = ["FusedAdam", "FusedLAMB", "FusedSGD"]

@@ -211,6 +211,13 @@ class FusedOptimizerBase(torch.optim.Optimizer):
             return False
         return plan["watch"].ok()
 
+    def _table_columns(self, s):
+        """Columns of the step table of one dtype set: gradient, parameter, state..., model copy."""
+        return [s["g"], s["p"]] + s["state"] + ([s["c"]] if s["c"] else [])
+
+    def _table_built(self, key, s, table):
+        """Hook: a dtype set got a new table (subclasses that launch more than one kernel per set build theirs here)."""
+
     def _ensure_plan(self):
         if self._plan_is_current():
             return self._plan
@@ -265,7 +272,7 @@ class FusedOptimizerBase(torch.optim.Optimizer):
             return None
         launches = []
         for key, s in sets.items():
-            columns = [s["g"], s["p"]] + s["state"] + ([s["c"]] if s["c"] else [])
+            columns = self._table_columns(s)
             # m / v / momentum are owned by this object (stable); grads, params and model copies
             # can be re-allocated behind our back, so their addresses form the cache key
             sig = (tuple(t.data_ptr() for t in s["g"]), tuple(t.data_ptr() for t in s["p"]),
@@ -274,6 +281,7 @@ class FusedOptimizerBase(torch.optim.Optimizer):
             if table is None or table.signature != sig:
                 table = TensorTable(columns, groups=s["grp"], signature=sig)
                 self._tables[key] = table
+                self._table_built(key, s, table)
             launches.append((key, table, s["gids"]))
         st_ = self._amp_stash
         self._plan = {"launches": launches, "device": device,

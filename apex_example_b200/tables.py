@@ -144,6 +144,21 @@ class TensorTable:
     def ptr(self) -> int:
         return self.dev.data_ptr()
 
+    @property
+    def tile_elems(self) -> int:
+        return int(self.image[16:20].view(torch.int32)[0])
+
+    def first_tiles(self) -> torch.Tensor:
+        """int32[n_tensors + 1] on the table's device: exclusive prefix sum of the tensors' tile counts (what
+        b200_l2norm_per_tensor takes as dev_first_tile), read back from the image's own rows."""
+        rows_off = int(self.image[24:32].view(torch.int64)[0])
+        rows = self.image[rows_off:rows_off + 64 * self.n_tensors].view(torch.int64).view(self.n_tensors, 8)
+        numel = rows[:, _lib.MAX_DEPTH]
+        te = self.tile_elems
+        first = torch.zeros(self.n_tensors + 1, dtype=torch.int64)
+        torch.cumsum((numel + te - 1) // te, 0, out=first[1:])
+        return first.to(torch.int32).to(self.dev.device)
+
     def order_for_peer_step(self, local_base_ptr: int, grad_elem_size: int, bounds, rank: int, chunk_elems: int):
         """Re-order the tile list for b200_peer_spec_step (chunk-major, this rank's shard first) and upload
         the image again.  ``bounds`` are the world+1 tile-aligned shard offsets of the flat gradient buffer."""

@@ -85,7 +85,7 @@ typedef struct b200_table_row {
     int64_t  numel;
     uint32_t group;
     uint32_t flags;             /* bit 0: every column is aligned for the 128/256-bit path */
-    uint64_t reserved;
+    uint64_t reserved;          /* the row's index in the list (set by b200_table_build) */
 } b200_table_row;               /* 64 bytes */
 
 typedef struct b200_table_tile {
@@ -369,6 +369,52 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
                             float inv_scale, const float* dev_inv_scale,
                             const int32_t* dev_found_inf, const b200_step_sync* sync,
                             const b200_peer_pull* pull, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * S2'' — per-tensor L2 norms and FusedLAMB.
+ * Replaces amp_C.multi_tensor_l2norm(..., per_tensor=True) (apex csrc/multi_tensor_l2norm_kernel.cu)
+ * and amp_C.multi_tensor_lamb (apex csrc/multi_tensor_lamb.cu: stage 1 = moments + update,
+ * stage 2 = trust-ratio apply) as apex/optimizers/fused_lamb.py calls them.  apex itself is not
+ * vendored in the reference (it is a pip dependency of test_apex_distributed_spawn.py:14-16);
+ * the rule restated in oracle/amp_step_oracle.c (lamb_*) follows the LAMB paper and apex's
+ * published kernel; parity for this row is UNPINNED against apex (no apex build here).
+ *
+ * b200_l2norm_per_tensor: sum of squares of column `col` of every tensor, deterministic (one CTA
+ * per tile in fixed order -> one warp per tensor over its tiles -> one warp over the tensors; no
+ * floating-point atomics).  dev_first_tile[n_tensors + 1] is the exclusive prefix sum of the
+ * tensors' tile counts (ceil(numel / tile_elems)); dev_tile_ss holds n_tiles floats of scratch.
+ * Writes dev_sumsq_per_tensor[t], dev_norm_per_tensor[t] = sqrt (may be NULL), ADDS the list's
+ * total to *dev_total_sumsq (may be NULL; several dtype lists accumulate) and raises *dev_flag
+ * on inf/NaN (may be NULL).
+ *
+ * b200_lamb_stage1, columns 0 g, 1 p (read only), 2 m, 3 v, 4 u (fp32 out):
+ *   g' = g * inv_scale / max(1, ||g * inv_scale||_all / max_grad_norm)      (max_grad_norm <= 0: no clip)
+ *   L2 mode: g' += wd * p;   m = b1*m + b3*g';  v = b2*v + (1-b2)*g'^2;  b3 = grad_averaging ? 1-b1 : 1
+ *   u = (m/bc1) / (sqrt(v/bc2) + eps);   AdamW mode: u += wd * p
+ * b200_lamb_stage2, columns 0 u (fp32), 1 p, 2 model copy (optional):
+ *   ratio = lr * ||p|| / ||u|| if (use_nvlamb or wd != 0) and both norms non-zero, else lr;  p -= ratio * u
+ * dev_p_norm / dev_u_norm are indexed by the row's index in the list.  Both stages skip when
+ * *dev_found_inf != 0. */
+typedef struct b200_lamb_group {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;
+    int32_t bias_correction;
+    int32_t adam_w_mode;
+    int32_t grad_averaging;
+    int32_t use_nvlamb;
+} b200_lamb_group;
+
+int32_t b200_l2norm_per_tensor(const void* dev_table, int64_t n_tiles, int32_t col, int32_t dtype,
+                               const uint32_t* dev_first_tile, int32_t n_tensors, float* dev_tile_ss,
+                               float* dev_sumsq_per_tensor, float* dev_norm_per_tensor,
+                               float* dev_total_sumsq, int32_t* dev_flag, void* stream);
+int32_t b200_lamb_stage1(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                         const b200_lamb_group* groups, int32_t n_groups,
+                         float inv_scale, const float* dev_inv_scale, const int32_t* dev_found_inf,
+                         const float* dev_grad_sumsq, float max_grad_norm, void* stream);
+int32_t b200_lamb_stage2(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                         const b200_lamb_group* groups, int32_t n_groups, const int32_t* dev_found_inf,
+                         const float* dev_p_norm, const float* dev_u_norm, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * S2' — speculative single-pass step: the overflow check rides on the update pass.

@@ -47,6 +47,14 @@ class _AdamGroup(ctypes.Structure):
                 ("adam_w_mode", ctypes.c_int32)]
 
 
+class _LambGroup(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double), ("weight_decay", ctypes.c_double),
+                ("step", ctypes.c_int64), ("bias_correction", ctypes.c_int32),
+                ("adam_w_mode", ctypes.c_int32), ("grad_averaging", ctypes.c_int32),
+                ("use_nvlamb", ctypes.c_int32)]
+
+
 class _SgdGroup(ctypes.Structure):
     _fields_ = [("lr", ctypes.c_double), ("momentum", ctypes.c_double),
                 ("dampening", ctypes.c_double), ("weight_decay", ctypes.c_double),
@@ -203,6 +211,36 @@ def sgd_list(gs, ps, moms, copies=None, *, check_overflow=True, inv_scale=1.0, *
                   _ptr_array(moms) if moms else None, _dt(ps[0]),
                   _ptr_array(copies) if copies else None, _dt(copies[0]) if copies else F32,
                   numel, ctypes.byref(grp), ctypes.c_float(inv_scale), ctypes.c_int(int(check_overflow))))
+
+
+def l2norm_per_tensor(xs, tile_elems: int):
+    """(per-tensor sums of squares as a float32 tensor, total as a python float, inf/NaN flag), summed in the order
+    the contract fixes (see amp_step_oracle.c)."""
+    n = len(xs)
+    numel = (ctypes.c_int64 * n)(*[t.numel() for t in xs])
+    out = torch.zeros(max(n, 1), dtype=torch.float32)
+    total = ctypes.c_float(0.0)
+    fn = lib().oracle_l2norm_per_tensor
+    fn.restype = ctypes.c_int
+    flag = int(fn(ctypes.c_int(n), _ptr_array(xs), _dt(xs[0]) if n else F32, numel, ctypes.c_int(tile_elems),
+                  ctypes.c_void_p(out.data_ptr()), ctypes.byref(total)))
+    return out[:n], total.value, flag
+
+
+def lamb_list(gs, ps, ms, vs, copies=None, *, tile_elems: int, grad_sumsq: float, inv_scale=1.0, max_grad_norm=0.0,
+              **hyper) -> None:
+    """One LAMB step over a list with one hyper-parameter group (state updated in place)."""
+    grp = _LambGroup(hyper.get("lr", 1e-3), hyper.get("beta1", 0.9), hyper.get("beta2", 0.999),
+                     hyper.get("eps", 1e-6), hyper.get("weight_decay", 0.01), hyper.get("step", 1),
+                     int(hyper.get("bias_correction", True)), int(hyper.get("adam_w_mode", True)),
+                     int(hyper.get("grad_averaging", True)), int(hyper.get("use_nvlamb", False)))
+    n = len(gs)
+    numel = (ctypes.c_int64 * n)(*[t.numel() for t in ps])
+    us = [torch.zeros(t.numel(), dtype=torch.float32) for t in ps]
+    lib().oracle_lamb_list(ctypes.c_int(n), _ptr_array(gs), _dt(gs[0]), _ptr_array(ps), _ptr_array(ms), _ptr_array(vs),
+                           _dt(ps[0]), _ptr_array(copies) if copies else None, _dt(copies[0]) if copies else F32,
+                           _ptr_array(us), numel, ctypes.c_int(tile_elems), ctypes.byref(grp),
+                           ctypes.c_float(inv_scale), ctypes.c_float(grad_sumsq), ctypes.c_float(max_grad_norm))
 
 
 # ------------------------------------------------------------------- torch-op restatement (pin)

@@ -27,6 +27,7 @@
  */
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #define DT_F32  0
@@ -421,4 +422,120 @@ int oracle_sgd_list(int n_tensors, const void* const* g, int g_dt,
     for (int t = 0; t < n_tensors; t++)
         oracle_sgd(g[t], g_dt, p[t], mom ? mom[t] : 0, s_dt, copy ? copy[t] : 0, c_dt, numel[t], grp, inv_scale);
     return 0;
+}
+
+/* ---- per-tensor L2 norms and LAMB -------------------------------------
+ * PARITY UNPINNED against apex: apex is a pip dependency of the reference (test_apex_distributed_spawn.py:14-16),
+ * not vendored, and cannot be built here.  The rule below restates the LAMB paper (You et al. 2020, Alg. 2) with the
+ * conventions apex.optimizers.FusedLAMB documents: global-norm clip of the gradients before the moments
+ * (max_grad_norm), beta3 = 1-beta1 when grad_averaging, bias correction, L2 or decoupled decay, trust ratio
+ * ||p||/||u|| applied when weight_decay != 0 or use_nvlamb, lr otherwise.  tests/test_gpu_lamb.py additionally
+ * compares with a straight torch restatement of the same published rule within a tolerance.
+ * The summation ORDER is part of the contract (the trust ratio depends on it bit for bit): a tile of `tile_elems`
+ * elements is summed by 256 strided accumulators (fused multiply-add), folded by a 32-wide butterfly and then over the
+ * 8 groups in order; a tensor's tiles are summed by 32 strided accumulators + butterfly; tensors likewise. */
+static float butterfly32(float* x) {
+    for (int o = 16; o > 0; o >>= 1) {
+        float y[32];
+        for (int l = 0; l < 32; l++) y[l] = x[l] + x[l ^ o];
+        memcpy(x, y, sizeof(y));
+    }
+    return x[0];
+}
+
+static float tile_sumsq(const void* x, int dt, int64_t start, int n, int* bad) {
+    float acc[256];
+    for (int t = 0; t < 256; t++) acc[t] = 0.0f;
+    for (int i = 0; i < n; i++) {
+        const float v = load_as_float(x, dt, start + i);
+        if (!finite_f(v)) *bad = 1;
+        acc[i & 255] = fmaf(v, v, acc[i & 255]);
+    }
+    float tot = 0.0f;
+    for (int w = 0; w < 8; w++) tot += butterfly32(acc + 32 * w);
+    return tot;
+}
+
+static float strided_sum32(const float* x, int64_t n) {
+    float acc[32];
+    for (int l = 0; l < 32; l++) acc[l] = 0.0f;
+    for (int64_t i = 0; i < n; i++) acc[i & 31] += x[i];
+    return butterfly32(acc);
+}
+
+/* sumsq[t] for every tensor; returns the inf/NaN flag; *total += sum over tensors (if total) */
+int oracle_l2norm_per_tensor(int n_tensors, const void* const* x, int dt, const int64_t* numel, int tile_elems,
+                             float* sumsq, float* total) {
+    int bad = 0;
+    for (int t = 0; t < n_tensors; t++) {
+        const int64_t tiles = numel[t] <= 0 ? 0 : (numel[t] + tile_elems - 1) / tile_elems;
+        float* ss = (float*)malloc(sizeof(float) * (size_t)(tiles > 0 ? tiles : 1));
+        for (int64_t k = 0; k < tiles; k++) {
+            const int64_t start = k * tile_elems;
+            const int64_t left = numel[t] - start;
+            ss[k] = tile_sumsq(x[t], dt, start, (int)(left < tile_elems ? left : tile_elems), &bad);
+        }
+        sumsq[t] = strided_sum32(ss, tiles);
+        free(ss);
+    }
+    if (total) *total += strided_sum32(sumsq, n_tensors);
+    return bad;
+}
+
+typedef struct {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;
+    int32_t bias_correction;
+    int32_t adam_w_mode;
+    int32_t grad_averaging;
+    int32_t use_nvlamb;
+} oracle_lamb_group;
+
+/* One LAMB step over a list that shares one hyper-parameter group.  grad_sumsq is the sum of squares of ALL (still
+ * scaled) gradients of the optimizer (every list).  u is fp32 scratch per tensor. */
+void oracle_lamb_list(int n_tensors, const void* const* g, int g_dt, void* const* p, void* const* m, void* const* v,
+                      int s_dt, void* const* copy, int c_dt, float* const* u, const int64_t* numel, int tile_elems,
+                      const oracle_lamb_group* grp, float inv_scale, float grad_sumsq, float max_grad_norm) {
+    const float b1 = (float)grp->beta1, b2 = (float)grp->beta2, one_m_b2 = (float)(1.0 - grp->beta2);
+    const float b3 = grp->grad_averaging ? (float)(1.0 - grp->beta1) : 1.0f;
+    const float bc1 = grp->bias_correction ? (float)(1.0 - pow(grp->beta1, (double)grp->step)) : 1.0f;
+    const float bc2 = grp->bias_correction ? (float)(1.0 - pow(grp->beta2, (double)grp->step)) : 1.0f;
+    const float eps = (float)grp->eps, wd = (float)grp->weight_decay, lr = (float)grp->lr;
+    const float gn = sqrtf(grad_sumsq) * inv_scale;
+    const float clip = (max_grad_norm > 0.0f && gn > max_grad_norm) ? gn / max_grad_norm : 1.0f;
+    for (int t = 0; t < n_tensors; t++)
+        for (int64_t i = 0; i < numel[t]; i++) {
+            float gi = load_as_float(g[t], g_dt, i) * inv_scale;
+            gi = gi / clip;
+            const float pi = load_as_float(p[t], s_dt, i);
+            float mi = load_as_float(m[t], s_dt, i), vi = load_as_float(v[t], s_dt, i);
+            if (!grp->adam_w_mode) { float d = wd * pi; gi = gi + d; }
+            { float a = b1 * mi, b = b3 * gi; mi = a + b; }
+            { float a = b2 * vi, b = one_m_b2 * gi; b = b * gi; vi = a + b; }
+            const float mh = mi / bc1, vh = vi / bc2;
+            float ui = mh / (sqrtf(vh) + eps);
+            if (grp->adam_w_mode) { float d = wd * pi; ui = ui + d; }
+            store_from_float(m[t], s_dt, i, mi);
+            store_from_float(v[t], s_dt, i, vi);
+            u[t][i] = ui;
+        }
+    float* pn = (float*)malloc(sizeof(float) * (size_t)(n_tensors + 1));
+    float* un = (float*)malloc(sizeof(float) * (size_t)(n_tensors + 1));
+    oracle_l2norm_per_tensor(n_tensors, (const void* const*)p, s_dt, numel, tile_elems, pn, 0);
+    oracle_l2norm_per_tensor(n_tensors, (const void* const*)u, DT_F32, numel, tile_elems, un, 0);
+    for (int t = 0; t < n_tensors; t++) {
+        float ratio = lr;
+        if (grp->use_nvlamb || grp->weight_decay != 0.0) {
+            const float a = sqrtf(pn[t]), b = sqrtf(un[t]);
+            if (a != 0.0f && b != 0.0f) ratio = lr * (a / b);
+        }
+        for (int64_t i = 0; i < numel[t]; i++) {
+            float pi = load_as_float(p[t], s_dt, i);
+            { float d = ratio * u[t][i]; pi = pi - d; }
+            store_from_float(p[t], s_dt, i, pi);
+            if (copy) store_from_float(copy[t], c_dt, i, s_dt == DT_F32 ? pi : load_as_float(p[t], s_dt, i));
+        }
+    }
+    free(pn);
+    free(un);
 }

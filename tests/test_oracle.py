@@ -272,3 +272,39 @@ def test_vectorised_o2_path_is_bit_identical_to_the_generic_loop():
                 force.value = 0
         for a, b in zip(*outs):
             assert _bits_equal_or_both_nan(a, b)
+
+
+def test_lamb_oracle_follows_the_published_rule():
+    """oracle.lamb_list against a double-precision restatement of LAMB (You et al. 2020, Alg. 2, with the global-norm
+    clip and bias correction apex.optimizers.FusedLAMB documents).  apex itself is not in the image: UNPINNED against
+    apex; this pins the oracle to the published rule within fp32 rounding (rtol 1e-5)."""
+    gen = torch.Generator().manual_seed(9)
+    sizes = [5, 4096, 4097, 10000]
+    ps = [torch.randn(n, generator=gen) * 0.1 for n in sizes]
+    ms = [torch.zeros(n) for n in sizes]
+    vs = [torch.zeros(n) for n in sizes]
+    dp, dm, dv = ([t.double() for t in lst] for lst in (ps, ms, vs))
+    lr, wd, b1, b2, eps, max_norm = 1e-2, 0.01, 0.9, 0.999, 1e-6, 1.0
+    for step in (1, 2, 3):
+        gs = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+        ss, total, flag = oracle.l2norm_per_tensor(gs, 4096)
+        assert flag == 0
+        torch.testing.assert_close(ss.double(), torch.stack([g.double().square().sum() for g in gs]), rtol=1e-5, atol=0)
+        oracle.lamb_list(gs, ps, ms, vs, tile_elems=4096, grad_sumsq=total, max_grad_norm=max_norm, lr=lr,
+                         weight_decay=wd, step=step, eps=eps)
+        gn = torch.sqrt(sum(g.double().square().sum() for g in gs))
+        clip = max(gn.item() / max_norm, 1.0)
+        for p, g, m, v in zip(dp, gs, dm, dv):
+            g = g.double() / clip
+            m.mul_(b1).add_(g, alpha=1 - b1)
+            v.mul_(b2).addcmul_(g, g, value=1 - b2)
+            u = (m / (1 - b1 ** step)) / ((v / (1 - b2 ** step)).sqrt() + eps) + wd * p
+            p.sub_(lr * p.norm() / u.norm() * u)
+        for a, b in zip(ps, dp):
+            torch.testing.assert_close(a.double(), b, rtol=1e-5, atol=1e-8)
+
+
+def test_l2norm_oracle_flags_non_finite_values():
+    xs = [torch.ones(10), torch.tensor([1.0, float("inf")])]
+    _, _, flag = oracle.l2norm_per_tensor(xs, 4096)
+    assert flag == 1
