@@ -85,7 +85,7 @@ class FusedLAMB(FusedOptimizerBase):
             return
         device = plan["device"]
         inv_scale, dev_inv, dev_found = self._scale_args()
-        if dev_found is not None and int(dev_found.item()) != 0:
+        if dev_found is not None and int(dev_found.reshape(-1)[0].item()) != 0:
             return                                           # skipped step: state and step count untouched
         steps, _ = self._next_steps(device, False)
         max_norm = float(self.defaults["max_grad_norm"] or 0.0)
