@@ -60,6 +60,11 @@ class PeerPull(ctypes.Structure):            # b200_peer_pull
     _fields_ = [("local_base", c_void_p), ("bounds", c_int64 * (MAX_PEERS + 1)), ("delta", c_int64 * MAX_PEERS),
                 ("world", c_int32), ("elem_size", c_int32), ("first_tile", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
 
+class PeerFan(ctypes.Structure):             # b200_peer_fan
+    _fields_ = [("grads", c_void_p * MAX_PEERS), ("models", c_void_p * MAX_PEERS), ("world", c_int32), ("rank", c_int32),
+                ("factor", c_float), ("reserved", c_int32), ("model_mc", c_void_p), ("grads_mc", c_void_p)]
+
+
 NOALLOC_TABLE_BYTES = 256 * 1024
 NORM_SCRATCH_BYTES = 16384
 
@@ -137,6 +142,11 @@ SIGNATURES = {
                                       c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
                                       ctypes.POINTER(PeerPull), ctypes.POINTER(c_void_p), c_void_p, c_float,
                                       ctypes.POINTER(PeerSync), c_int32, c_int64, c_void_p, c_int64, c_void_p]),
+    "b200_peer_shard_step": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup), c_int32,
+                                       c_float, c_void_p, c_void_p, c_void_p, ctypes.POINTER(StepSync),
+                                       ctypes.POINTER(PeerFan), ctypes.POINTER(PeerSync), c_void_p]),
+    "b200_peer_shard_repair": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p, ctypes.POINTER(PeerFan),
+                                         ctypes.POINTER(PeerSync), c_void_p]),
     "b200_fused_adam_noalloc": (c_int32, [c_int32, ctypes.POINTER(c_void_p), ctypes.POINTER(c_int64), c_int32, c_int32,
                                           c_int32, ctypes.POINTER(AdamGroup), c_float, c_void_p, c_void_p, c_void_p]),
     "b200_bucket_epilogue": (c_int32, [c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p]),

@@ -145,6 +145,44 @@ __device__ __forceinline__ void store8(void* base, int64_t idx, const float (&f)
     }
 }
 
+// 8 floats -> 8 sixteen-bit values (16 bytes), rounded like store8
+template <int DT>
+__device__ __forceinline__ void pack8_16(const float (&f)[kVec], uint32_t (&r)[4]) {
+    static_assert(DT == B200_F16 || DT == B200_BF16, "16-bit types only");
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if constexpr (DT == B200_F16) {
+            __half2 h = __halves2half2(__float2half_rn(f[2 * i]), __float2half_rn(f[2 * i + 1]));
+            r[i] = *reinterpret_cast<uint32_t*>(&h);
+        } else {
+            __nv_bfloat162 h = __halves2bfloat162(__float2bfloat16_rn(f[2 * i]), __float2bfloat16_rn(f[2 * i + 1]));
+            r[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+    }
+}
+
+// One 16-byte store through a MULTICAST address: the switch writes it into the same offset of every GPU bound to
+// the multicast object (this GPU included).  Stores only — no load, and nothing TMA, ever goes through this address.
+__device__ __forceinline__ void multimem_st128(void* mc_addr, const uint32_t (&r)[4]) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc_addr), "f"(__uint_as_float(r[0])), "f"(__uint_as_float(r[1])), "f"(__uint_as_float(r[2])),
+                    "f"(__uint_as_float(r[3]))
+                 : "memory");
+}
+
+// Eight 16-bit values summed over every GPU bound to the multicast object, inside the switch (.acc::f32; the order of the
+// addends and the precision of the switch's partial sums are not specified: a few 16-bit ulps from a rank-ordered sum).  A plain (non-TMA) load instruction.
+template <int DT>
+__device__ __forceinline__ void multimem_ld_reduce128(const void* mc_addr, uint32_t (&r)[4]) {
+    static_assert(DT == B200_F16 || DT == B200_BF16, "16-bit types only");
+    if constexpr (DT == B200_F16)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(mc_addr) : "memory");
+    else
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "l"(mc_addr) : "memory");
+}
+
 template <int DT>
 __device__ __forceinline__ float load1(const void* base, int64_t idx) {
     using T = typename Elem<DT>::type;

@@ -1160,6 +1160,238 @@ __global__ void peer_wait_flags_kernel(const __grid_constant__ PeerSync sync, in
     if (threadIdx.x == 0 && s_any && flag) *flag = 1;
 }
 
+// ============================================================================================
+// sharded step (ZeRO-1 style): reduce-scatter + speculative Adam on the own shard + all-gather, ONE pass
+// ============================================================================================
+// Each rank owns the fp32 master / m / v of its shard only.  For every 8-element group of its shard a thread
+// reads the gradients of ALL ranks (its own from HBM, the others over NVLink), averages them in rank order
+// exactly like peer_reduce_kernel (fp32 sum -> round to the gradient type -> x factor -> round), inspects the
+// mean, runs the speculative Adam update into the other copy of p / m / v, and STORES the new 16-bit weights
+// into the model buffer of every rank (posted writes over NVLink).  Tiles are independent of each other —
+// no chunk flags, no reducer/updater roles — and the inbound (gradients) and outbound (weights) directions of the
+// link are busy at the same time.  Per GPU and step: HBM 28 B x P/N + 2 x 2 B x P(N-1)/N served to / received
+// from peers; NVLink 2 B x P(N-1)/N each way.
+// Hand-shake: head = "my gradients of this epoch are in place and I no longer read my model weights" (ready);
+// tail = last CTA publishes "my reads of your gradients are over, my writes to your model have landed" + this
+// rank's overflow bit (done).  b200_peer_wait_flags then ORs the bits into the scaler's overflow word and
+// b200_spec_commit flips the parity unless any rank overflowed; b200_peer_shard_repair re-sends the old weights
+// after an overflow (rare), and exits at once otherwise.
+struct PeerFan {
+    long long grad_delta[B200_MAX_PEERS];    // bytes from this rank's gradient buffer to rank r's (0 for itself)
+    long long copy_delta[B200_MAX_PEERS];    // bytes from this rank's model buffer to rank r's
+    int world;
+    int store_world;                         // = world (a debug build of the host side may lower it)
+    float factor;
+    int use_mc;                              // 1: 16-byte groups go out as ONE multicast store (copy_mc_delta)
+    long long copy_mc_delta;                 // bytes from this rank's model buffer to the multicast address of the model buffers
+    int use_mc_grad;                         // 1: 16-byte groups of gradients are summed inside the switch (grad_mc_delta)
+    long long grad_mc_delta;
+};
+
+struct ShardStepParams {
+    AdamConsts grp[B200_MAX_GROUPS][B200_STEP_WINDOW];
+    float inv_scale;
+    const float* dev_inv_scale;
+    const int32_t* parity;
+    int32_t* flag;                           // used when there is no hand-shake (emulated ranks)
+    StepSync sync;
+    PeerFan fan;
+    PeerSync psync;
+};
+
+// tail of a kernel that takes part in the hand-shake: the last CTA to finish publishes done[rank] everywhere
+__device__ __forceinline__ void publish_done(const PeerSync& sync, bool bad) {
+    b200_peer_signal_pad* mine = sync.pad[sync.rank];
+    raise_flag(&mine->local_flag, bad);
+    __shared__ bool s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();
+        s_last = atomicAdd(reinterpret_cast<unsigned*>(&mine->ticket), 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        __threadfence_system();
+        const int32_t bit = *reinterpret_cast<volatile int32_t*>(&mine->local_flag) != 0 ? 1 : 0;
+        if (threadIdx.x < sync.world) st_release_sys(&sync.pad[threadIdx.x]->done[sync.rank], (sync.epoch << 1) | bit);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            mine->local_flag = 0;
+            mine->ticket = 0;
+        }
+    }
+}
+
+template <int G, int S, int C, int kWorld>
+struct ShardStepOp {
+    using Params = ShardStepParams;
+    static constexpr int kUnrollMul = 1;
+    struct Ctx { AdamConsts k; float s; const char* g; char* c; int64_t rd, wr; const PeerFan* fan; };
+    struct Acc { bool bad; };
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int& win) {
+        step_prologue(nullptr, p.sync, win);
+        if (p.psync.pad[0] != nullptr) {
+            b200_peer_signal_pad* mine = p.psync.pad[p.psync.rank];
+            if (blockIdx.x == 0 && threadIdx.x < p.psync.world)
+                st_release_sys(&p.psync.pad[threadIdx.x]->ready[p.psync.rank], p.psync.epoch);
+            if (threadIdx.x < p.psync.world) wait_at_least(&mine->ready[threadIdx.x], p.psync.epoch, &mine->error);
+            __syncthreads();
+            if (wait_failed(&mine->error)) {             // a rank never arrived: touch nobody's memory, poison the step
+                publish_done(p.psync, true);
+                return true;
+            }
+        }
+        return false;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int win, int64_t) {
+        using ST = typename Elem<S>::type;
+        const int cur = *reinterpret_cast<const volatile int32_t*>(p.parity) & 1;
+        const int64_t delta = spec_delta(r.numel, sizeof(ST)) / static_cast<int64_t>(sizeof(ST));
+        return Ctx{p.grp[r.group][win], p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale,
+                   reinterpret_cast<const char*>(r.ptr[0]), reinterpret_cast<char*>(r.ptr[4]),
+                   cur ? delta : 0, cur ? 0 : delta, &p.fan};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], Acc& acc) {
+        const int world = c.fan->world;
+        Raw8<G> rg[U][kWorld];
+        Raw8<S> rp[U], rm[U], rv[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                if (c.fan->use_mc_grad) {
+                    multimem_ld_reduce128<G>(c.g + c.fan->grad_mc_delta + idx[u] * 2, rg[u][0].r);
+                } else {
+#pragma unroll
+                    for (int w = 0; w < kWorld; w++)
+                        if (w < world) load8<G, false>(c.g + c.fan->grad_delta[w], idx[u], rg[u][w]);
+                }
+                load8<S, true>(r.ptr[1], idx[u] + c.rd, rp[u]);
+                load8<S, true>(r.ptr[2], idx[u] + c.rd, rm[u]);
+                load8<S, true>(r.ptr[3], idx[u] + c.rd, rv[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float g[kVec], p[kVec], m[kVec], v[kVec];
+            unpack8<G>(rg[u][0], g);
+#pragma unroll
+            for (int w = 1; w < kWorld; w++)
+                if (w < world && !c.fan->use_mc_grad) {
+                    float f[kVec];
+                    unpack8<G>(rg[u][w], f);
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) g[i] = __fadd_rn(g[i], f[i]);
+                }
+            unpack8<S>(rp[u], p);
+            unpack8<S>(rm[u], m);
+            unpack8<S>(rv[u], v);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) {
+                g[i] = round_through<G>(__fmul_rn(round_through<G>(g[i]), c.fan->factor));
+                acc.bad |= !is_finite(g[i]);
+            }
+            store8<G>(const_cast<char*>(c.g), idx[u], g);      // the mean replaces this rank's own gradient (its shard only)
+#pragma unroll
+            for (int i = 0; i < kVec; i++) adam_elem(g[i], p[i], m[i], v[i], c.k, c.s);
+            store8<S>(r.ptr[1], idx[u] + c.wr, p);
+            store8<S>(r.ptr[2], idx[u] + c.wr, m);
+            store8<S>(r.ptr[3], idx[u] + c.wr, v);
+            if (c.fan->use_mc) {
+                uint32_t packed[4];
+                pack8_16<C>(p, packed);
+                multimem_st128(c.c + c.fan->copy_mc_delta + idx[u] * 2, packed);
+            } else {
+#pragma unroll
+                for (int w = 0; w < kWorld; w++)
+                    if (w < c.fan->store_world) store8<C>(c.c + c.fan->copy_delta[w], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, Acc& acc) {
+        const int world = c.fan->world;
+        float g = load1<G>(c.g + c.fan->grad_delta[0], i);
+        for (int w = 1; w < world; w++) g = __fadd_rn(g, load1<G>(c.g + c.fan->grad_delta[w], i));
+        g = round_through<G>(__fmul_rn(round_through<G>(g), c.fan->factor));
+        acc.bad |= !is_finite(g);
+        store1<G>(const_cast<char*>(c.g), i, g);
+        float p = load1<S>(r.ptr[1], i + c.rd), m = load1<S>(r.ptr[2], i + c.rd), v = load1<S>(r.ptr[3], i + c.rd);
+        adam_elem(g, p, m, v, c.k, c.s);
+        store1<S>(r.ptr[1], i + c.wr, p);
+        store1<S>(r.ptr[2], i + c.wr, m);
+        store1<S>(r.ptr[3], i + c.wr, v);
+        for (int w = 0; w < c.fan->store_world; w++) store1<C>(c.c + c.fan->copy_delta[w], i, p);
+    }
+    static __device__ __forceinline__ void finish(const Params& p, const Acc& acc) {
+        if (p.psync.pad[0] != nullptr) publish_done(p.psync, acc.bad);
+        else if (p.flag) raise_flag(p.flag, acc.bad);
+    }
+};
+
+// after a skipped sharded step: every rank re-sends cast(current master) of its shard to every rank's model buffer
+struct ShardRepairParams {
+    const int32_t* found_inf;
+    const int32_t* parity;
+    PeerFan fan;
+    PeerSync psync;
+};
+
+template <int S, int C, int kWorld>
+struct ShardRepairOp {
+    using Params = ShardRepairParams;
+    static constexpr int kUnrollMul = 2;
+    struct Ctx { int64_t rd; char* c; const PeerFan* fan; };
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int&) {
+        return *reinterpret_cast<const volatile int32_t*>(p.found_inf) == 0;     // every rank sees the same word
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int, int64_t) {
+        using ST = typename Elem<S>::type;
+        const int cur = *reinterpret_cast<const volatile int32_t*>(p.parity) & 1;
+        return Ctx{cur ? spec_delta(r.numel, sizeof(ST)) / static_cast<int64_t>(sizeof(ST)) : 0,
+                   reinterpret_cast<char*>(r.ptr[4]), &p.fan};
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+        Raw8<S> in[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) load8<S, true>(r.ptr[1], idx[u] + c.rd, in[u]);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float x[kVec];
+            unpack8<S>(in[u], x);
+            if (c.fan->use_mc) {
+                uint32_t packed[4];
+                pack8_16<C>(x, packed);
+                multimem_st128(c.c + c.fan->copy_mc_delta + idx[u] * 2, packed);
+            } else {
+#pragma unroll
+                for (int w = 0; w < kWorld; w++)
+                    if (w < c.fan->store_world) store8<C>(c.c + c.fan->copy_delta[w], idx[u], x);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        const float x = load1<S>(r.ptr[1], i + c.rd);
+        for (int w = 0; w < c.fan->store_world; w++) store1<C>(c.c + c.fan->copy_delta[w], i, x);
+    }
+    static __device__ __forceinline__ void finish(const Params& p, bool) {
+        if (p.psync.pad[0] != nullptr) publish_done(p.psync, false);
+    }
+};
+
+// waits for every rank's done[] of `epoch` — only when *cond != 0 (the ranks agree on *cond)
+__global__ void peer_wait_done_if_kernel(const __grid_constant__ PeerSync sync, const int32_t* cond) {
+    if (*reinterpret_cast<const volatile int32_t*>(cond) == 0) return;
+    b200_peer_signal_pad* mine = sync.pad[sync.rank];
+    if (threadIdx.x < sync.world) wait_at_least(&mine->done[threadIdx.x], sync.epoch << 1, &mine->error);
+}
+
 // All-gather half as a kernel of its own (used where the averaged gradient must be materialised, i.e.
 // inside apex.parallel.DistributedDataParallel): wait for every rank's shard, OR the overflow bits,
 // then copy each 8-element group from its owner's `reduced` buffer into the local bucket.
@@ -2108,6 +2340,108 @@ static int to_peer_sync(const b200_peer_sync* s, PeerSync& out, const char* name
     out.rank = s->rank;
     out.epoch = s->epoch;
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// sharded step (see ShardStepOp)
+// ------------------------------------------------------------------------------------------------
+static int to_fan(const b200_peer_fan* f, PeerFan& out, const char* name) {
+    if (!f) return set_error(B200_EINVAL, "%s: fan is NULL", name);
+    if (f->world < 1 || f->world > B200_MAX_PEERS || f->rank < 0 || f->rank >= f->world)
+        return set_error(B200_EINVAL, "%s: bad b200_peer_fan (world %d, rank %d)", name, f->world, f->rank);
+    memset(&out, 0, sizeof(out));
+    for (int r = 0; r < f->world; r++) {
+        if (!f->grads[r] || !f->models[r]) return set_error(B200_EINVAL, "%s: buffer of rank %d is NULL", name, r);
+        out.grad_delta[r] = static_cast<const char*>(f->grads[r]) - static_cast<const char*>(f->grads[f->rank]);
+        out.copy_delta[r] = static_cast<const char*>(f->models[r]) - static_cast<const char*>(f->models[f->rank]);
+        if (out.grad_delta[r] % 32 || out.copy_delta[r] % 32)
+            return set_error(B200_EINVAL, "%s: the ranks' buffers must be 32-byte aligned relative to each other", name);
+    }
+    out.world = f->world;
+    out.store_world = f->world;
+    out.factor = f->factor;
+    if (f->grads_mc) {
+        out.grad_mc_delta = static_cast<const char*>(f->grads_mc) - static_cast<const char*>(f->grads[f->rank]);
+        if (out.grad_mc_delta % 32) return set_error(B200_EINVAL, "%s: grads_mc must be 32-byte aligned like the buffers", name);
+        out.use_mc_grad = 1;
+    }
+    if (f->model_mc) {
+        out.copy_mc_delta = static_cast<const char*>(f->model_mc) - static_cast<const char*>(f->models[f->rank]);
+        if (out.copy_mc_delta % 32) return set_error(B200_EINVAL, "%s: model_mc must be 32-byte aligned like the buffers", name);
+        out.use_mc = 1;
+    }
+    // measurement aid (tools/, never set by the package): B200_SHARD_DEBUG bit 0 = store to the local model buffer only,
+    // bit 1 = read every rank's gradient from the local buffer.  Results are then wrong by construction.
+    if (const char* e = std::getenv("B200_SHARD_DEBUG")) {
+        const int dbg = std::atoi(e);
+        if (dbg & 1) {
+            out.store_world = 1;
+            out.copy_delta[0] = 0;
+        }
+        if (dbg & 2)
+            for (int r = 0; r < f->world; r++) out.grad_delta[r] = 0;
+    }
+    return 0;
+}
+
+int32_t b200_peer_shard_step(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                             int32_t copy_dtype, const b200_adam_group* groups, int32_t n_groups, float inv_scale,
+                             const float* dev_inv_scale, int32_t* dev_flag, const int32_t* dev_parity,
+                             const b200_step_sync* sync, const b200_peer_fan* fan, const b200_peer_sync* psync,
+                             void* stream) {
+    if (!dev_parity) return set_error(B200_EINVAL, "peer_shard_step: dev_parity is NULL");
+    ShardStepParams prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = to_fan(fan, prm.fan, "peer_shard_step")) return rc;
+    if (int rc = to_peer_sync(psync, prm.psync, "peer_shard_step")) return rc;
+    if (psync && (psync->world != fan->world || psync->rank != fan->rank))
+        return set_error(B200_EINVAL, "peer_shard_step: fan and psync disagree on world / rank");
+    if (int rc = fill_adam_consts("peer_shard_step", groups, n_groups, prm.grp)) return rc;
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.parity = dev_parity;
+    prm.flag = dev_flag;
+    prm.sync = to_sync(sync);
+    prm.sync.read_only = 1;
+    if (n_tiles <= 0) return set_error(B200_EINVAL, "peer_shard_step: the shard must hold at least one tile");
+    const unsigned cap = static_cast<unsigned>(g_peer_max_ctas.load());
+    const int w = fan->world;
+#define B200_TRY(G_, W_)                                                                                              \
+    if (grad_dtype == G_ && state_dtype == B200_F32 && copy_dtype == G_ && w <= W_)                                    \
+        return launch_tiles<ShardStepOp<G_, B200_F32, G_, W_>>("peer_shard_step", dev_table, n_tiles, prm, stream, cap);
+    B200_TRY(B200_F16, 2)
+    B200_TRY(B200_F16, 4)
+    B200_TRY(B200_F16, 8)
+    B200_TRY(B200_BF16, 2)
+    B200_TRY(B200_BF16, 4)
+    B200_TRY(B200_BF16, 8)
+#undef B200_TRY
+    return set_error(B200_EDTYPE, "peer_shard_step: (grad,state,copy) dtypes (%d,%d,%d) not instantiated (16-bit gradients "
+                     "and model, fp32 state)", grad_dtype, state_dtype, copy_dtype);
+}
+
+int32_t b200_peer_shard_repair(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                               const int32_t* dev_found_inf, const int32_t* dev_parity, const b200_peer_fan* fan,
+                               const b200_peer_sync* psync, void* stream) {
+    if (!dev_found_inf || !dev_parity) return set_error(B200_EINVAL, "peer_shard_repair: NULL argument");
+    ShardRepairParams prm;
+    memset(&prm, 0, sizeof(prm));
+    if (int rc = to_fan(fan, prm.fan, "peer_shard_repair")) return rc;
+    if (int rc = to_peer_sync(psync, prm.psync, "peer_shard_repair")) return rc;
+    prm.found_inf = dev_found_inf;
+    prm.parity = dev_parity;
+    if (n_tiles <= 0) return set_error(B200_EINVAL, "peer_shard_repair: the shard must hold at least one tile");
+    if (state_dtype != B200_F32 || (copy_dtype != B200_F16 && copy_dtype != B200_BF16))
+        return set_error(B200_EDTYPE, "peer_shard_repair: fp32 state and a 16-bit model copy expected");
+    const unsigned cap = static_cast<unsigned>(g_peer_max_ctas.load());
+    int rc = 0;
+    if (copy_dtype == B200_F16)
+        rc = launch_tiles<ShardRepairOp<B200_F32, B200_F16, 8>>("peer_shard_repair", dev_table, n_tiles, prm, stream, cap);
+    else
+        rc = launch_tiles<ShardRepairOp<B200_F32, B200_BF16, 8>>("peer_shard_repair", dev_table, n_tiles, prm, stream, cap);
+    if (rc || !psync) return rc;
+    peer_wait_done_if_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(prm.psync, dev_found_inf);
+    return after_launch("peer_shard_repair(wait)");
 }
 
 int32_t b200_peer_wait_flags(const b200_peer_sync* sync, int32_t* dev_flag, void* stream) {

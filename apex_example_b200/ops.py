@@ -315,6 +315,44 @@ def peer_spec_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, grou
                "peer_spec_step")
 
 
+PeerFan = _lib.PeerFan
+
+
+def make_peer_fan(grad_ptrs, model_ptrs, rank: int, factor: float, model_mc: int | None = None,
+                  grads_mc: int | None = None) -> "PeerFan":
+    """b200_peer_fan: every rank's flat gradient and model-weight buffer as addressable from this process."""
+    fan = PeerFan()
+    for r, (g, m) in enumerate(zip(grad_ptrs, model_ptrs)):
+        fan.grads[r] = g
+        fan.models[r] = m
+    fan.world, fan.rank, fan.factor = len(grad_ptrs), rank, factor
+    fan.model_mc = model_mc or None
+    fan.grads_mc = grads_mc or None
+    return fan
+
+
+def peer_shard_step(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[AdamGroup], dev_parity, fan,
+                    psync=None, dev_flag=None, inv_scale: float = 1.0, dev_inv_scale=None, sync: StepSync | None = None):
+    """Reduce-scatter + speculative Adam on this rank's shard + all-gather of the new weights, one kernel
+    (b200_peer_shard_step).  ``table`` lists the shard only."""
+    _require_cuda(table)
+    arr = (AdamGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_peer_shard_step(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                                dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                                _addr(dev_flag), _addr(dev_parity),
+                                                ctypes.byref(sync) if sync is not None else None, ctypes.byref(fan),
+                                                ctypes.byref(psync) if psync is not None else None, _stream()),
+               "peer_shard_step")
+
+
+def peer_shard_repair(table: TensorTable, state_dtype, copy_dtype, dev_found_inf, dev_parity, fan, psync=None):
+    _require_cuda(table)
+    _lib.check(_lib.load().b200_peer_shard_repair(table.ptr, table.n_tiles, dtype_code(state_dtype), dtype_code(copy_dtype),
+                                                  _addr(dev_found_inf), _addr(dev_parity), ctypes.byref(fan),
+                                                  ctypes.byref(psync) if psync is not None else None, _stream()),
+               "peer_shard_repair")
+
+
 def new_peer_step_scratch(device) -> torch.Tensor:
     return torch.zeros(2048 + 20 * 512, dtype=torch.int32, device=device)     # tickets, chunk counters (+ room for profile builds)
 

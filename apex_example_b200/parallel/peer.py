@@ -42,7 +42,8 @@ class PeerBuffers:
     ``ptrs(name)[r]`` is rank r's buffer as a device address valid in THIS process.
     Call :meth:`close` on every rank before the process group goes away."""
 
-    def __init__(self, numel: int, dtype: torch.dtype, names=("grads", "reduced"), group=None, device=None):
+    def __init__(self, numel: int, dtype: torch.dtype, names=("grads", "reduced"), group=None, device=None,
+                 multicast=()):
         if not dist.is_initialized():
             raise RuntimeError("PeerBuffers needs an initialised process group")
         lib = _lib.load()
@@ -58,9 +59,31 @@ class PeerBuffers:
         nbytes = (numel * esize + 255) // 256 * 256
         self._own, self._opened = {}, []
         handles = {}
+        # buffers named in `multicast` come from torch's symmetric memory, which also binds them to an NVSwitch
+        # multicast object (set-up only: no torch collective runs in the step); mc_ptr(name) is then the address
+        # through which ONE store reaches every rank's buffer.  Anything missing -> plain IPC buffers, mc_ptr = None.
+        self._symm, self._mc, self.multicast_note = {}, {}, None
+        for n in multicast:
+            if n not in self.names:
+                raise RuntimeError(f"multicast buffer {n!r} is not one of {self.names}")
+            try:
+                self._symm[n] = self._symm_alloc(nbytes // esize, dtype, group)
+            except Exception as exc:                      # noqa: BLE001 — every rank must take the same branch below
+                self._symm[n] = None
+                self.multicast_note = f"{type(exc).__name__}: {exc}"[:200]
+        if multicast:
+            ok = torch.tensor([int(all(self._symm[n] is not None and self._symm[n][1].multicast_ptr for n in multicast))],
+                              device=self.device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if not int(ok.item()):
+                if self.multicast_note is None:
+                    self.multicast_note = "no multicast address (has_multicast_support is false on some rank)"
+                self._symm = {}
         with torch.cuda.device(self.device):
             torch.cuda.current_stream().synchronize()
             for n in self.names:
+                if n in self._symm:
+                    continue
                 ptr = ctypes.c_void_p()
                 h = (ctypes.c_ubyte * 64)()
                 _lib.check(lib.b200_peer_alloc(nbytes, ctypes.byref(ptr), h), "peer_alloc")
@@ -70,6 +93,11 @@ class PeerBuffers:
             dist.all_gather_object(gathered, handles, group=group)
             self._ptrs = {}
             for n in self.names:
+                if n in self._symm:
+                    t, hdl = self._symm[n]
+                    self._ptrs[n] = [int(x) for x in hdl.buffer_ptrs]
+                    self._mc[n] = int(hdl.multicast_ptr)
+                    continue
                 row = []
                 for r in range(self.world):
                     if r == self.rank:
@@ -81,14 +109,26 @@ class PeerBuffers:
                     self._opened.append(ptr.value)
                     row.append(ptr.value)
                 self._ptrs[n] = row
-        self.local = {n: _wrap(self._own[n], numel, dtype, self.device) for n in self.names}
+        self.local = {n: (self._symm[n][0][:numel] if n in self._symm else _wrap(self._own[n], numel, dtype, self.device))
+                      for n in self.names}
         self.signal_ptrs = None
         self._bar = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._closed = False
         dist.barrier(group=group)
 
+    def _symm_alloc(self, numel, dtype, group):
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(numel, dtype=dtype, device=self.device)
+        hdl = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+        t.zero_()
+        return t, hdl
+
     def ptrs(self, name):
         return list(self._ptrs[name])
+
+    def mc_ptr(self, name):
+        """Multicast address of buffer ``name`` (None unless it was requested and the fabric provides one)."""
+        return self._mc.get(name) or None
 
     def signal_pads(self, count: int = 1, index: int = 0):
         """Allocate (once) ``count`` 128-byte signal pads per rank and return pad ``index`` of every rank
@@ -150,6 +190,7 @@ class PeerBuffers:
             except Exception:
                 pass
             self.local = {}
+            self._symm, self._mc = {}, {}
             self._signal_view = None
             for p in self._own.values():
                 lib.b200_peer_free(p)
@@ -239,3 +280,106 @@ class PeerSpecStep:
         ops.peer_spec_step(self.table, grad_dtype, state_dtype, copy_dtype, groups, dev_flag, dev_parity, self.pull,
                            self._grad_ptrs, b.local["reduced"], self.factor, psync, self.n_reducers, self.chunk_elems,
                            self.scratch, inv_scale=inv_scale, dev_inv_scale=dev_inv_scale, sync=sync)
+
+
+def even_shards(total: int, world: int, align: int = 1024):
+    """world+1 element offsets splitting [0, total) evenly at multiples of ``align`` (pure host code)."""
+    bounds = [0]
+    for r in range(1, world):
+        b = min(total, (r * total // world + align - 1) // align * align)
+        bounds.append(max(b, bounds[-1]))
+    bounds.append(total)
+    return bounds
+
+
+def shard_segments(offsets, sizes, begin: int, end: int):
+    """The pieces of the tensors (tensor t at flat offset offsets[t], sizes[t] long) that fall inside [begin, end):
+    a list of (tensor index, first element inside the tensor, length, flat offset).  Pure host code."""
+    out = []
+    for t, (o, n) in enumerate(zip(offsets, sizes)):
+        a, b = max(o, begin), min(o + n, end)
+        if a < b:
+            out.append((t, a - o, b - a, a))
+    return out
+
+
+class PeerShardedStep:
+    """ZeRO-1 style data-parallel step as ONE kernel per rank (b200_peer_shard_step): each rank keeps the fp32
+    master / m / v of its shard only, averages every rank's gradients for that shard in rank order, runs the
+    speculative Adam update and stores the new 16-bit weights into EVERY rank's model buffer — gradient reads
+    (NVLink inbound) and weight writes (outbound) overlap, and no tile waits for another.  Followed here by the
+    flag exchange, the commit (loss-scaler update + parity flip) and the repair that re-sends the old weights
+    after an overflow.
+
+    ``buffers`` must have been built with names containing "grads" and "model" (same 16-bit dtype): every rank
+    produces its gradients into ``buffers.local["grads"]`` and reads its weights from ``buffers.local["model"]``
+    (tensor t at element offset offsets[t]).  ``masters``: optional fp32 flat tensor (the whole model) to take
+    the shard's initial master weights from; default = the local model buffer widened to fp32.
+    ``use_multicast``: "none" | "stores" | "reduce" | "both" — which of the two NVSwitch multicast paths to use when
+    the buffers have a multicast address (PeerBuffers(multicast=("grads", "model"))): "stores" sends every 16 bytes
+    of new weights out once (multimem.st), "reduce" sums the gradients inside the switch (multimem.ld_reduce: fp32
+    accumulation, addend order and partial-sum precision unspecified -> the mean may differ from the rank-ordered one by a few
+    16-bit ulps)."""
+
+    def __init__(self, buffers: PeerBuffers, offsets, sizes, group_ids=None, gradient_average: bool = True,
+                 bounds=None, masters: torch.Tensor | None = None, tile_elems: int | None = None, use_multicast="both"):
+        from ..tables import TensorTable
+        if "grads" not in buffers.names or "model" not in buffers.names:
+            raise RuntimeError('PeerShardedStep needs PeerBuffers(names=("grads", "model"))')
+        self.buf = buffers
+        self.bounds = list(bounds) if bounds is not None else even_shards(buffers.numel, buffers.world)
+        assert len(self.bounds) == buffers.world + 1
+        self.begin, self.end = self.bounds[buffers.rank], self.bounds[buffers.rank + 1]
+        if self.end <= self.begin:
+            raise RuntimeError("PeerShardedStep: this rank's shard is empty (fewer elements than ranks x 1024?)")
+        self.segments = shard_segments(offsets, sizes, self.begin, self.end)
+        g, w = buffers.local["grads"], buffers.local["model"]
+        src = masters if masters is not None else w
+        self.state = {"p": [], "m": [], "v": []}
+        gcol, wcol, grp = [], [], []
+        for t, first, n, flat in self.segments:
+            gcol.append(g[flat:flat + n])
+            wcol.append(w[flat:flat + n])
+            init = src[flat:flat + n].to(device=buffers.device, dtype=torch.float32)
+            self.state["p"].append(ops.spec_state_like(init, fill=init))
+            zero = torch.zeros(n, dtype=torch.float32, device=buffers.device)
+            self.state["m"].append(ops.spec_state_like(zero))
+            self.state["v"].append(ops.spec_state_like(zero))
+            grp.append(int(group_ids[t]) if group_ids is not None else 0)
+        self.table = TensorTable([gcol] + [[a for a, _ in self.state[k]] for k in "pmv"] + [wcol], groups=grp,
+                                 tile_elems=tile_elems)
+        self.factor = (1.0 / buffers.world) if gradient_average else 1.0
+        want = {"none": (False, False), "stores": (True, False), "reduce": (False, True), "both": (True, True),
+                True: (True, False), False: (False, False)}[use_multicast]
+        self.multicast_stores = bool(buffers.mc_ptr("model")) and want[0]
+        self.multicast_reduce = bool(buffers.mc_ptr("grads")) and want[1]
+        self.multicast = self.multicast_stores
+        self.fan = ops.make_peer_fan(buffers.ptrs("grads"), buffers.ptrs("model"), buffers.rank, self.factor,
+                                     model_mc=buffers.mc_ptr("model") if self.multicast_stores else None,
+                                     grads_mc=buffers.mc_ptr("grads") if self.multicast_reduce else None)
+        self._pads = buffers.signal_pads()
+        self.parity = torch.zeros(1, dtype=torch.int32, device=buffers.device)
+        self.epoch = 0
+        self.dtype = buffers.dtype
+
+    def current(self, name: str, parity: int):
+        """The current copies of the shard's state ('p', 'm' or 'v'), one tensor per segment."""
+        return [ops.spec_current(a, b, parity) for a, b in self.state[name]]
+
+    def step(self, groups, scaler_state: torch.Tensor, dynamic: bool = True, scale_window: int = 2000,
+             scale_factor: float = 2.0, min_scale: float = 0.0, max_scale: float = 2.0 ** 24, sync=None,
+             ev_after_kernel=None):
+        """One data-parallel step.  ``scaler_state``: the device-side b200_scaler_state words (its inverse scale
+        unscales the gradients, its overflow word collects every rank's flag, the commit updates it)."""
+        b = self.buf
+        self.epoch += 2
+        fs = scaler_state.view(torch.float32)
+        psync = ops.make_peer_sync(self._pads, b.rank, self.epoch)
+        ops.peer_shard_step(self.table, self.dtype, torch.float32, self.dtype, groups, self.parity, self.fan, psync,
+                            dev_inv_scale=fs[ops.IDX_INV_LOSS_SCALE:], sync=sync)
+        if ev_after_kernel is not None:
+            ev_after_kernel.record()
+        ops.peer_wait_flags(psync, scaler_state[ops.IDX_OVERFLOW_ACC:])
+        ops.spec_commit(scaler_state, dynamic, scale_window, scale_factor, min_scale, max_scale, self.parity, sync=sync)
+        ops.peer_shard_repair(self.table, torch.float32, self.dtype, scaler_state[ops.IDX_FOUND_INF:], self.parity, self.fan,
+                              ops.make_peer_sync(self._pads, b.rank, self.epoch + 1))

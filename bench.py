@@ -63,8 +63,13 @@ def workload_sizes(name):
 def config_dict(desc, world, collective="peer", note=None, step_mode="spec"):
     """The `config` object both arms print (the driver compares them)."""
     spec = step_mode == "spec" and (world == 1 or collective == "peer")
+    if step_mode == "sharded" and world == 1:
+        spec = True
     if world == 1:
         coll = "none"
+    elif collective == "peer" and step_mode == "sharded":
+        coll = ("peer-memory: every rank reads all ranks' gradients for ITS shard and writes its shard's new fp16 weights "
+                "into every rank's model buffer, inside the update kernel (ZeRO-1 style sharded optimizer state)")
     elif collective == "peer" and spec:
         coll = "peer-memory reduce-scatter fused with the speculative update in one kernel (chunk-wise progress flags)"
     elif collective == "peer":
@@ -72,7 +77,11 @@ def config_dict(desc, world, collective="peer", note=None, step_mode="spec"):
     else:
         coll = "nccl all-reduce"
     return {"workload": desc, "l2": "inputs larger than L2 (3.5 GB touched per step vs 126 MB L2)",
-            "step": ("speculative single pass (check + unscale + AdamW + fp16 copy into double-buffered state) -> "
+            "step": ("sharded: reduce-scatter + speculative AdamW on the own 1/N shard + all-gather of the fp16 weights in ONE "
+                     "kernel per rank -> flag exchange -> scaler update + commit -> repair-if-skipped (every rank ends the step "
+                     "with the whole updated fp16 model; fp32 master/m/v exist once per job, not once per rank)")
+            if (step_mode == "sharded" and world > 1 and collective == "peer") else
+                    ("speculative single pass (check + unscale + AdamW + fp16 copy into double-buffered state) -> "
                      "scaler update + commit -> repair-if-skipped") if spec else
                     "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
             "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS, "collective": coll, "collective_note": note}
@@ -260,7 +269,22 @@ def parity_block(ctx, sabotage=False):
     wflag = oracle.peer_reduce(host_all, want_mean, 0, n, factor) if world > 1 else oracle.check(host_all[0])
     if world == 1:
         want_mean = host_all[0]
-    if ctx["path"] in ("peer", "peer-spec"):
+    if ctx["path"] == "peer-sharded":
+        # the kernel leaves the mean of this rank's shard in the shard of its own gradient buffer
+        b0, b1 = ctx["bounds"][rank], ctx["bounds"][rank + 1]
+        got = gflat[b0:b1].cpu()
+        exact = bool(torch.equal(got.view(torch.int16), want_mean[b0:b1].view(torch.int16)))
+        res["mean_bit_exact"] = exact
+        step_grad = want_mean
+        if ctx.get("in_switch_sum"):
+            # summed inside the switch: neither the addend order nor the precision of its partial sums is specified
+            # (measured: up to 4 fp16 ulps from the rank-ordered fp32 sum at 4 ranks), so the mean gets the same bound as
+            # the NCCL arm (<= world ulps) and the update is then checked bit for bit on the mean the switch produced
+            res["mean_max_ulp_vs_oracle"] = 0 if exact else _ulp_fp16(got, want_mean[b0:b1])
+            res["mean_ok"] = res["mean_max_ulp_vs_oracle"] <= world
+            step_grad = want_mean.clone()
+            step_grad[b0:b1] = got
+    elif ctx["path"] in ("peer", "peer-spec"):
         b0, b1 = ctx["bounds"][rank], ctx["bounds"][rank + 1]
         got = ctx["pbufs"].local["reduced"][b0:b1].cpu()
         res["mean_bit_exact"] = bool(torch.equal(got.view(torch.int16), want_mean[b0:b1].view(torch.int16)))
@@ -283,8 +307,11 @@ def parity_block(ctx, sabotage=False):
         res["mean_bit_exact"] = True
         step_grad = want_mean
     assert wflag == 0 and found == 0, "parity block: finite gradients flagged as overflow"
-    hg = list(torch.split(step_grad, sizes))
-    hp, hm, hv, hc = before
+    if ctx.get("segments") is not None:
+        hg = [step_grad[f:f + c].clone() for f, c in ctx["segments"]]       # this rank's shard only
+    else:
+        hg = list(torch.split(step_grad, sizes))
+    hp, hm, hv, hc = before[:4]
     oracle.adam_list(hg, hp, hm, hv, hc, inv_scale=1.0 / LOSS_SCALE, step=ctx["step_no"][0], adam_w_mode=True,
                      check_overflow=False, **HYPER)
     ok = True
@@ -296,6 +323,15 @@ def parity_block(ctx, sabotage=False):
                 ok = False
                 break
     res["state_bit_exact"] = ok
+    if ctx["path"] == "peer-sharded":
+        # every rank checked its own shard (state and weights) against the oracle; the whole model buffer must be the
+        # same on every rank, so every rank holds the oracle's weights everywhere
+        digest = torch.tensor([int(cols[4][0].view(torch.int16).to(torch.int64).sum())], device=dev)
+        lo, hi = digest.clone(), digest.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        res["model_identical_on_all_ranks"] = bool(int(lo) == int(hi))
+        res["state_bit_exact"] = ok and res["model_identical_on_all_ranks"]
     del host_all, before, hg
 
     # overflow on the last rank only
@@ -311,7 +347,7 @@ def parity_block(ctx, sabotage=False):
     halved = float(st.view(torch.float32)[ops.IDX_LOSS_SCALE]) == LOSS_SCALE / 2
     res["skip_agreed"] = bool(skipped and untouched and halved)
     del snap
-    mean_good = res["mean_ok"] if ctx["path"] == "nccl" else res["mean_bit_exact"]
+    mean_good = res["mean_ok"] if (ctx["path"] == "nccl" or ctx.get("in_switch_sum")) else res["mean_bit_exact"]
     if ctx["path"] == "peer-spec":
         res["overflow_seen_by"] = "every rank's own update role (it inspects every reduced gradient it pulls)"
     good = res["state_bit_exact"] and res["skip_agreed"] and mean_good
@@ -319,6 +355,10 @@ def parity_block(ctx, sabotage=False):
         t = torch.tensor([1 if good else 0], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         res["all_ranks_ok"] = bool(int(t.item()))
+        if "mean_max_ulp_vs_oracle" in res:                                 # MAX over ranks
+            t = torch.tensor([res["mean_max_ulp_vs_oracle"]], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res["mean_max_ulp_vs_oracle"] = int(t.item())
         for k in ("mean_bit_exact", "state_bit_exact", "skip_agreed"):      # AND over ranks
             t = torch.tensor([1 if res.get(k, True) else 0], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MIN)
@@ -365,10 +405,13 @@ def main():
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--peer-barrier", default="signal", choices=["signal", "nccl"],
                     help="peer path: in-kernel signal-pad hand-shake (default) or two 4-byte NCCL all-reduces")
-    ap.add_argument("--step-mode", default="spec", choices=["spec", "checked"],
+    ap.add_argument("--step-mode", default="spec", choices=["spec", "checked", "sharded"],
                     help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
                          "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
                          "check pass -> scaler update -> update in place")
+    ap.add_argument("--multicast", default="none", choices=["none", "stores", "reduce", "both"],
+                    help="sharded mode: NVSwitch multicast for the weight stores (multimem.st) and / or the gradient sum "
+                         "(multimem.ld_reduce: in-switch, addend order unspecified)")
     ap.add_argument("--reducers", type=int, default=0, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
     ap.add_argument("--chunk-elems", type=int, default=0, help="spec mode, N>1: elements per announced chunk of the fused kernel (0 = default)")
     ap.add_argument("--collective", default="peer", choices=["peer", "nccl"],
@@ -415,6 +458,9 @@ def main():
             peer_note = "peer access not available between all GPUs: fell back to NCCL"
     reducer, bounds = None, None
     spec = args.step_mode == "spec" and (world == 1 or use_peer)
+    sharded = args.step_mode == "sharded" and use_peer
+    if args.step_mode == "sharded" and not sharded:
+        spec = world == 1                          # one rank (or no peer access): the shard is the whole model
     if use_peer:
         from apex_example_b200.parallel.peer import PeerBuffers, PeerGradientReducer
         from apex_example_b200.tables import tile_aligned_shards
@@ -422,9 +468,11 @@ def main():
         for s_ in sizes:
             offs.append(acc)
             acc += s_
-        pbufs = PeerBuffers(n, torch.float16)
+        pbufs = PeerBuffers(n, torch.float16, names=("grads", "model") if sharded else ("grads", "reduced"),
+                            multicast={"none": (), "stores": ("model",), "reduce": ("grads",),
+                                       "both": ("grads", "model")}[args.multicast] if sharded else ())
         bounds, first_tiles = tile_aligned_shards(offs, sizes, n, world, return_first_tiles=True)
-        if not spec:                               # the fused speculative step brings its own hand-shake
+        if not spec and not sharded:               # the fused steps bring their own hand-shake
             reducer = PeerGradientReducer(pbufs, bounds, first_tiles=first_tiles, barrier=args.peer_barrier)
         gflat = pbufs.local["grads"]
     else:
@@ -434,8 +482,26 @@ def main():
         gflat.copy_((torch.randn(n, device=dev, generator=gen) * 1e-3 * LOSS_SCALE).half())
 
     grads = list(torch.split(gflat, sizes))
-    copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
-    if spec:
+    shard_stepper, segs = None, None
+    if sharded:
+        # ZeRO-1 style: the fp16 model lives in a peer-addressable flat buffer (every rank writes its shard's new
+        # weights into every rank's buffer); fp32 master / m / v exist for this rank's shard only
+        from apex_example_b200.parallel.peer import PeerShardedStep
+        wflat = pbufs.local["model"]
+        wflat.copy_((torch.randn(n, device=dev, generator=torch.Generator(device=dev).manual_seed(77)) * 0.02).half())
+        copy = list(torch.split(wflat, sizes))
+        shard_stepper = PeerShardedStep(pbufs, offs, sizes, use_multicast=args.multicast)
+        shard_multicast, shard_mc_note = shard_stepper.multicast_stores, pbufs.multicast_note
+        shard_mc_reduce = shard_stepper.multicast_reduce
+        bounds = shard_stepper.bounds
+        segs = [(flat, cnt) for _, _, cnt, flat in shard_stepper.segments]
+        parity_word = shard_stepper.parity
+        table = shard_stepper.table
+    else:
+        copy = [(torch.randn(s, device=dev, generator=gen) * 0.02).half() for s in sizes]
+    if sharded:
+        pass
+    elif spec:
         # double-buffered state: every p / m / v tensor is followed by its shadow copy (b200_spec_shadow_delta)
         pb = [ops.spec_state_like(c.float(), fill=c.float()) for c in copy]
         mb = [ops.spec_state_like(c.float()) for c in copy]
@@ -446,7 +512,8 @@ def main():
         p = [c.float() for c in copy]
         m = [torch.zeros(s, device=dev) for s in sizes]
         v = [torch.zeros(s, device=dev) for s in sizes]
-    table = TensorTable([grads, p, m, v, copy])
+    if not sharded:
+        table = TensorTable([grads, p, m, v, copy])
     stepper = None
     if spec and use_peer:
         from apex_example_b200.parallel.peer import PeerSpecStep
@@ -454,6 +521,10 @@ def main():
 
     def current_cols():
         """p, m, v, copy as they are current right now (synchronises in spec mode to read the parity)."""
+        if sharded:
+            par = int(parity_word.item())
+            return [shard_stepper.current("p", par), shard_stepper.current("m", par), shard_stepper.current("v", par),
+                    [wflat[f:f + c] for f, c in segs], [wflat]]
         if not spec:
             return [p, m, v, copy]
         par = int(parity_word.item())
@@ -475,6 +546,22 @@ def main():
 
     def step(ev=None, factor_override=None):
         step_no[0] += 1
+        if sharded:
+            # ONE kernel per rank: gradients of all ranks for the own shard -> mean -> speculative AdamW -> new fp16
+            # weights stored into every rank's model buffer; then flag exchange, commit, repair (exits at once)
+            if ev is not None:
+                ev[2].record()
+                ev[3].record()
+                ev[0].record()
+            grp = [ops.AdamGroup(HYPER["lr"], HYPER["beta1"], HYPER["beta2"], HYPER["eps"], HYPER["weight_decay"],
+                                 step_no[0], 1, 1)]
+            if factor_override is not None:
+                keep = shard_stepper.fan.factor
+                shard_stepper.fan.factor = factor_override
+            shard_stepper.step(grp, state, ev_after_kernel=ev[1] if ev is not None else None)
+            if factor_override is not None:
+                shard_stepper.fan.factor = keep
+            return
         if spec:
             # ONE pass: check + unscale + AdamW + copy into the shadow state; commit = scaler update + parity flip;
             # repair exits at once unless the step was skipped
@@ -546,7 +633,8 @@ def main():
     if args.parity:
         ctx = dict(world=world, rank=rank, dev=dev, n=n, sizes=sizes, gflat=gflat, state=state, reducer=reducer,
                    pbufs=pbufs if use_peer else None,
-                   cols=current_cols, path=("peer-spec" if spec else "peer") if use_peer else ("nccl" if world > 1 else ("single-spec" if spec else "single")),
+                   segments=segs, in_switch_sum=bool(sharded and shard_mc_reduce),
+                   cols=current_cols, path=("peer-sharded" if sharded else "peer-spec" if spec else "peer") if use_peer else ("nccl" if world > 1 else ("single-spec" if spec else "single")),
                    bounds=bounds, step=step, step_no=step_no)
         parity = parity_block(ctx, sabotage=args.parity_sabotage)
         step_no[0] -= 1                               # the skipped step did not count
@@ -617,7 +705,24 @@ def main():
             "kernel_ms_avg": adam_avg_ms, "kernel_ms_min": min(adam_ms), "kernel_share_of_step": adam_avg_ms / ms_per_step,
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
     cm = sum(check_ms) / len(check_ms)
-    if spec and world > 1:
+    if sharded:
+        link = 2 * n * (world - 1) // world                 # bytes per GPU and direction
+        hbm = BYTES_PER_PARAM * n // world + 2 * link       # own shard + gradients served to / weights received from peers
+        t = adam_avg_ms * 1e-3
+        roof.update({"kernel": "tile_kernel<ShardStepOp<f16,f32,f16,W>> (b200_peer_shard_step: all ranks' gradients of the own "
+                               "shard -> mean in rank order -> check + unscale + AdamW (speculative) -> fp16 weights stored into "
+                               "every rank's model buffer; one launch, no inter-tile dependency)",
+                     "achieved": hbm / t / 1e9, "frac": hbm / t / 1e9 / peak, "algorithmic_bytes_per_launch": hbm,
+                     "bound_note": "NVLink-bound at N >= 4: per GPU the kernel moves (N-1)/N x 2 B/param in EACH direction",
+                     "nvlink": {"bytes_in_per_gpu": link, "bytes_out_per_gpu": link, "inbound_gbs": link / t / 1e9,
+                                "outbound_gbs": link / t / 1e9, "nvlink_peak_gbs_per_dir": 900.0,
+                                "frac_of_nvlink_peak": link / t / 1e9 / 900.0},
+                     "weights_pushed_by": "multimem.st through the NVSwitch multicast address (one store leaves the GPU per 16 bytes)"
+                     if shard_multicast else "one store per rank", "multicast_note": shard_mc_note,
+                     "gradients_summed_by": "multimem.ld_reduce inside the NVSwitch (fp32 accumulation, one rounding, addend order "
+                     "unspecified)" if shard_mc_reduce else "one load per rank, fp32 sum in rank order (bit-exact vs the oracle)",
+                     "replicated_equivalent_gbs_per_gpu": BYTES_PER_PARAM * n / t / 1e9})
+    elif spec and world > 1:
         roof["kernel"] = ("peer_spec_step_kernel<f16,f32,f16> (b200_peer_spec_step: a few reducer CTAs reduce-scatter this rank's shard "
                           "over NVLink through bulk-copy staged shared memory while all other CTAs run check + unscale + AdamW + "
                           "copy on tiles whose chunk has been announced; one launch)")
@@ -650,7 +755,11 @@ def main():
             pass
 
     extra = {}
-    del table, check_table, grads, p, m, v, copy, buckets
+    del table, check_table, grads, copy, buckets
+    if sharded:
+        del shard_stepper, wflat
+    else:
+        del p, m, v
     if spec:
         del pb, mb, vb
     if use_peer:

@@ -371,6 +371,57 @@ int32_t b200_fused_sgd_peer(const void* dev_table, int64_t n_tiles,
                             const b200_peer_pull* pull, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * S3''' — sharded step: reduce-scatter + speculative Adam on the own shard + all-gather of the
+ * new 16-bit weights, ONE kernel per rank.  (Counterpart in apex: apex.contrib.optimizers.
+ * DistributedFusedAdam — ZeRO-1 style sharding of the optimizer state over the data-parallel ranks; not used
+ * by the reference script, whose ranks keep full replicas, test_apex_distributed_spawn.py:119-122.)
+ *
+ * The table lists ONLY this rank's shard (tensor segments clipped to the shard):
+ *   column 0 = the segment inside this rank's flat gradient buffer   (fan->grads[rank])
+ *   columns 1-3 = fp32 master / m / v of the segment, double-buffered as for b200_fused_adam_spec
+ *   column 4 = the segment inside this rank's flat model-weight buffer (fan->models[rank])
+ * For every element the kernel reads the gradient of EVERY rank at the same offset (fan->grads[r]), forms
+ * the mean exactly like b200_peer_reduce_shard (fp32 sum in rank order, rounded to the gradient type,
+ * times `factor`, rounded), inspects it, writes it back over this rank's own gradient (column 0: after the step
+ * the shard of the local gradient buffer holds the mean), runs the speculative update, and stores the new
+ * weights at the same offset of EVERY rank's model buffer (fan->models[r]).  With `psync`: the kernel first announces /
+ * awaits "gradients in place, model weights no longer read" and its last block publishes done[rank] =
+ * (epoch << 1) | overflow to every pad; then call b200_peer_wait_flags(psync, &state->overflow_acc) and
+ * b200_spec_commit, and b200_peer_shard_repair with epoch + 1 (so `epoch` grows by TWO per step).  Without
+ * `psync` (all buffers on one GPU: tests) the overflow is raised in *dev_flag.
+ * b200_peer_shard_repair exits at once unless *dev_found_inf != 0 (the same on every rank after the
+ * commit); otherwise it re-sends cast(current master) of the shard to every rank and waits until every rank
+ * has done so.  Bounded waits; a rank that never arrives poisons the step (it is skipped).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct b200_peer_fan {
+    const void* grads[B200_MAX_PEERS];      /* rank r's flat gradient buffer as addressable from this process */
+    void*       models[B200_MAX_PEERS];     /* rank r's flat model-weight buffer */
+    int32_t     world, rank;
+    float       factor;                     /* 1/world for the mean, 1 for the sum */
+    int32_t     reserved;
+    void*       model_mc;                   /* optional: MULTICAST address of the model buffers (an NVSwitch multicast
+                                               object every rank's buffer is bound to at the same offset).  With it a
+                                               16-byte group of new weights leaves this GPU ONCE (multimem.st) and the
+                                               switch writes it into every rank's buffer; models[] still serves the
+                                               ragged elements.  NULL: one store per rank.  Only stores use it. */
+    const void* grads_mc;                   /* optional: MULTICAST address of the gradient buffers.  With it a 16-byte group
+                                               of gradients is summed INSIDE the switch (multimem.ld_reduce, fp32
+                                               accumulation, rounded once; the order of the addends is not specified, so
+                                               the mean can differ from the rank-ordered one by a few 16-bit ulps; 4 seen at 4 ranks) and only
+                                               the sum crosses the link.  NULL: one load per rank, rank order, bit-exact. */
+} b200_peer_fan;
+
+int32_t b200_peer_shard_step(const void* dev_table, int64_t n_tiles,
+                             int32_t grad_dtype, int32_t state_dtype, int32_t copy_dtype,
+                             const b200_adam_group* groups, int32_t n_groups,
+                             float inv_scale, const float* dev_inv_scale,
+                             int32_t* dev_flag, const int32_t* dev_parity, const b200_step_sync* sync,
+                             const b200_peer_fan* fan, const b200_peer_sync* psync, void* stream);
+int32_t b200_peer_shard_repair(const void* dev_table, int64_t n_tiles, int32_t state_dtype, int32_t copy_dtype,
+                               const int32_t* dev_found_inf, const int32_t* dev_parity,
+                               const b200_peer_fan* fan, const b200_peer_sync* psync, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * S2'' — per-tensor L2 norms and FusedLAMB.
  * Replaces amp_C.multi_tensor_l2norm(..., per_tensor=True) (apex csrc/multi_tensor_l2norm_kernel.cu)
  * and amp_C.multi_tensor_lamb (apex csrc/multi_tensor_lamb.cu: stage 1 = moments + update,

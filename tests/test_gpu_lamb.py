@@ -166,13 +166,13 @@ def test_fused_lamb_under_amp_o2_trains_and_skips_on_overflow():
     for it in range(30):
         opt.zero_grad()
         loss = torch.nn.functional.cross_entropy(model(x).float(), y)
+        scale_before = opt._amp_stash.scaler.loss_scale()
         if it == 10:
             loss = loss * float("inf")                        # every gradient becomes inf/NaN
         with amp.scale_loss(loss, opt) as scaled:
             scaled.backward()
         if it == 10:
             before = [p.detach().clone() for p in amp.master_params(opt)]
-            scale_before = opt._amp_stash.scaler.loss_scale()
             opt.step()
             for b, p in zip(before, amp.master_params(opt)):
                 assert torch.equal(b, p.detach())

@@ -276,6 +276,98 @@ def _worker_fused(rank, world, port, repeats):
     dist.destroy_process_group()
 
 
+def _worker_sharded(rank, world, port, repeats, multicast):
+    """Real ranks: PeerShardedStep (b200_peer_shard_step + flag exchange + commit + repair) over CUDA-IPC buffers,
+    against the oracle, incl. an overflow on the last rank only (every rank skips, weights repaired everywhere)."""
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from apex_example_b200.parallel.peer import PeerBuffers, PeerShardedStep, shard_segments
+    sizes = [5000, 17, 4096, 70001, 8, 12345, 9000, 1600000]
+    offs, total = _layout(sizes)
+    bufs = PeerBuffers(total, torch.float16, names=("grads", "model"), multicast=("grads", "model") if multicast != "none" else ())
+    if multicast != "none" and rank == 0:
+        print(f"[sharded step, world {world}] multicast address: {bool(bufs.mc_ptr('model'))} ({bufs.multicast_note})", flush=True)
+    S = 256.0
+    gen = torch.Generator().manual_seed(7)
+    hp = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+    hm, hv = [torch.zeros(n) for n in sizes], [torch.zeros(n) for n in sizes]
+    hc = [h.half() for h in hp]
+    flat_p = torch.zeros(total)
+    for o, n, h in zip(offs, sizes, hp):
+        flat_p[o:o + n] = h
+    g_local, w_local = bufs.local["grads"], bufs.local["model"]
+    w_local.copy_(flat_p.half())
+    stepper = PeerShardedStep(bufs, offs, sizes, masters=flat_p, use_multicast=multicast)
+    in_switch = stepper.multicast_reduce
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    ops.scaler_init(state, S)
+
+    def launch(step_no, lr=1e-3, wd=0.01):
+        stepper.step([ops.AdamGroup(lr, 0.9, 0.999, 1e-8, wd, step_no, 1, 1)], state)
+
+    scale, good, par = S, 0, 0
+    for it in range(4):
+        host_all = [(torch.randn(total, generator=torch.Generator().manual_seed(100 * it + r)) * 1e-2 * scale).half()
+                    for r in range(world)]
+        if it == 1:
+            host_all[world - 1][total - 1] = float("inf")          # overflow on the LAST rank only
+        g_local.copy_(host_all[rank])
+        launch(good + 1)
+        torch.cuda.synchronize()
+        dist.barrier()
+        want = torch.zeros(total, dtype=torch.float16)
+        wflag = oracle.peer_reduce(host_all, want, 0, total, 1.0 / world)
+        assert wflag == (1 if it == 1 else 0)
+        assert int(state.cpu()[ops.IDX_FOUND_INF]) == wflag, f"rank {rank}: skip decision at iteration {it}"
+        if not wflag:
+            # every rank left the mean of ITS shard in its own gradient buffer
+            parts = [torch.empty_like(g_local) for _ in range(world)]
+            dist.all_gather(parts, g_local)
+            b = stepper.bounds
+            mean = want.clone()                  # (the alignment gaps between tensors are not part of any shard's table)
+            for r in range(world):
+                for _, _, n, f in shard_segments(offs, sizes, b[r], b[r + 1]):
+                    mean[f:f + n] = parts[r][f:f + n].cpu()
+            if in_switch:       # addend order and partial-sum precision inside the switch are unspecified: <= world ulps
+                ka, kb = (t.view(torch.int16).to(torch.int32) for t in (mean, want))
+                ka, kb = torch.where(ka < 0, -(ka & 0x7fff), ka), torch.where(kb < 0, -(kb & 0x7fff), kb)
+                assert int((ka - kb).abs().max()) <= world, f"rank {rank}: in-switch mean differs by more than {world} ulps"
+            else:
+                assert torch.equal(mean.view(torch.int16), want.view(torch.int16)), f"rank {rank}: mean"
+            good += 1
+            par ^= 1
+            for i, (o, n) in enumerate(zip(offs, sizes)):
+                oracle.adam(mean[o:o + n].clone(), hp[i], hm[i], hv[i], hc[i], lr=1e-3, weight_decay=0.01, step=good,
+                            inv_scale=1.0 / scale)
+        else:
+            scale /= 2
+        assert int(stepper.parity) == par
+        for k, h in (("p", hp), ("m", hm), ("v", hv)):
+            assert_lists_bit_equal(stepper.current(k, par), [h[t][a:a + n] for t, a, n, _ in stepper.segments],
+                                   f"{k} (rank {rank}, it {it})")
+        assert_lists_bit_equal([w_local[o:o + n] for o, n in zip(offs, sizes)], hc, f"model (rank {rank}, it {it})")
+        dist.barrier()
+    for _ in range(repeats):                 # hammer the hand-shake: back-to-back steps, no host sync
+        launch(good + 1, lr=0.0, wd=0.0)
+    torch.cuda.synchronize()
+    bufs.check_signals()
+    del stepper
+    bufs.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("multicast", ["none", "stores", "both"])
+def test_real_rank_sharded_step(world, multicast):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run under gpurun --gpus {world})")
+    mp.spawn(_worker_sharded, args=(world, _free_port(), 100, multicast), nprocs=world, join=True)
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_real_rank_fused_reduce_and_speculative_step(world):
     if torch.cuda.device_count() < world:

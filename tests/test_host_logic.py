@@ -54,3 +54,24 @@ def test_scaler_keep_skip_mode_matches_apex_one_shot_skip_step():
     t = oracle.LossScaler(loss_scale=2.0 ** 16, scale_window=3)
     t.update_scale(True)
     assert t.update_scale(False) is False
+
+
+def test_even_shards_and_shard_segments():
+    from apex_example_b200.parallel.peer import even_shards, shard_segments
+    sizes = [5000, 17, 4096, 70001, 8]
+    offs, o = [], 0
+    for n in sizes:
+        offs.append(o)
+        o += (n + 15) // 16 * 16
+    total = o
+    for world in (1, 2, 3, 8):
+        b = even_shards(total, world)
+        assert b[0] == 0 and b[-1] == total and len(b) == world + 1 and b == sorted(b)
+        assert all(x % 1024 == 0 for x in b[1:-1])
+        covered = [0] * len(sizes)
+        for r in range(world):
+            for t, first, n, flat in shard_segments(offs, sizes, b[r], b[r + 1]):
+                assert flat == offs[t] + first and n > 0 and b[r] <= flat and flat + n <= b[r + 1]
+                covered[t] += n
+        assert covered == sizes                                       # every element belongs to exactly one rank
+    assert even_shards(100, 4) == [0, 100, 100, 100, 100]             # tiny buffers: trailing shards are empty
