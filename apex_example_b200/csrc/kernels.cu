@@ -2405,7 +2405,9 @@ int32_t b200_peer_shard_step(const void* dev_table, int64_t n_tiles, int32_t gra
     prm.sync.read_only = 1;
     if (n_tiles <= 0) return set_error(B200_EINVAL, "peer_shard_step: the shard must hold at least one tile");
     const unsigned cap = static_cast<unsigned>(g_peer_max_ctas.load());
-    const int w = fan->world;
+    // with both multicast paths on, a thread issues ONE load and ONE store per group whatever the rank count: the
+    // 2-rank instantiation (fewest registers, 2 CTAs/SM) serves every world size (ragged elements loop over `world`)
+    const int w = (prm.fan.use_mc && prm.fan.use_mc_grad) ? 2 : fan->world;
 #define B200_TRY(G_, W_)                                                                                              \
     if (grad_dtype == G_ && state_dtype == B200_F32 && copy_dtype == G_ && w <= W_)                                    \
         return launch_tiles<ShardStepOp<G_, B200_F32, G_, W_>>("peer_shard_step", dev_table, n_tiles, prm, stream, cap);

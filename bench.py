@@ -405,11 +405,11 @@ def main():
     ap.add_argument("--ctas-per-sm", type=int, default=0)
     ap.add_argument("--peer-barrier", default="signal", choices=["signal", "nccl"],
                     help="peer path: in-kernel signal-pad hand-shake (default) or two 4-byte NCCL all-reduces")
-    ap.add_argument("--step-mode", default="spec", choices=["spec", "checked", "sharded"],
+    ap.add_argument("--step-mode", default="auto", choices=["auto", "spec", "checked", "sharded"],
                     help="'spec' (N = 1): speculative single pass — the overflow check rides on the update, p/m/v are "
                          "double-buffered (+12 B/param resident), commit flips a device-side parity; 'checked': "
                          "check pass -> scaler update -> update in place")
-    ap.add_argument("--multicast", default="none", choices=["none", "stores", "reduce", "both"],
+    ap.add_argument("--multicast", default="auto", choices=["auto", "none", "stores", "reduce", "both"],
                     help="sharded mode: NVSwitch multicast for the weight stores (multimem.st) and / or the gradient sum "
                          "(multimem.ld_reduce: in-switch, addend order unspecified)")
     ap.add_argument("--reducers", type=int, default=0, help="spec mode, N>1: CTAs of the fused kernel that take the reduce role")
@@ -419,6 +419,14 @@ def main():
                          "'nccl' = ncclAllReduce per bucket + epilogue kernel")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    n_ranks = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.step_mode == "auto":
+        # N = 1: speculative single pass.  N > 1 over peer memory: the sharded step (fastest at every N measured,
+        # profiles/r02_summary.md); `--step-mode spec` keeps the replicated-state fused step of §6a.
+        args.step_mode = "sharded" if (n_ranks > 1 and args.collective == "peer") else "spec"
+    if args.multicast == "auto":
+        # the multicast paths pay from 4 ranks on (at 2 ranks the echo of the own stores costs more than it saves)
+        args.multicast = "both" if n_ranks >= 4 else "none"
     sizes, desc = workload_sizes(args.workload)
     if args.impl == "reference":
         return reference_arm(args, sizes, desc)
@@ -706,22 +714,31 @@ def main():
             "algorithmic_bytes_per_launch": BYTES_PER_PARAM * n, "traffic": None}
     cm = sum(check_ms) / len(check_ms)
     if sharded:
-        link = 2 * n * (world - 1) // world                 # bytes per GPU and direction
-        hbm = BYTES_PER_PARAM * n // world + 2 * link       # own shard + gradients served to / weights received from peers
+        per = 2 * n // world                                # bytes of one shard of fp16 gradients / weights
+        # NVLink bytes per GPU: gradients in + weights in; gradients out + weights out
+        g_in = per if shard_mc_reduce else per * (world - 1)        # in-switch sum: only the sum comes in
+        g_out = per * world if shard_mc_reduce else per * (world - 1)   # ... but every GPU's whole buffer feeds the switch
+        w_out = per if shard_multicast else per * (world - 1)       # multicast store: leaves once
+        w_in = per * world if shard_multicast else per * (world - 1)    # ... and the sender receives its own echo
+        link_in, link_out = g_in + w_in, g_out + w_out
+        hbm = BYTES_PER_PARAM * n // world + g_out + w_in    # own shard + gradients served + weights received
         t = adam_avg_ms * 1e-3
         roof.update({"kernel": "tile_kernel<ShardStepOp<f16,f32,f16,W>> (b200_peer_shard_step: all ranks' gradients of the own "
-                               "shard -> mean in rank order -> check + unscale + AdamW (speculative) -> fp16 weights stored into "
+                               "shard -> mean -> check + unscale + AdamW (speculative) -> fp16 weights stored into "
                                "every rank's model buffer; one launch, no inter-tile dependency)",
                      "achieved": hbm / t / 1e9, "frac": hbm / t / 1e9 / peak, "algorithmic_bytes_per_launch": hbm,
-                     "bound_note": "NVLink-bound at N >= 4: per GPU the kernel moves (N-1)/N x 2 B/param in EACH direction",
-                     "nvlink": {"bytes_in_per_gpu": link, "bytes_out_per_gpu": link, "inbound_gbs": link / t / 1e9,
-                                "outbound_gbs": link / t / 1e9, "nvlink_peak_gbs_per_dir": 900.0,
-                                "frac_of_nvlink_peak": link / t / 1e9 / 900.0},
+                     "limiter": "NVLink, not HBM: per GPU the kernel receives and sends the bytes in `nvlink` while it touches "
+                                "only 1/N of the optimizer state; NCCL's best all-reduce bus bandwidth on this box is in `allreduce`",
+                     "nvlink": {"bytes_in_per_gpu": link_in, "bytes_out_per_gpu": link_out, "inbound_gbs": link_in / t / 1e9,
+                                "outbound_gbs": link_out / t / 1e9, "nvlink_peak_gbs_per_dir": 900.0,
+                                "frac_of_nvlink_peak": max(link_in, link_out) / t / 1e9 / 900.0},
                      "weights_pushed_by": "multimem.st through the NVSwitch multicast address (one store leaves the GPU per 16 bytes)"
                      if shard_multicast else "one store per rank", "multicast_note": shard_mc_note,
                      "gradients_summed_by": "multimem.ld_reduce inside the NVSwitch (fp32 accumulation, one rounding, addend order "
                      "unspecified)" if shard_mc_reduce else "one load per rank, fp32 sum in rank order (bit-exact vs the oracle)",
-                     "replicated_equivalent_gbs_per_gpu": BYTES_PER_PARAM * n / t / 1e9})
+                     "replicated_equivalent_gbs_per_gpu": BYTES_PER_PARAM * n / t / 1e9,
+                     "value_note": "`value` counts 28 B/param x N: the bytes a replicated-state step of the same N-rank job "
+                                   "moves (the unit the N = 1 line is quoted in); this step moves fewer (see hbm / nvlink)"})
     elif spec and world > 1:
         roof["kernel"] = ("peer_spec_step_kernel<f16,f32,f16> (b200_peer_spec_step: a few reducer CTAs reduce-scatter this rank's shard "
                           "over NVLink through bulk-copy staged shared memory while all other CTAs run check + unscale + AdamW + "
