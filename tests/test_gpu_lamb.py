@@ -166,7 +166,7 @@ def test_fused_lamb_under_amp_o2_trains_and_skips_on_overflow():
     for it in range(30):
         opt.zero_grad()
         loss = torch.nn.functional.cross_entropy(model(x).float(), y)
-        scale_before = opt._amp_stash.scaler.loss_scale()
+        scale_before = amp._amp_state.loss_scalers[0].loss_scale()
         if it == 10:
             loss = loss * float("inf")                        # every gradient becomes inf/NaN
         with amp.scale_loss(loss, opt) as scaled:
@@ -177,7 +177,7 @@ def test_fused_lamb_under_amp_o2_trains_and_skips_on_overflow():
             for b, p in zip(before, amp.master_params(opt)):
                 assert torch.equal(b, p.detach())
             assert opt.param_groups[0]["step"] == 10           # the skipped step did not count
-            assert opt._amp_stash.scaler.loss_scale() < scale_before or scale_before == 1.0
+            assert amp._amp_state.loss_scalers[0].loss_scale() < scale_before or scale_before == 1.0
             continue
         opt.step()
         losses.append(loss.item())
