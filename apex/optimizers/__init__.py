@@ -1,1 +1,1 @@
-from apex_example_b200.optimizers import FusedAdam, FusedLAMB, FusedSGD  # noqa: F401
+from apex_example_b200.optimizers import FusedAdam, FusedLAMB, FusedNovoGrad, FusedSGD  # noqa: F401

@@ -32,6 +32,12 @@ class LambGroup(ctypes.Structure):           # b200_lamb_group
                 ("adam_w_mode", c_int32), ("grad_averaging", c_int32), ("use_nvlamb", c_int32)]
 
 
+class NovoGradGroup(ctypes.Structure):       # b200_novograd_group
+    _fields_ = [("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
+                ("weight_decay", c_double), ("step", c_int64), ("bias_correction", c_int32),
+                ("reg_inside_moment", c_int32), ("grad_averaging", c_int32), ("init_zero", c_int32)]
+
+
 class SgdGroup(ctypes.Structure):            # b200_sgd_group
     _fields_ = [("lr", c_double), ("momentum", c_double), ("dampening", c_double),
                 ("weight_decay", c_double), ("step", c_int64), ("nesterov", c_int32),
@@ -108,6 +114,10 @@ SIGNATURES = {
                                    c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
     "b200_lamb_stage2": (c_int32, [c_void_p, c_int64, c_int32, c_int32, ctypes.POINTER(LambGroup), c_int32, c_void_p,
                                    c_void_p, c_void_p, c_void_p]),
+    "b200_novograd_blend": (c_int32, [c_void_p, c_int32, ctypes.POINTER(NovoGradGroup), c_int32, c_float, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p]),
+    "b200_fused_novograd": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(NovoGradGroup), c_int32,
+                                      c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b200_clip_scale": (c_int32, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "b200_fused_adam": (c_int32, [c_void_p, c_int64, c_int32, c_int32, c_int32, ctypes.POINTER(AdamGroup),
                                   c_int32, c_float, c_void_p, c_void_p, ctypes.POINTER(StepSync), c_void_p]),

@@ -572,6 +572,109 @@ struct Lamb2Op {
 };
 
 // ============================================================================================
+// NovoGrad: layer-wise second moments (one float per tensor) + momentum update
+// ============================================================================================
+struct NovoConsts {
+    float b1, b3, b2, one_m_b2, bc1, bc2, eps, decay, lr;
+    uint32_t flags;                 // bit0: regularise inside the moment (apex MOMENT_MODE_0), bit1: first step and !init_zero
+};
+
+struct NovoParams {
+    NovoConsts grp[B200_MAX_GROUPS];
+    float inv_scale;
+    const float* dev_inv_scale;
+    const int32_t* dev_found_inf;
+    const float* v;                 // per tensor (row index): the blended gradient norm of this step
+};
+
+// v[t] <- sqrt(b2 * v[t]^2 + (1 - b2) * n^2), n = sqrt(sumsq[t]) * inv_scale (norm of the unscaled gradient of tensor t);
+// on the first step (unless init_zero) v[t] starts from n.  One thread per tensor.
+__global__ void novograd_blend_kernel(const void* __restrict__ table, const __grid_constant__ NovoParams prm,
+                                      float* __restrict__ v, const float* __restrict__ grad_sumsq) {
+    if (prm.dev_found_inf != nullptr && *reinterpret_cast<const volatile int32_t*>(prm.dev_found_inf) != 0) return;
+    const TableView tv = open_table(table);
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= reinterpret_cast<const b200_table_header*>(table)->n_tensors) return;
+    const NovoConsts& k = prm.grp[tv.rows[t].group];
+    const float s = prm.dev_inv_scale ? __ldg(prm.dev_inv_scale) : prm.inv_scale;
+    const float n = __fmul_rn(__fsqrt_rn(grad_sumsq[t]), s);
+    float old = (k.flags & 2u) ? n : v[t];
+    const float a = __fmul_rn(k.b2, __fmul_rn(old, old));
+    const float b = __fmul_rn(k.one_m_b2, __fmul_rn(n, n));
+    v[t] = __fsqrt_rn(__fadd_rn(a, b));
+}
+
+// columns: 0 g, 1 p, 2 m, 3 model copy (optional)
+template <int G, int S, int C>
+struct NovoGradOp {
+    using Params = NovoParams;
+    static constexpr int kUnrollMul = 1;
+    struct Ctx { NovoConsts k; float s, denom; };
+    static constexpr int kCopyCol = 3;
+    static __device__ __forceinline__ uint32_t rotation(const Params&) { return 0u; }
+    static __device__ __forceinline__ bool prologue(const Params& p, int&) {
+        return p.dev_found_inf != nullptr && *reinterpret_cast<const volatile int32_t*>(p.dev_found_inf) != 0;
+    }
+    static __device__ __forceinline__ Ctx make_ctx(const Params& p, const b200_table_row& r, int, int64_t) {
+        const NovoConsts& k = p.grp[r.group];
+        const float s = p.dev_inv_scale ? __ldg(p.dev_inv_scale) : p.inv_scale;
+        return Ctx{k, s, __fadd_rn(__fdiv_rn(__ldg(p.v + r.reserved), k.bc2), k.eps)};
+    }
+    static __device__ __forceinline__ void one(float g_in, float& p, float& m, const Ctx& c) {
+        float g = __fmul_rn(g_in, c.s);
+        if (c.k.flags & 1u) {
+            g = __fadd_rn(__fdiv_rn(g, c.denom), __fmul_rn(c.k.decay, p));
+            m = __fadd_rn(__fmul_rn(c.k.b1, m), __fmul_rn(c.k.b3, g));
+            p = __fsub_rn(p, __fmul_rn(c.k.lr, __fdiv_rn(m, c.k.bc1)));
+        } else {
+            m = __fadd_rn(__fmul_rn(c.k.b1, m), __fmul_rn(c.k.b3, g));
+            const float u = __fadd_rn(__fdiv_rn(__fdiv_rn(m, c.k.bc1), c.denom), __fmul_rn(c.k.decay, p));
+            p = __fsub_rn(p, __fmul_rn(c.k.lr, u));
+        }
+    }
+    template <int U>
+    static __device__ __forceinline__ void vec(const b200_table_row& r, const Ctx& c, const int64_t (&idx)[U],
+                                               const bool (&act)[U], bool&) {
+        Raw8<G> rg[U];
+        Raw8<S> rp[U], rm[U];
+#pragma unroll
+        for (int u = 0; u < U; u++)
+            if (act[u]) {
+                load8<G, true>(r.ptr[0], idx[u], rg[u]);
+                load8<S, false>(r.ptr[1], idx[u], rp[u]);
+                load8<S, false>(r.ptr[2], idx[u], rm[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!act[u]) continue;
+            float g[kVec], p[kVec], m[kVec];
+            unpack8<G>(rg[u], g);
+            unpack8<S>(rp[u], p);
+            unpack8<S>(rm[u], m);
+#pragma unroll
+            for (int i = 0; i < kVec; i++) one(g[i], p[i], m[i], c);
+            store8<S>(r.ptr[1], idx[u], p);
+            store8<S>(r.ptr[2], idx[u], m);
+            if constexpr (C != B200_NONE) {
+                if constexpr (S != B200_F32) {
+#pragma unroll
+                    for (int i = 0; i < kVec; i++) p[i] = round_through<S>(p[i]);
+                }
+                store8<C>(r.ptr[kCopyCol], idx[u], p);
+            }
+        }
+    }
+    static __device__ __forceinline__ void scalar(const b200_table_row& r, const Ctx& c, int64_t i, bool&) {
+        float p = load1<S>(r.ptr[1], i), m = load1<S>(r.ptr[2], i);
+        one(load1<G>(r.ptr[0], i), p, m, c);
+        store1<S>(r.ptr[1], i, p);
+        store1<S>(r.ptr[2], i, m);
+        if constexpr (C != B200_NONE) store1<C>(r.ptr[kCopyCol], i, round_through<S>(p));
+    }
+    static __device__ __forceinline__ void finish(const Params&, bool) {}
+};
+
+// ============================================================================================
 // fused unscale + Adam + master->model copy
 // ============================================================================================
 struct AdamConsts {
@@ -2200,6 +2303,57 @@ int32_t b200_lamb_stage2(const void* dev_table, int64_t n_tiles, int32_t state_d
     B200_TRY(B200_BF16, B200_NONE)
 #undef B200_TRY
     return set_error(B200_EDTYPE, "lamb_stage2: (state,copy) dtypes (%d,%d) not instantiated", state_dtype, copy_dtype);
+}
+
+// ------------------------------------------------------------------------------------------------
+// NovoGrad
+// ------------------------------------------------------------------------------------------------
+static int fill_novo(const char* name, const b200_novograd_group* groups, int32_t n_groups, float inv_scale,
+                     const float* dev_inv_scale, const int32_t* dev_found_inf, const float* dev_v, NovoParams& prm) {
+    memset(&prm, 0, sizeof(prm));
+    if (!groups || n_groups < 1 || n_groups > B200_MAX_GROUPS)
+        return set_error(B200_EINVAL, "%s: n_groups must be 1..%d", name, B200_MAX_GROUPS);
+    if (!dev_v) return set_error(B200_EINVAL, "%s: dev_v is NULL", name);
+    for (int i = 0; i < n_groups; i++) {
+        const b200_novograd_group& h = groups[i];
+        if (h.step < 1) return set_error(B200_EINVAL, "%s: step must be >= 1", name);
+        NovoConsts& k = prm.grp[i];
+        k.b1 = static_cast<float>(h.beta1);
+        k.b3 = h.grad_averaging ? static_cast<float>(1.0 - h.beta1) : 1.0f;
+        k.b2 = static_cast<float>(h.beta2);
+        k.one_m_b2 = static_cast<float>(1.0 - h.beta2);
+        k.bc1 = h.bias_correction ? static_cast<float>(1.0 - std::pow(h.beta1, static_cast<double>(h.step))) : 1.0f;
+        k.bc2 = h.bias_correction ? static_cast<float>(std::sqrt(1.0 - std::pow(h.beta2, static_cast<double>(h.step)))) : 1.0f;
+        k.eps = static_cast<float>(h.eps);
+        k.decay = static_cast<float>(h.weight_decay);
+        k.lr = static_cast<float>(h.lr);
+        k.flags = (h.reg_inside_moment ? 1u : 0u) | ((h.step == 1 && !h.init_zero) ? 2u : 0u);
+    }
+    prm.inv_scale = inv_scale;
+    prm.dev_inv_scale = dev_inv_scale;
+    prm.dev_found_inf = dev_found_inf;
+    prm.v = dev_v;
+    return 0;
+}
+
+int32_t b200_novograd_blend(const void* dev_table, int32_t n_tensors, const b200_novograd_group* groups, int32_t n_groups,
+                            float inv_scale, const float* dev_inv_scale, const int32_t* dev_found_inf, float* dev_v,
+                            const float* dev_grad_sumsq, void* stream) {
+    if (n_tensors <= 0) return 0;
+    if (!dev_table || !dev_grad_sumsq) return set_error(B200_EINVAL, "novograd_blend: NULL argument");
+    NovoParams prm;
+    if (int rc = fill_novo("novograd_blend", groups, n_groups, inv_scale, dev_inv_scale, dev_found_inf, dev_v, prm)) return rc;
+    novograd_blend_kernel<<<(n_tensors + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(dev_table, prm, dev_v,
+                                                                                                 dev_grad_sumsq);
+    return after_launch("novograd_blend");
+}
+
+int32_t b200_fused_novograd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                            int32_t copy_dtype, const b200_novograd_group* groups, int32_t n_groups, float inv_scale,
+                            const float* dev_inv_scale, const int32_t* dev_found_inf, const float* dev_v, void* stream) {
+    NovoParams prm;
+    if (int rc = fill_novo("fused_novograd", groups, n_groups, inv_scale, dev_inv_scale, dev_found_inf, dev_v, prm)) return rc;
+    return dispatch_step<NovoGradOp>("fused_novograd", grad_dtype, state_dtype, copy_dtype, dev_table, n_tiles, prm, stream);
 }
 
 // ------------------------------------------------------------------------------------------------

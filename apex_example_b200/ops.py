@@ -224,6 +224,28 @@ def lamb_stage2(table: TensorTable, state_dtype, copy_dtype, groups: Sequence[La
                                             _stream()), "lamb_stage2")
 
 
+NovoGradGroup = _lib.NovoGradGroup
+
+
+def novograd_blend(table: TensorTable, groups: Sequence[NovoGradGroup], v: torch.Tensor, grad_sumsq: torch.Tensor,
+                   inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+    """v[t] <- blend(v[t], norm of the unscaled gradient of tensor t); see b200_novograd_blend."""
+    _require_cuda(table)
+    arr = (NovoGradGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_novograd_blend(table.ptr, table.n_tensors, arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                               _addr(dev_found_inf), v.data_ptr(), grad_sumsq.data_ptr(), _stream()),
+               "novograd_blend")
+
+
+def fused_novograd(table: TensorTable, grad_dtype, state_dtype, copy_dtype, groups: Sequence[NovoGradGroup], v: torch.Tensor,
+                   inv_scale: float = 1.0, dev_inv_scale=None, dev_found_inf=None):
+    _require_cuda(table)
+    arr = (NovoGradGroup * len(groups))(*groups)
+    _lib.check(_lib.load().b200_fused_novograd(table.ptr, table.n_tiles, dtype_code(grad_dtype), dtype_code(state_dtype),
+                                               dtype_code(copy_dtype), arr, len(groups), inv_scale, _addr(dev_inv_scale),
+                                               _addr(dev_found_inf), v.data_ptr(), _stream()), "fused_novograd")
+
+
 def new_norm_scratch(device) -> torch.Tensor:
     return torch.zeros(_lib.NORM_SCRATCH_BYTES // 4, dtype=torch.float32, device=device)
 

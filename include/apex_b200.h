@@ -467,6 +467,31 @@ int32_t b200_lamb_stage2(const void* dev_table, int64_t n_tiles, int32_t state_d
                          const b200_lamb_group* groups, int32_t n_groups, const int32_t* dev_found_inf,
                          const float* dev_p_norm, const float* dev_u_norm, void* stream);
 
+/* NovoGrad (amp_C.multi_tensor_novograd as apex.optimizers.FusedNovoGrad calls it; apex is not vendored in the
+ * reference: parity UNPINNED, rule restated in oracle/amp_step_oracle.c).  The second moment is ONE float per tensor:
+ *   b200_novograd_blend:  n = sqrt(grad_sumsq[t]) * inv_scale;  v[t] = sqrt(b2 * v[t]^2 + (1-b2) * n^2), with v[t] starting
+ *                         from n on step 1 unless init_zero  (grad_sumsq from b200_l2norm_per_tensor, indexed by row)
+ *   b200_fused_novograd, columns 0 g, 1 p, 2 m, 3 model copy (optional):  denom = v[t]/bc2 + eps, bc2 = sqrt(1 - b2^step)
+ *     reg_inside_moment:  g' = g/denom + wd*p;  m = b1*m + b3*g';  p -= lr * m/bc1
+ *     otherwise (default): m = b1*m + b3*g;  p -= lr * ((m/bc1)/denom + wd*p)          b3 = grad_averaging ? 1-b1 : 1
+ * Both skip when *dev_found_inf != 0. */
+typedef struct b200_novograd_group {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;
+    int32_t bias_correction;
+    int32_t reg_inside_moment;
+    int32_t grad_averaging;
+    int32_t init_zero;
+} b200_novograd_group;
+
+int32_t b200_novograd_blend(const void* dev_table, int32_t n_tensors, const b200_novograd_group* groups, int32_t n_groups,
+                            float inv_scale, const float* dev_inv_scale, const int32_t* dev_found_inf,
+                            float* dev_v, const float* dev_grad_sumsq, void* stream);
+int32_t b200_fused_novograd(const void* dev_table, int64_t n_tiles, int32_t grad_dtype, int32_t state_dtype,
+                            int32_t copy_dtype, const b200_novograd_group* groups, int32_t n_groups,
+                            float inv_scale, const float* dev_inv_scale, const int32_t* dev_found_inf,
+                            const float* dev_v, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * S2' — speculative single-pass step: the overflow check rides on the update pass.
  * (No counterpart in apex, whose unscale pass inspects every gradient before multi_tensor_adam

@@ -55,6 +55,14 @@ class _LambGroup(ctypes.Structure):
                 ("use_nvlamb", ctypes.c_int32)]
 
 
+class _NovoGroup(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double), ("weight_decay", ctypes.c_double),
+                ("step", ctypes.c_int64), ("bias_correction", ctypes.c_int32),
+                ("reg_inside_moment", ctypes.c_int32), ("grad_averaging", ctypes.c_int32),
+                ("init_zero", ctypes.c_int32)]
+
+
 class _SgdGroup(ctypes.Structure):
     _fields_ = [("lr", ctypes.c_double), ("momentum", ctypes.c_double),
                 ("dampening", ctypes.c_double), ("weight_decay", ctypes.c_double),
@@ -241,6 +249,22 @@ def lamb_list(gs, ps, ms, vs, copies=None, *, tile_elems: int, grad_sumsq: float
                            _dt(ps[0]), _ptr_array(copies) if copies else None, _dt(copies[0]) if copies else F32,
                            _ptr_array(us), numel, ctypes.c_int(tile_elems), ctypes.byref(grp),
                            ctypes.c_float(inv_scale), ctypes.c_float(grad_sumsq), ctypes.c_float(max_grad_norm))
+
+
+def novograd_list(gs, ps, ms, v, grad_sumsq, copies=None, *, inv_scale=1.0, **hyper) -> None:
+    """One NovoGrad step over a list with one hyper-parameter group.  ``v``: float32 tensor, one entry per tensor
+    (updated in place); ``grad_sumsq``: per-tensor sums of squares of the still scaled gradients."""
+    grp = _NovoGroup(hyper.get("lr", 1e-3), hyper.get("beta1", 0.9), hyper.get("beta2", 0.999),
+                     hyper.get("eps", 1e-8), hyper.get("weight_decay", 0.0), hyper.get("step", 1),
+                     int(hyper.get("bias_correction", True)), int(hyper.get("reg_inside_moment", False)),
+                     int(hyper.get("grad_averaging", True)), int(hyper.get("init_zero", False)))
+    n = len(gs)
+    numel = (ctypes.c_int64 * n)(*[t.numel() for t in ps])
+    assert v.dtype == torch.float32 and grad_sumsq.dtype == torch.float32 and v.numel() >= n
+    lib().oracle_novograd_list(ctypes.c_int(n), _ptr_array(gs), _dt(gs[0]), _ptr_array(ps), _ptr_array(ms), _dt(ps[0]),
+                               _ptr_array(copies) if copies else None, _dt(copies[0]) if copies else F32,
+                               ctypes.c_void_p(v.data_ptr()), ctypes.c_void_p(grad_sumsq.data_ptr()), numel,
+                               ctypes.byref(grp), ctypes.c_float(inv_scale))
 
 
 # ------------------------------------------------------------------- torch-op restatement (pin)

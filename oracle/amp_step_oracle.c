@@ -539,3 +539,51 @@ void oracle_lamb_list(int n_tensors, const void* const* g, int g_dt, void* const
     free(pn);
     free(un);
 }
+
+/* ---- NovoGrad ------------------------------------------------------------
+ * PARITY UNPINNED against apex (not vendored, cannot be built here).  Restates NovoGrad (Ginsburg et al. 2019,
+ * "Stochastic Gradient Methods with Layer-wise Adaptive Moments") with the conventions apex.optimizers.FusedNovoGrad
+ * documents: the second moment is one number per tensor, kept as a NORM and blended as sqrt(b2 v^2 + (1-b2) n^2) with
+ * n = ||g||_2 (norm_type 2); on the first step it starts from n unless init_zero; bias corrections 1-b1^t and
+ * sqrt(1-b2^t); weight decay inside the moment (reg_inside_moment) or on the update (default). */
+typedef struct {
+    double  lr, beta1, beta2, eps, weight_decay;
+    int64_t step;
+    int32_t bias_correction;
+    int32_t reg_inside_moment;
+    int32_t grad_averaging;
+    int32_t init_zero;
+} oracle_novograd_group;
+
+/* v: one float per tensor (state).  grad_sumsq[t]: sum of squares of the still scaled gradient of tensor t. */
+void oracle_novograd_list(int n_tensors, const void* const* g, int g_dt, void* const* p, void* const* m, int s_dt,
+                          void* const* copy, int c_dt, float* v, const float* grad_sumsq, const int64_t* numel,
+                          const oracle_novograd_group* grp, float inv_scale) {
+    const float b1 = (float)grp->beta1, b2 = (float)grp->beta2, one_m_b2 = (float)(1.0 - grp->beta2);
+    const float b3 = grp->grad_averaging ? (float)(1.0 - grp->beta1) : 1.0f;
+    const float bc1 = grp->bias_correction ? (float)(1.0 - pow(grp->beta1, (double)grp->step)) : 1.0f;
+    const float bc2 = grp->bias_correction ? (float)sqrt(1.0 - pow(grp->beta2, (double)grp->step)) : 1.0f;
+    const float eps = (float)grp->eps, wd = (float)grp->weight_decay, lr = (float)grp->lr;
+    const int first = grp->step == 1 && !grp->init_zero;
+    for (int t = 0; t < n_tensors; t++) {
+        const float n = sqrtf(grad_sumsq[t]) * inv_scale;
+        const float old = first ? n : v[t];
+        { float a = old * old; a = b2 * a; float b = n * n; b = one_m_b2 * b; v[t] = sqrtf(a + b); }
+        const float denom = v[t] / bc2 + eps;
+        for (int64_t i = 0; i < numel[t]; i++) {
+            float gi = load_as_float(g[t], g_dt, i) * inv_scale;
+            float pi = load_as_float(p[t], s_dt, i), mi = load_as_float(m[t], s_dt, i);
+            if (grp->reg_inside_moment) {
+                { float a = gi / denom, b = wd * pi; gi = a + b; }
+                { float a = b1 * mi, b = b3 * gi; mi = a + b; }
+                { float a = mi / bc1; a = lr * a; pi = pi - a; }
+            } else {
+                { float a = b1 * mi, b = b3 * gi; mi = a + b; }
+                { float a = mi / bc1; a = a / denom; float b = wd * pi; a = a + b; a = lr * a; pi = pi - a; }
+            }
+            store_from_float(p[t], s_dt, i, pi);
+            store_from_float(m[t], s_dt, i, mi);
+            if (copy) store_from_float(copy[t], c_dt, i, s_dt == DT_F32 ? pi : load_as_float(p[t], s_dt, i));
+        }
+    }
+}

@@ -308,3 +308,31 @@ def test_l2norm_oracle_flags_non_finite_values():
     xs = [torch.ones(10), torch.tensor([1.0, float("inf")])]
     _, _, flag = oracle.l2norm_per_tensor(xs, 4096)
     assert flag == 1
+
+
+def test_novograd_oracle_follows_the_published_rule():
+    """oracle.novograd_list against a double-precision restatement of NovoGrad with apex's documented conventions
+    (layer-wise second moment kept as a norm, first step initialised from the gradient norm, bias corrections 1-b1^t and
+    sqrt(1-b2^t)).  UNPINNED against apex itself; rtol 1e-5 against the published rule."""
+    gen = torch.Generator().manual_seed(21)
+    sizes = [5, 4096, 4097, 10000]
+    ps = [torch.randn(n, generator=gen) * 0.1 for n in sizes]
+    ms = [torch.zeros(n) for n in sizes]
+    v = torch.zeros(len(sizes))
+    dp, dm = ([t.double() for t in lst] for lst in (ps, ms))
+    dv = [None] * len(sizes)
+    lr, wd, b1, b2, eps = 1e-2, 0.01, 0.95, 0.98, 1e-8
+    for step in (1, 2, 3):
+        gs = [torch.randn(n, generator=gen) * 0.05 for n in sizes]
+        ss, _, _ = oracle.l2norm_per_tensor(gs, 4096)
+        oracle.novograd_list(gs, ps, ms, v, ss, lr=lr, weight_decay=wd, beta1=b1, beta2=b2, eps=eps, step=step)
+        for i, (p, g, m) in enumerate(zip(dp, gs, dm)):
+            g = g.double()
+            n = g.norm()
+            dv[i] = n if step == 1 else torch.sqrt(b2 * dv[i] ** 2 + (1 - b2) * n ** 2)
+            m.mul_(b1).add_(g, alpha=1 - b1)
+            denom = dv[i] / (1 - b2 ** step) ** 0.5 + eps
+            p.sub_(lr * ((m / (1 - b1 ** step)) / denom + wd * p))
+        torch.testing.assert_close(v.double(), torch.stack(dv), rtol=1e-5, atol=0)
+        for a, b in zip(ps, dp):
+            torch.testing.assert_close(a.double(), b, rtol=1e-5, atol=1e-8)
