@@ -1700,32 +1700,6 @@ __device__ __forceinline__ int step_tile_ready(const PeerStepParams& prm, const 
     return 1;
 }
 
-// A warp has stored its part of a folded piece: count it; the warp that completes a chunk announces it everywhere.
-__device__ __forceinline__ void step_count_piece(const PeerStepParams& prm, long long pb, int warps_per_piece) {
-    __threadfence();
-    __syncwarp();
-    if ((threadIdx.x & 31) == 0) {
-        const long long shard = prm.end - prm.begin;
-        const long long c = (pb - prm.begin) / prm.chunk_elems;
-        const long long c_end = (c + 1) * prm.chunk_elems < shard ? (c + 1) * prm.chunk_elems : shard;
-        const int in_chunk = static_cast<int>((c_end - c * prm.chunk_elems + kPieceElems - 1) / kPieceElems) * warps_per_piece;
-        if (atomicAdd(prm.scratch + 8 + c, 1) == in_chunk - 1) {
-            prm.scratch[8 + c] = 0;                                    // ready for the next step
-            __threadfence_system();
-            for (int r = 0; r < prm.sync.world; r++)
-                st_release_sys(peer_board(prm.sync.pad[r]) + prm.sync.rank * B200_PEER_STEP_MAX_CHUNKS + c, prm.sync.epoch);
-        }
-    }
-}
-
-#ifdef B200_STEP_PROFILE
-#define B200_PROF_DECL long long prof_t = clock64(), prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}; int prof_iters = 0, prof_tiles = 0;
-#define B200_PROF(i) { const long long now_ = clock64(); prof_acc[i] += now_ - prof_t; prof_t = now_; }
-#else
-#define B200_PROF_DECL
-#define B200_PROF(i)
-#endif
-
 template <int G, int S, int C, int kThreads, int kWorld>
 __global__ void __launch_bounds__(kThreads, 2)          // two CTAs per SM, like the plain step kernel: <= 128 registers
 peer_spec_step_kernel(const void* __restrict__ table, const __grid_constant__ PeerStepParams prm) {
