@@ -360,6 +360,80 @@ def _worker_sharded(rank, world, port, repeats, multicast):
     dist.destroy_process_group()
 
 
+def _worker_sharded_training(rank, world, port):
+    """Real ranks: a small fp16 model whose weights live in the peer-addressable model buffer and whose gradients are
+    produced straight into the flat gradient buffer, trained with PeerShardedStep."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    from apex_example_b200.parallel.peer import PeerBuffers, PeerShardedStep
+    torch.manual_seed(0)                                             # the same initial weights on every rank
+    model = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 10)).cuda().half()
+    params = list(model.parameters())
+    sizes = [p.numel() for p in params]
+    offs, total = _layout(sizes)
+    mc = ("grads", "model") if world >= 4 else ()
+    bufs = PeerBuffers(total, torch.float16, names=("grads", "model"), multicast=mc)
+    g_flat, w_flat = bufs.local["grads"], bufs.local["model"]
+    for p, o, n in zip(params, offs, sizes):
+        w_flat[o:o + n].copy_(p.data.view(-1))
+        p.data = w_flat[o:o + n].view_as(p)
+        p.grad = g_flat[o:o + n].view_as(p)
+    stepper = PeerShardedStep(bufs, offs, sizes, use_multicast="both" if world >= 4 else "none")
+    state = torch.zeros(ops.SCALER_WORDS, dtype=torch.int32, device="cuda")
+    ops.scaler_init(state, 1024.0)
+    fs = state.view(torch.float32)
+    gen = torch.Generator().manual_seed(1)
+    x_all = torch.randn(32 * world, 64, generator=gen)
+    y_all = torch.randint(0, 10, (32 * world,), generator=gen)
+    x, y = x_all[rank * 32:(rank + 1) * 32].cuda().half(), y_all[rank * 32:(rank + 1) * 32].cuda()
+    losses, good = [], 0
+    for it in range(14):
+        g_flat.zero_()
+        loss = torch.nn.functional.cross_entropy(model(x).float(), y)
+        scaled = loss * fs[ops.IDX_LOSS_SCALE]
+        if it == 5 and rank == world - 1:
+            scaled = scaled * float("inf")                          # overflow on the last rank only
+        scaled.backward()
+        assert params[0].grad.data_ptr() == g_flat.data_ptr() + 2 * offs[0], "autograd replaced the gradient view"
+        before = w_flat.clone()
+        stepper.step([ops.AdamGroup(1e-2, 0.9, 0.999, 1e-8, 0.0, good + 1, 1, 1)], state)
+        torch.cuda.synchronize()
+        found = int(state.cpu()[ops.IDX_FOUND_INF])
+        assert found == (1 if it == 5 else 0), f"rank {rank}: skip decision at iteration {it}"
+        if found:
+            assert torch.equal(w_flat, before), f"rank {rank}: weights changed on a skipped step"
+        else:
+            good += 1
+            assert not torch.equal(w_flat, before)
+            losses.append(float(loss))
+        dist.barrier()
+    assert all(l == l and abs(l) < 1e4 for l in losses)
+    mean_loss = torch.tensor([losses[0], losses[-1]], device="cuda")
+    dist.all_reduce(mean_loss)
+    assert float(mean_loss[1]) < 0.8 * float(mean_loss[0]), f"loss did not fall: {mean_loss.tolist()}"
+    parts = [torch.empty_like(w_flat) for _ in range(world)]
+    dist.all_gather(parts, w_flat)
+    assert all(torch.equal(parts[0], q) for q in parts[1:]), "ranks hold different weights"
+    assert float(fs[ops.IDX_LOSS_SCALE]) == 512.0
+    torch.cuda.synchronize()
+    bufs.check_signals()
+    for p in params:
+        p.grad = None
+    del stepper, params, model, g_flat, w_flat, parts, before
+    bufs.close()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_real_rank_training_with_the_sharded_step(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs (run under gpurun --gpus {world})")
+    mp.spawn(_worker_sharded_training, args=(world, _free_port()), nprocs=world, join=True)
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("multicast", ["none", "stores", "both"])
 def test_real_rank_sharded_step(world, multicast):
