@@ -84,6 +84,10 @@ def config_dict(desc, world, collective="peer", note=None, step_mode="spec"):
                     ("speculative single pass (check + unscale + AdamW + fp16 copy into double-buffered state) -> "
                      "scaler update + commit -> repair-if-skipped") if spec else
                     "check|allreduce+epilogue -> scaler update -> fused unscale+AdamW+fp16 copy",
+            "value_counts": "28 B/param x params x ranks / step time: the bytes a replicated-state step of this N-rank job moves "
+                            "(the N = 1 unit); with the sharded step fewer bytes really move — see roofline.algorithmic_bytes_per_launch "
+                            "and roofline.nvlink" if (step_mode == "sharded" and world > 1 and collective == "peer") else
+                            "28 B/param x params x ranks / step time",
             "parallelism": f"dp{world}", "bucket_elems": BUCKET_ELEMS, "collective": coll, "collective_note": note}
 
 

@@ -26,7 +26,7 @@ def test_reference_arm_prints_the_contract_line():
     assert d["metric"] == "fused optimizer step HBM GB/s" and d["unit"] == "GB/s" and d["higher_is_better"] is True
     assert d["vs_baseline"] is None and "workload" in d["config"] and "model" not in d["config"]
     assert d["warmup"] == 3 and d["steps"] == 1          # W >= 3 like the B200 arm, K as asked
-    assert set(d["config"]) == {"workload", "l2", "step", "parallelism", "bucket_elems", "collective", "collective_note"}
+    assert set(d["config"]) == {"workload", "l2", "step", "value_counts", "parallelism", "bucket_elems", "collective", "collective_note"}
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
