@@ -174,3 +174,34 @@ def test_header_is_plain_c_and_the_library_links_from_c(tmp_path):
     subprocess.run([cc, "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe),
                     "-L", libdir, "-l:" + os.path.basename(_lib.SO_PATH), "-Wl,-rpath," + libdir], check=True)
     assert subprocess.run([str(exe)]).returncode == 0
+
+
+def test_ctypes_structs_match_the_header_field_by_field(tmp_path):
+    """Every struct that crosses the C ABI by value or pointer: size and the offset of every field as gcc lays the header
+    out, against the ctypes mirror in apex_example_b200/_lib.py (guards against a field added on one side only)."""
+    import subprocess
+    pairs = {"b200_adam_group": _lib.AdamGroup, "b200_sgd_group": _lib.SgdGroup, "b200_lamb_group": _lib.LambGroup,
+             "b200_novograd_group": _lib.NovoGradGroup, "b200_step_sync": _lib.StepSync, "b200_peer_sync": _lib.PeerSync,
+             "b200_peer_pull": _lib.PeerPull, "b200_peer_fan": _lib.PeerFan, "b200_table_header": _lib.TableHeader}
+    header_names = {"b200_step_sync": {"dev_counters": "dev_counters"}}
+    lines = ["#include <stdio.h>", "#include <stddef.h>", '#include "apex_b200.h"', "int main(void) {"]
+    for cname, cls in pairs.items():
+        lines.append(f'    printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            hname = header_names.get(cname, {}).get(fname, fname)
+            lines.append(f'    printf("{cname} {fname} %zu\\n", offsetof({cname}, {hname}));')
+    lines += ["    return 0;", "}"]
+    src = tmp_path / "probe.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "probe"
+    inc = os.path.join(ROOT, "include")
+    subprocess.run(["gcc", "-std=c99", "-I", inc, str(src), "-o", str(exe)], check=True, capture_output=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout
+    got = {}
+    for line in out.splitlines():
+        cname, fname, val = line.split()
+        got[(cname, fname)] = int(val)
+    for cname, cls in pairs.items():
+        assert got[(cname, "size")] == ctypes.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert got[(cname, fname)] == getattr(cls, fname).offset, f"{cname}.{fname}"
