@@ -148,6 +148,26 @@ def test_kernel_entry_points_validate_arguments_without_a_gpu():
     assert lib.b200_multi_tensor_scale(None, 1, 7, _lib.F32, 1.0, None, None, None) == -3
     assert lib.b200_bucket_epilogue(None, -1, _lib.F16, 1.0, None, None) == -1
     assert lib.b200_set_launch_config(0, 100, 2) == -1
+    # round-2 entry points: everything that can be refused is refused before the first CUDA call
+    ok = (_lib.AdamGroup * 1)(_lib.AdamGroup(1e-3, 0.9, 0.999, 1e-8, 0.0, 1, 1, 1))
+    dummy = ctypes.c_void_p(256)
+    assert lib.b200_fused_adam_spec(None, 1, _lib.F16, _lib.F32, _lib.F16, ok, 1, 1.0, None, None, None, None, None, None) == -1  # no parity word
+    assert lib.b200_peer_shard_step(None, 1, _lib.F16, _lib.F32, _lib.F16, ok, 1, 1.0, None, None, None, None, None, None, None) == -1
+    assert lib.b200_peer_shard_step(None, 1, _lib.F16, _lib.F32, _lib.F16, ok, 1, 1.0, None, None, dummy, None, None, None, None) == -1  # no fan
+    fan = _lib.PeerFan()
+    fan.world, fan.rank = 9, 0
+    assert lib.b200_peer_shard_step(None, 1, _lib.F16, _lib.F32, _lib.F16, ok, 1, 1.0, None, None, dummy, None, ctypes.byref(fan), None, None) == -1
+    assert "world 9" in lib.b200_last_error().decode()
+    fan.world = 2
+    assert lib.b200_peer_shard_repair(None, 1, _lib.F32, _lib.F16, dummy, dummy, ctypes.byref(fan), None, None) == -1   # NULL buffers
+    assert lib.b200_l2norm_per_tensor(None, 1, 0, 7, None, 1, None, None, None, None, None, None) == -3                 # dtype
+    assert lib.b200_l2norm_per_tensor(None, 1, 9, _lib.F32, None, 1, None, None, None, None, None, None) == -1         # column
+    lg = (_lib.LambGroup * 1)(_lib.LambGroup(1e-3, 0.9, 0.999, 1e-6, 0.01, 1, 1, 1, 1, 0))
+    assert lib.b200_lamb_stage1(None, 1, _lib.F16, _lib.F32, lg, 1, 1.0, None, None, None, 1.0, None) == -1             # no gradient norm
+    assert lib.b200_lamb_stage2(None, 1, _lib.F32, _lib.F16, lg, 1, None, None, None, None) == -1                        # no norm arrays
+    ng = (_lib.NovoGradGroup * 1)(_lib.NovoGradGroup(1e-3, 0.9, 0.999, 1e-8, 0.0, 0, 1, 0, 1, 0))
+    assert lib.b200_fused_novograd(None, 1, _lib.F16, _lib.F32, _lib.F16, ng, 1, 1.0, None, None, dummy, None) == -1     # step 0
+    assert lib.b200_fused_novograd(None, 1, _lib.F16, _lib.F32, _lib.F16, ng, 1, 1.0, None, None, None, None) == -1      # no moments
     with pytest.raises(RuntimeError):
         _lib.check(lib.b200_set_launch_config(0, 256, 3), "set_launch_config")
     assert lib.b200_set_launch_config(0, 256, 2) == 0
